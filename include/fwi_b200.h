@@ -1,0 +1,111 @@
+/* fwi_b200.h — C ABI of the B200-native finite-difference wave propagator.
+ *
+ * This is the drop-in boundary of the hot path: everything the reference reaches through
+ *     deepwave.scalar.Propagator({'vp': v}, dx)(source_amplitudes, x_s, x_r, dt)
+ * (reference call sites models/networks.py:5408-5411, :5449, :5464) and through the autograd
+ * backward of that call (models/networks.py:5491).  The reference itself has no native
+ * interface for this path (deepwave is an external Python/C/CUDA package), so the entry points
+ * below are what a binding for the path has to offer: plain pointers, sizes and a CUDA stream.
+ * No torch types appear here; physicsbasedfwi2_b200/scalar.py binds them with ctypes.
+ *
+ * All pointers are DEVICE pointers unless marked host.  All calls are asynchronous on `stream`
+ * (a cudaStream_t passed as void*), never allocate, and return 0 on success or a negative
+ * fwi_status; fwi_last_error() gives the thread-local message of the last failure.
+ *
+ * Scheme (derivation of the adjoint in DESIGN.md):
+ *   q    = Lap(u) + Dz(pz) + Dy(py)
+ *   u+   = cu*u + cum*u- + a*w*q ,  w = v^2 dt^2, a = 1/(1 + dt(sz+sy)/2)
+ *   pz+  = (1 - dt sz) pz - dt (sz - sy) Dz(u),   py+ likewise
+ *   u+[inj cells] += coef * amp(t)
+ * The adjoint pass is the same recurrence run backwards in time on mu = a*w*lambda, so one
+ * kernel family serves forward (models/networks.py:5464) and backward (:5491).
+ */
+#ifndef FWI_B200_H
+#define FWI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum fwi_status {
+    FWI_OK = 0,
+    FWI_ERR_ARG = -1,     /* bad descriptor / null pointer / unsupported order */
+    FWI_ERR_CUDA = -2,    /* a CUDA runtime call or launch failed */
+    FWI_ERR_NODEVICE = -3 /* no sm_100 device */
+};
+
+/* ---- acoustic (constant density, 2-D) ------------------------------------------------- */
+
+/* Problem descriptor (host POD).  Padded grid = model + 2*(pml_width + order/2) per axis; the
+ * outermost order/2 ring is never updated and stays zero. */
+typedef struct fwi_acoustic_desc {
+    int32_t nzp, nyp;         /* padded grid extents (z slow, y fast) */
+    int32_t order;            /* spatial accuracy: 2, 4, 6 or 8 */
+    int32_t pml_width;        /* cells of PML on each of the four sides (0 = none) */
+    int32_t n_shots;          /* shots advanced together by one call */
+    int32_t shots_per_group;  /* shots one CTA walks per launch (w / image amortisation); 0 = auto */
+    int32_t nsteps;           /* inner time steps */
+    int32_t adjoint;          /* 0: n = 0..nsteps-1;  1: n = nsteps-1..0 (time-reversed driver) */
+    int32_t n_inj;            /* injection points per shot (sources fwd / receivers adj) */
+    int32_t inj_scale_a;      /* 1: injection coefficient a*w (adjoint), 0: w (forward) */
+    int32_t n_smp;            /* sampling points per shot (receivers fwd / sources adj) */
+    int32_t smp_div_a;        /* 1: sampled value divided by a (adjoint source gradient) */
+    double dz, dy, dt;        /* grid spacings (m) and inner time step (s) */
+} fwi_acoustic_desc;
+
+/* Device memory layout chosen by the library for a descriptor (host POD, output). */
+typedef struct fwi_acoustic_layout {
+    int32_t pitch;            /* floats per grid row in device arrays (multiple of 32) */
+    int32_t col0;             /* device column that holds padded column 0 */
+    int64_t shot_stride;      /* floats per shot per field = nzp * pitch */
+    int32_t tile_z, tile_y;   /* CTA tile (cells) */
+    int32_t tiles_z, tiles_y; /* tiles over the computational region */
+    int32_t n_groups;         /* shot groups = image partial buffers */
+    int32_t wave_fields;      /* number of [n_shots][nzp][pitch] fields in the workspace */
+} fwi_acoustic_layout;
+
+/* Buffers of one propagation (host struct of device pointers). */
+typedef struct fwi_acoustic_buffers {
+    const float *w;           /* [nzp][pitch]   v^2 dt^2 on the padded grid */
+    const float *sigz;        /* [nzp]          PML profile along z */
+    const float *sigy;        /* [pitch]        PML profile along y, device columns */
+    float *wave;              /* [wave_fields][n_shots][nzp][pitch], zero on entry: u, u-, pz, pz+, py, py+ */
+    const int32_t *inj_tile_start; /* [n_shots][tiles_z*tiles_y + 1] offsets into the two lists below */
+    const int32_t *inj_cell;  /* [n_shots*n_inj] device cell (z*pitch + col), grouped by (shot, tile) */
+    const int32_t *inj_col;   /* [n_shots*n_inj] column of inj_amp each entry reads */
+    const float *inj_amp;     /* [nsteps][n_shots][n_inj] */
+    const int32_t *smp_cell;  /* [n_shots][n_smp] device cell */
+    float *smp_out;           /* [nsteps][n_shots][n_smp] */
+    float *q_write;           /* [nsteps][n_shots][nzp][pitch] or NULL: snapshot of q per step */
+    const float *q_read;      /* same layout or NULL: snapshots consumed by the imaging sum */
+    float *image;             /* [n_groups][nzp][pitch] or NULL: image += field * q_read */
+} fwi_acoustic_buffers;
+
+/* Fills `out` for `desc`.  Replaces nothing in the reference (layout is private to deepwave
+ * there); needed so a host can size and fill the arrays above. */
+int fwi_acoustic_get_layout(const fwi_acoustic_desc *desc, fwi_acoustic_layout *out);
+
+/* Runs desc->nsteps steps.  Per step n:  smp_out[n] = field[smp_cell] (/a);  [image += field *
+ * q_read[n]];  advance (writing q_write[n]);  field+[inj_cell] += coef * inj_amp[n].
+ * adjoint=0 replaces the time loop of deepwave's forward (models/networks.py:5464);
+ * adjoint=1 with q_read/image replaces its backward (models/networks.py:5491). */
+int fwi_acoustic_run(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);
+
+/* Named wrappers with the direction fixed (argument checks differ). */
+int fwi_acoustic_forward(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);
+int fwi_acoustic_backward(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);
+
+/* ---- common ---------------------------------------------------------------------------- */
+
+const char *fwi_last_error(void);     /* thread-local, never NULL */
+int fwi_version(void);                /* ABI version, bumps on any struct change */
+int64_t fwi_kernel_launches(void);    /* kernels launched by this library in this process */
+int fwi_device_ok(int device);        /* FWI_OK if `device` is sm_100 */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FWI_B200_H */

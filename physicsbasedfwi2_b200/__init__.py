@@ -1,0 +1,12 @@
+"""physicsbasedfwi2_b200 — B200-native finite-difference wave propagator for FWI.
+
+Drop-in for the propagator path of ADharaUTEXAS123007/PhysicsBasedFWI2 (the deepwave-style
+call ``Propagator({'vp'[, 'vs', 'rho']}, dx)(source_amplitudes, x_s, x_r, dt)``; reference
+call sites models/networks.py:5408-5411, :5449, :5464, :5491).  The hot path is hand-written
+sm_100a CUDA behind the C ABI in include/fwi_b200.h; there is no CPU fallback.
+"""
+from . import wavelets  # noqa: F401
+from . import scalar  # noqa: F401
+from ._lib import build, kernel_launches, lib  # noqa: F401
+
+__all__ = ["scalar", "wavelets", "build", "lib", "kernel_launches"]

@@ -1,0 +1,105 @@
+"""ctypes binding of libfwi_b200.so (the C ABI declared in include/fwi_b200.h).
+
+The product path has no CPU fallback: if the library is missing or a call fails, a
+RuntimeError is raised (deepwave raises RuntimeError for bad arguments too).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import shutil
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_CSRC = os.path.join(_HERE, "csrc")
+SO_PATH = os.path.join(_HERE, "libfwi_b200.so")
+_SOURCES = ["common.cu", "acoustic.cu", "elastic.cu", "persist.cu"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
+
+
+class AcousticDesc(C.Structure):
+    _fields_ = [("nzp", C.c_int32), ("nyp", C.c_int32), ("order", C.c_int32),
+                ("pml_width", C.c_int32), ("n_shots", C.c_int32), ("shots_per_group", C.c_int32),
+                ("nsteps", C.c_int32), ("adjoint", C.c_int32), ("n_inj", C.c_int32),
+                ("inj_scale_a", C.c_int32), ("n_smp", C.c_int32), ("smp_div_a", C.c_int32),
+                ("dz", C.c_double), ("dy", C.c_double), ("dt", C.c_double)]
+
+
+class AcousticLayout(C.Structure):
+    _fields_ = [("pitch", C.c_int32), ("col0", C.c_int32), ("shot_stride", C.c_int64),
+                ("tile_z", C.c_int32), ("tile_y", C.c_int32), ("tiles_z", C.c_int32),
+                ("tiles_y", C.c_int32), ("n_groups", C.c_int32), ("wave_fields", C.c_int32)]
+
+
+class AcousticBuffers(C.Structure):
+    _fields_ = [("w", C.c_void_p), ("sigz", C.c_void_p), ("sigy", C.c_void_p),
+                ("wave", C.c_void_p), ("inj_tile_start", C.c_void_p), ("inj_cell", C.c_void_p),
+                ("inj_col", C.c_void_p), ("inj_amp", C.c_void_p), ("smp_cell", C.c_void_p),
+                ("smp_out", C.c_void_p), ("q_write", C.c_void_p), ("q_read", C.c_void_p),
+                ("image", C.c_void_p)]
+
+
+def sources():
+    return [os.path.join(_CSRC, s) for s in _SOURCES if os.path.exists(os.path.join(_CSRC, s))]
+
+
+def is_stale() -> bool:
+    if not os.path.exists(SO_PATH):
+        return True
+    t = os.path.getmtime(SO_PATH)
+    deps = sources() + [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".h", ".cuh"))]
+    deps.append(os.path.join(_HERE, "..", "include", "fwi_b200.h"))
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile every CUDA source for sm_100a into the in-tree libfwi_b200.so (nvcc cross-compiles
+    without a GPU)."""
+    if not force and not is_stale():
+        return SO_PATH
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        raise RuntimeError("nvcc not found: cannot build libfwi_b200.so")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO_PATH] + sources()
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(r.stderr)
+    return SO_PATH
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Loads libfwi_b200.so.  Never falls back to anything else."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise RuntimeError(
+            f"{SO_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU or PyTorch fallback for the propagator)")
+    L = C.CDLL(SO_PATH)
+    L.fwi_last_error.restype = C.c_char_p
+    L.fwi_version.restype = C.c_int
+    L.fwi_kernel_launches.restype = C.c_int64
+    L.fwi_device_ok.argtypes = [C.c_int]
+    L.fwi_acoustic_get_layout.argtypes = [C.POINTER(AcousticDesc), C.POINTER(AcousticLayout)]
+    for name in ("fwi_acoustic_run", "fwi_acoustic_forward", "fwi_acoustic_backward"):
+        getattr(L, name).argtypes = [C.POINTER(AcousticDesc), C.POINTER(AcousticBuffers), C.c_void_p]
+        getattr(L, name).restype = C.c_int
+    _lib = L
+    return L
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().fwi_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"{what} failed (status {rc}): {msg}")
+
+
+def kernel_launches() -> int:
+    return int(lib().fwi_kernel_launches())

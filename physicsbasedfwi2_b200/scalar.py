@@ -1,0 +1,245 @@
+"""deepwave-style scalar (constant-density acoustic) propagator on the B200 kernels.
+
+Drop-in for the call the reference makes every training iteration
+(models/networks.py:5408-5411, :5449, :5464, backward at :5491):
+
+    prop = Propagator({'vp': model}, dx)
+    receiver_amplitudes = prop(source_amplitudes, x_s, x_r, dt)     # [nt, shots, receivers]
+    loss(receiver_amplitudes, ...).backward()                        # -> model.grad, src.grad
+
+The time loops run in libfwi_b200.so (sm_100a kernels, include/fwi_b200.h).  There is no CPU
+path: tensors must live on a CUDA device and the library must be built.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import _host as H
+from . import _lib
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class _Plan:
+    """Everything about one call that does not depend on the direction of time."""
+
+    def __init__(self, v: torch.Tensor, dx, dt: float, order: int, pml_width: int,
+                 vpmax: Optional[float], n_shots: int, shots_per_group: int = 0):
+        if v.dim() != 2:
+            raise RuntimeError(f"model['vp'] must be 2-D [nz, ny], got shape {tuple(v.shape)}")
+        if not v.is_cuda:
+            raise RuntimeError("model['vp'] must be a CUDA tensor: this propagator has no CPU path")
+        if v.dtype != torch.float32:
+            raise RuntimeError(f"model['vp'] must be float32, got {v.dtype}")
+        if order not in (2, 4, 6, 8):
+            raise RuntimeError(f"accuracy must be 2, 4, 6 or 8, got {order}")
+        self.dev = v.device
+        self.dz, self.dy = H.spacing(dx)
+        self.nz, self.ny = int(v.shape[0]), int(v.shape[1])
+        self.order, self.h, self.pw = order, order // 2, int(pml_width)
+        self.P = self.pw + self.h
+        self.nzp, self.nyp = self.nz + 2 * self.P, self.ny + 2 * self.P
+        self.vmax = float(vpmax) if vpmax is not None else float(v.detach().abs().max())
+        self.ratio, self.dti = H.inner_step(float(dt), self.dz, self.dy, self.vmax)
+        self.S = n_shots
+        self.spg = shots_per_group
+
+        lay = _lib.AcousticLayout()
+        d = self.desc(nsteps=0, adjoint=0, n_inj=0, n_smp=0)
+        _lib.check(_lib.lib().fwi_acoustic_get_layout(C.byref(d), C.byref(lay)), "fwi_acoustic_get_layout")
+        self.lay = lay
+        self.pitch, self.col0 = int(lay.pitch), int(lay.col0)
+        self.stride = int(lay.shot_stride)
+        self.n_tiles = int(lay.tiles_z) * int(lay.tiles_y)
+
+        vp = F.pad(v.detach()[None, None], (self.P,) * 4, mode="replicate")[0, 0]
+        self.v_pad = vp
+        dti = torch.tensor(self.dti, dtype=torch.float32, device=self.dev)
+        self.w = torch.zeros(self.nzp, self.pitch, dtype=torch.float32, device=self.dev)
+        self.w[:, self.col0:self.col0 + self.nyp] = (vp * vp) * (dti * dti)
+        sz = H.sigma_profile(self.nzp, self.h, self.pw, self.dz, self.vmax).float()
+        sy = torch.zeros(self.pitch, dtype=torch.float32)
+        sy[self.col0:self.col0 + self.nyp] = H.sigma_profile(self.nyp, self.h, self.pw, self.dy, self.vmax).float()
+        self.sigz, self.sigy = sz.to(self.dev), sy.to(self.dev)
+
+    def desc(self, nsteps, adjoint, n_inj, n_smp) -> _lib.AcousticDesc:
+        return _lib.AcousticDesc(self.nzp, self.nyp, self.order, self.pw, self.S, self.spg, nsteps,
+                                 adjoint, n_inj, 1 if adjoint else 0, n_smp, 1 if adjoint else 0,
+                                 self.dz, self.dy, self.dti)
+
+    def points(self, x: torch.Tensor, what: str, loc_mode: str):
+        """[S, n, 2] metres -> (cell [S, n] int32, z [S, n], ycol [S, n]) in device layout + bad flag."""
+        c = H.to_cells(x.to(self.dev), self.dz, self.dy, loc_mode)
+        bad = ((c[..., 0] < 0) | (c[..., 0] >= self.nz) | (c[..., 1] < 0) | (c[..., 1] >= self.ny)).any()
+        z = c[..., 0].clamp(0, self.nz - 1) + self.P
+        ycol = c[..., 1].clamp(0, self.ny - 1) + self.P + self.col0
+        cell = z * self.pitch + ycol
+        return cell, z, ycol, bad
+
+    def lists(self, cell, z, ycol):
+        L = self.lay
+        return H.tile_lists(cell, z, ycol, self.h, self.col0 + self.h, int(L.tile_z), int(L.tile_y),
+                            int(L.tiles_y), self.n_tiles)
+
+    def run(self, *, nsteps, adjoint, inj, inj_amp, smp_cell, n_smp, q_write=None, q_read=None,
+            image=None) -> torch.Tensor:
+        """One time loop.  inj = (start, cell, col) lists; returns smp_out [nsteps, S, n_smp]."""
+        n_inj = 0 if inj_amp is None else int(inj_amp.shape[2])
+        d = self.desc(nsteps, adjoint, n_inj, n_smp)
+        wave = torch.zeros(int(self.lay.wave_fields) * self.S * self.stride, dtype=torch.float32, device=self.dev)
+        smp_out = torch.empty(nsteps, self.S, n_smp, dtype=torch.float32, device=self.dev)
+        start, icell, icol = inj
+        b = _lib.AcousticBuffers(_ptr(self.w), _ptr(self.sigz), _ptr(self.sigy), _ptr(wave), _ptr(start),
+                                 _ptr(icell), _ptr(icol), _ptr(inj_amp), _ptr(smp_cell), _ptr(smp_out),
+                                 _ptr(q_write), _ptr(q_read), _ptr(image))
+        stream = torch.cuda.current_stream(self.dev).cuda_stream
+        with torch.cuda.device(self.dev):
+            fn = _lib.lib().fwi_acoustic_backward if adjoint else _lib.lib().fwi_acoustic_forward
+            _lib.check(fn(C.byref(d), C.byref(b), C.c_void_p(stream)),
+                       "fwi_acoustic_backward" if adjoint else "fwi_acoustic_forward")
+        return smp_out
+
+
+class _ScalarFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, v, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, loc_mode,
+                shots_per_group):
+        if source_amplitudes.dim() != 3:
+            raise RuntimeError("source_amplitudes must be [nt, n_shots, n_sources_per_shot]")
+        nt, S, Ns = source_amplitudes.shape
+        if x_s.dim() != 3 or x_s.shape[0] != S or x_s.shape[1] != Ns or x_s.shape[2] != 2:
+            raise RuntimeError(f"source_locations must be [{S}, {Ns}, 2], got {tuple(x_s.shape)}")
+        if x_r.dim() != 3 or x_r.shape[0] != S or x_r.shape[2] != 2:
+            raise RuntimeError(f"receiver_locations must be [{S}, n_receivers, 2], got {tuple(x_r.shape)}")
+        R = int(x_r.shape[1])
+        plan = _Plan(v, dx, dt, order, pml_width, vpmax, S, shots_per_group)
+        dev = plan.dev
+        s_cell, s_z, s_y, bad_s = plan.points(x_s, "source", loc_mode)
+        r_cell, r_z, r_y, bad_r = plan.points(x_r, "receiver", loc_mode)
+        if bool((bad_s | bad_r).item()):
+            raise RuntimeError("source/receiver location outside the model")
+        amp = H.resample_up(source_amplitudes.detach().to(dev, torch.float32), plan.ratio).contiguous()
+        nti = nt * plan.ratio
+        need_v = ctx.needs_input_grad[0]
+        need_s = ctx.needs_input_grad[1]
+        q = None
+        if need_v:
+            q = torch.empty(nti * S * plan.stride, dtype=torch.float32, device=dev)
+        r32 = r_cell.to(torch.int32).contiguous()
+        rec = plan.run(nsteps=nti, adjoint=0, inj=plan.lists(s_cell, s_z, s_y), inj_amp=amp,
+                       smp_cell=r32, n_smp=R, q_write=q)
+        out = rec[::plan.ratio].contiguous() if plan.ratio > 1 else rec
+        ctx.plan = plan
+        ctx.q = q
+        ctx.amp = amp if need_v else None
+        ctx.geom = (s_cell, r_cell, r_z, r_y, nt, S, Ns, R, nti)
+        ctx.need = (need_v, need_s)
+        ctx.src_like = source_amplitudes.detach()
+        return out
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, grad_rec):
+        plan: _Plan = ctx.plan
+        s_cell, r_cell, r_z, r_y, nt, S, Ns, R, nti = ctx.geom
+        need_v, need_s = ctx.need
+        dev = plan.dev
+        g = grad_rec.to(dev, torch.float32)
+        if plan.ratio > 1:
+            g_in = torch.zeros(nti, S, R, dtype=torch.float32, device=dev)
+            g_in[::plan.ratio] = g
+        else:
+            g_in = g.contiguous()
+        image = None
+        if need_v:
+            image = torch.zeros(int(plan.lay.n_groups) * plan.stride, dtype=torch.float32, device=dev)
+        gs = plan.run(nsteps=nti, adjoint=1, inj=plan.lists(r_cell, r_z, r_y), inj_amp=g_in,
+                      smp_cell=s_cell.to(torch.int32).contiguous(), n_smp=Ns,
+                      q_read=ctx.q if need_v else None, image=image)
+        grad_v = grad_s = None
+        if need_v:
+            G = image.view(int(plan.lay.n_groups), plan.nzp, plan.pitch).sum(0)
+            G = G[:, plan.col0:plan.col0 + plan.nyp].contiguous()
+            # the source term of dJ/dw: mu/a sampled at the source cells times the wavelet
+            flat = G.view(-1)
+            pcell = ((s_cell // plan.pitch) * plan.nyp + (s_cell % plan.pitch - plan.col0)).reshape(-1)
+            flat.index_add_(0, pcell, (gs * ctx.amp).sum(0).reshape(-1))
+            gpad = (2.0 / plan.v_pad) * G
+            grad_v = H.replicate_pad_adjoint(gpad, plan.P)
+        if need_s:
+            grad_s = H.resample_up_adjoint(gs, plan.ratio, ctx.src_like.to(dev, torch.float32))
+            grad_s = grad_s.to(ctx.src_like.device, ctx.src_like.dtype)
+        ctx.q = None
+        return grad_v, grad_s, None, None, None, None, None, None, None, None, None
+
+
+class Propagator(torch.nn.Module):
+    """``deepwave.scalar.Propagator`` (v0.0.x class API) on the B200 kernels.
+
+    Args follow the reference's usage (models/networks.py:5408, :5449): ``model`` is a dict with
+    key ``'vp'`` holding a float32 CUDA tensor [nz, ny]; ``dx`` a float or (dz, dy).
+    ``pml_width`` (int, default 10), ``survey_pad`` (None or cells) and ``vpmax`` as in deepwave.
+    Extensions: ``accuracy`` (2/4/6/8, default 4), ``loc_mode`` ('trunc' | 'round'),
+    ``shots_per_group`` (kernel tuning, 0 = auto).
+    """
+
+    def __init__(self, model: dict, dx, pml_width=None, survey_pad=None, vpmax=None, *,
+                 accuracy: int = 4, loc_mode: str = "trunc", shots_per_group: int = 0):
+        super().__init__()
+        if not isinstance(model, dict) or "vp" not in model:
+            raise RuntimeError("model must be a dict with key 'vp'")
+        extra = set(model) - {"vp"}
+        if extra:
+            raise RuntimeError(f"scalar propagator takes only 'vp'; got extra keys {sorted(extra)} "
+                               "(use physicsbasedfwi2_b200.Propagator for vp/vs/rho)")
+        if not isinstance(model["vp"], torch.Tensor):
+            raise RuntimeError("model['vp'] must be a torch.Tensor")
+        self.model = model
+        self.dx = dx
+        if pml_width is None:
+            pml_width = 10
+        if not isinstance(pml_width, int):
+            vals = [int(p) for p in (pml_width.tolist() if isinstance(pml_width, torch.Tensor) else pml_width)]
+            if len(set(vals)) != 1:
+                raise RuntimeError("pml_width must be the same on every side")
+            pml_width = vals[0]
+        if pml_width < 0:
+            raise RuntimeError("pml_width must be >= 0")
+        self.pml_width = pml_width
+        self.survey_pad = survey_pad
+        self.vpmax = vpmax
+        self.accuracy = accuracy
+        self.loc_mode = loc_mode
+        self.shots_per_group = shots_per_group
+
+    def forward(self, source_amplitudes: torch.Tensor, source_locations: torch.Tensor,
+                receiver_locations: torch.Tensor, dt: float) -> torch.Tensor:
+        v = self.model["vp"]
+        x_s, x_r = source_locations, receiver_locations
+        if self.survey_pad is not None:
+            v, x_s, x_r = _crop_to_survey(v, self.dx, x_s, x_r, self.survey_pad)
+        return _ScalarFunction.apply(v, source_amplitudes, x_s, x_r, float(dt), self.dx, self.accuracy,
+                                     self.pml_width, self.vpmax, self.loc_mode, self.shots_per_group)
+
+
+def _crop_to_survey(v, dx, x_s, x_r, survey_pad):
+    """Restricts the model to the bounding box of the survey plus `survey_pad` cells."""
+    dz, dy = H.spacing(dx)
+    pad = survey_pad if isinstance(survey_pad, (list, tuple)) else [survey_pad] * 4
+    pad = [0 if p is None else int(p) for p in pad]
+    if len(pad) == 2:
+        pad = [pad[0], pad[0], pad[1], pad[1]]
+    allx = torch.cat([x_s.reshape(-1, 2), x_r.reshape(-1, 2)], 0).double().cpu()
+    zc, yc = allx[:, 0] / dz, allx[:, 1] / dy
+    z0 = max(0, int(torch.floor(zc.min() + 1e-6)) - pad[0])
+    z1 = min(v.shape[0], int(torch.floor(zc.max() + 1e-6)) + pad[1] + 1)
+    y0 = max(0, int(torch.floor(yc.min() + 1e-6)) - pad[2])
+    y1 = min(v.shape[1], int(torch.floor(yc.max() + 1e-6)) + pad[3] + 1)
+    off = torch.tensor([z0 * dz, y0 * dy], dtype=x_s.dtype, device=x_s.device)
+    return v[z0:z1, y0:y1], x_s - off, x_r - off.to(x_r.device, x_r.dtype)
