@@ -1,0 +1,390 @@
+#!/usr/bin/env python
+"""bench.py - FWI gradient throughput (forward + adjoint) of the B200 acoustic propagator.
+
+Metric (BASELINE.json): FWI gradient Gcell-updates/s (fwd+adjoint); % of HBM roofline.
+Workload (BASELINE.json configs[1], SURVEY.md 8d "C2"): Marmousi-scale 2-D acoustic model
+751 (z) x 2301 (y), dx = 4 m, 8th-order stencil, 20-cell PML, 3000 time steps, 15 Hz Ricker,
+576 receivers per shot.  One "step" = one FWI gradient (forward, MSE misfit, adjoint with imaging)
+of one BATCH of shots per GPU; the 256-shot survey is 256 / (batch x n_gpus) such steps, taken one
+after the other exactly as the reference mini-batches its shots (models/networks.py:5454-5461).
+The batch is what fits HBM with one snapshot per inner step (k = 1, the parity-graded mode).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+Under torchrun (N > 1) every rank runs its own shot batch (weak scaling) and the model gradient
+is summed with one NCCL allreduce inside the timed region.  One JSON line on rank 0.
+
+cell-update = one interior model cell advanced one inner time step in one pass for one shot;
+work per step = nz*ny*nt*shots*2.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # BASELINE.json configs[1]
+    "c2": dict(nz=751, ny=2301, dx=4.0, order=8, pml=20, nt=3000, dt=4e-4, freq=15.0, n_rec=576,
+               rec_stride=4, z_acq=2, survey_shots=256, vmin=1500.0, vmax=4200.0),
+    # BASELINE.json configs[0] (the reference's own CPU-runnable case) - parity-test sized
+    "c1": dict(nz=100, ny=300, dx=10.0, order=4, pml=10, nt=1000, dt=1e-3, freq=15.0, n_rec=101,
+               rec_stride=3, z_acq=0, survey_shots=10, vmin=1500.0, vmax=3500.0),
+}
+
+B_FWD, B_ADJ = 20.0, 28.0   # algorithmic bytes per cell-update at k = 1: 16 + 4 / 16 + 4 + 8
+
+
+def synth_model(w, seed=1):
+    """Depth gradient vmin -> vmax plus band-limited dipping random layering (no dataset on disk)."""
+    nz, ny = w["nz"], w["ny"]
+    g = torch.Generator().manual_seed(seed)
+    n = nz + ny // 8 + 64
+    r = torch.randn(n, generator=g, dtype=torch.float64)
+    k = torch.arange(-24, 25, dtype=torch.float64)
+    ker = torch.exp(-0.5 * (k / 6.0) ** 2)
+    lay = torch.nn.functional.conv1d(r[None, None], (ker / ker.norm())[None, None], padding=24)[0, 0]
+    z = torch.arange(nz)[:, None]
+    y = torch.arange(ny)[None, :]
+    v = w["vmin"] + (w["vmax"] - w["vmin"]) * (z.double() / max(nz - 1, 1)) + 350.0 * lay[(z + y // 8)]
+    return v.clamp(w["vmin"], w["vmax"]).float().contiguous()
+
+
+def synth_survey(w, n_shots, first_shot=0):
+    """Shots evenly spaced along y at depth z_acq; receivers every rec_stride-th cell."""
+    ny, dx = w["ny"], w["dx"]
+    total = w["survey_shots"]
+    ys = torch.linspace(8, ny - 9, total).round()
+    idx = (first_shot + torch.arange(n_shots)) % total
+    x_s = torch.zeros(n_shots, 1, 2)
+    x_s[:, 0, 0] = w["z_acq"] * dx
+    x_s[:, 0, 1] = ys[idx] * dx
+    yr = (torch.arange(w["n_rec"]) * w["rec_stride"]).clamp(max=ny - 1).float()
+    x_r = torch.zeros(n_shots, w["n_rec"], 2)
+    x_r[:, :, 0] = w["z_acq"] * dx
+    x_r[:, :, 1] = yr[None, :] * dx
+    return x_s, x_r
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], None, [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1]); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port timed on the host cores (cpu_baseline leg and --impl reference)
+# ------------------------------------------------------------------------------------------------
+def cpu_gradient_sample(w, n_steps, v=None):
+    """One fwd+adjoint gradient of ONE shot for n_steps on the C/OpenMP oracle; returns seconds."""
+    from oracle import cpu_ref as O
+    from physicsbasedfwi2_b200.wavelets import ricker
+    if v is None:
+        v = synth_model(w)
+    x_s, x_r = synth_survey(w, 1, first_shot=w["survey_shots"] // 2)
+    src = ricker(w["freq"], n_steps, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1)
+    g = torch.Generator().manual_seed(2)
+    resid = torch.randn(n_steps, 1, w["n_rec"], generator=g)
+    t0 = time.perf_counter()
+    O.acoustic_gradient(v, w["dx"], src, x_s, x_r, w["dt"], grad_rec=resid, order=w["order"],
+                        pml_width=w["pml"], vpmax=w["vmax"], dtype=torch.float32)
+    return time.perf_counter() - t0
+
+
+def cpu_baseline(w, target_s=12.0):
+    from oracle import cpu_ref as O
+    O.build()
+    cells = w["nz"] * w["ny"]
+    v = synth_model(w)
+    probe = min(w["nt"], 40)
+    t = cpu_gradient_sample(w, probe, v)                       # also warms the page cache / threads
+    per_step = t / probe
+    n = int(max(probe, min(w["nt"], target_s / max(per_step, 1e-9), 600)))
+    t = cpu_gradient_sample(w, n, v)
+    val = cells * n * 2 / t / 1e9
+    return {"value": round(val, 4), "unit": "Gcell-updates/s", "cores": O.num_threads(), "kind": "port",
+            "sample": f"1 shot x {n} of {w['nt']} steps, fwd+adjoint, same grid/order/PML, fp32, "
+                      f"oracle/cpu_ref.c with OpenMP ({t:.1f} s)", "seconds": round(t, 2)}
+
+
+def run_reference(args, w):
+    """--impl reference: the reference's CPU path for this workload.  The reference's propagators
+    (deepwave, DENISE) are external and absent, so this is the oracle port (kind 'port')."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import cpu_ref as O
+    O.build()
+    cells = w["nz"] * w["ny"]
+    v = synth_model(w)
+    probe = min(w["nt"], 30)
+    per_step = cpu_gradient_sample(w, probe, v) / probe
+    n = int(max(10, min(w["nt"], 6.0 / max(per_step, 1e-9), 400)))
+    for _ in range(args.warmup):
+        cpu_gradient_sample(w, n, v)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_gradient_sample(w, n, v)
+    t = time.perf_counter() - t0
+    val = cells * n * 2 * args.steps / t / 1e9
+    sample = f"1 shot x {n} of {w['nt']} steps per step, fwd+adjoint, fp32, oracle/cpu_ref.c OpenMP"
+    line = {"impl": "reference", "metric": "FWI gradient Gcell-updates/s (fwd+adjoint)",
+            "value": round(val, 4), "unit": "Gcell-updates/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(1e3 * t / args.steps, 3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": bench_config(w, 1, 1, args.workload),
+            "cpu_baseline": {"value": round(val, 4), "unit": "Gcell-updates/s", "cores": O.num_threads(),
+                             "kind": "port", "sample": sample},
+            "e2e": {"value": round(val, 4), "unit": "Gcell-updates/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def bench_config(w, batch, world, name):
+    return {"workload": f"{name}: 2-D acoustic {w['nz']}x{w['ny']} dx={w['dx']}m order {w['order']} "
+                        f"pml {w['pml']} nt {w['nt']} dt {w['dt']} {w['freq']}Hz Ricker, "
+                        f"{w['n_rec']} receivers/shot, fwd+adjoint gradient (MSE), snapshot every step",
+            "shots_per_gpu_per_step": batch, "shots_per_step": batch * world,
+            "survey_shots": w["survey_shots"], "parallelism": f"shot-parallel x{world}",
+            "l2": "working set per launch exceeds L2 (no flush needed)"}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--shots", type=int, default=0, help="shots per GPU per step (0 = fit HBM, max 6)")
+    ap.add_argument("--nt", type=int, default=0, help="override the number of time steps (tuning only)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    w = dict(WORKLOADS[args.workload])
+    if args.nt:
+        w["nt"] = args.nt
+
+    if args.impl == "reference":
+        run_reference(args, w)
+        return
+
+    import torch.distributed as dist
+    import physicsbasedfwi2_b200 as pkg
+    from physicsbasedfwi2_b200 import _lib
+    from physicsbasedfwi2_b200.distributed import allreduce_gradient
+    from physicsbasedfwi2_b200.scalar import Propagator
+    from physicsbasedfwi2_b200.wavelets import ricker
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    L = pkg.lib()
+    if L.fwi_device_ok(local) != 0:
+        raise RuntimeError(L.fwi_last_error().decode())
+
+    nz, ny, nt = w["nz"], w["ny"], w["nt"]
+    # shots per step: one q snapshot per inner step per shot must fit HBM next to the wavefields
+    P = w["pml"] + w["order"] // 2
+    per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nt + 8)
+    free, _ = torch.cuda.mem_get_info(dev)
+    batch = args.shots or max(1, min(6, int(0.88 * free // per_shot)))
+
+    v_host = synth_model(w).pin_memory()
+    x_s_h, x_r_h = synth_survey(w, batch, first_shot=rank * batch)
+    src_h = ricker(w["freq"], nt, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1).repeat(1, batch, 1).contiguous().pin_memory()
+    gen = torch.Generator().manual_seed(2 + rank)
+    obs_h = torch.randn(nt, batch, w["n_rec"], generator=gen).mul_(1e-3).pin_memory()   # "observed" data
+    x_s_h, x_r_h = x_s_h.pin_memory(), x_r_h.pin_memory()
+    grad_h = torch.empty(nz, ny).pin_memory()
+    loss_h = torch.empty(1).pin_memory()
+
+    def gradient(v_d, src_d, xs_d, xr_d, obs_d):
+        """The call sequence of the reference (models/networks.py:5449,5464,5476,5491)."""
+        v_d = v_d.detach().requires_grad_(True)
+        prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"])
+        rec = prop(src_d, xs_d, xr_d, w["dt"])
+        loss = 0.5 * ((rec - obs_d) ** 2).sum()
+        loss.backward()
+        g, l = allreduce_gradient(v_d.grad, loss)
+        return g, l
+
+    # device-resident inputs for `value`
+    v_d, src_d, xs_d, xr_d, obs_d = (t.to(dev) for t in (v_host, src_h, x_s_h, x_r_h, obs_h))
+
+    def step_resident():
+        return gradient(v_d, src_d, xs_d, xr_d, obs_d)
+
+    def step_e2e():
+        tens = [t.to(dev, non_blocking=True) for t in (v_host, src_h, x_s_h, x_r_h, obs_h)]
+        g, l = gradient(*tens)
+        grad_h.copy_(g, non_blocking=True)
+        loss_h.copy_(l.reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return g, l
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, sampler=None):
+        barrier()
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), clocks, out
+
+    for _ in range(args.warmup):
+        g, l = step_resident()
+    torch.cuda.synchronize()
+    if not bool(torch.isfinite(g).all()) or not math.isfinite(float(l)):
+        raise RuntimeError("non-finite gradient / misfit in the benchmark step")
+
+    _lib.LOOP_TIMES = []
+    n0 = pkg.kernel_launches()
+    ms, clocks, _ = timed(step_resident, args.steps, ClockSampler(local))
+    launches = pkg.kernel_launches() - n0
+    loops = _lib.LOOP_TIMES
+    _lib.LOOP_TIMES = None
+    t_fwd = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag == "acoustic_fwd"]
+    t_adj = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag == "acoustic_adj"]
+    ms_fwd, ms_adj = sum(t_fwd) / len(t_fwd), sum(t_adj) / len(t_adj)      # ms per launch
+
+    cells = nz * ny
+    work = cells * nt * batch * world * 2            # cell-updates per step, whole job
+    value = work * args.steps / (ms * 1e-3) / 1e9
+
+    e2e = None
+    if not args.no_e2e:
+        step_e2e()
+        ms_e, _, _ = timed(step_e2e, args.steps)
+        h2d = sum(t.numel() * t.element_size() for t in (v_host, src_h, x_s_h, x_r_h, obs_h))
+        d2h = grad_h.numel() * 4 + 4
+        e2e = {"value": round(work * args.steps / (ms_e * 1e-3) / 1e9, 3), "unit": "Gcell-updates/s",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": round(ms_e / args.steps, 3)}
+
+    if rank == 0:
+        peak, peak_src = hbm_peak()
+        unit_launch = cells * batch                   # cell-updates one launch performs
+        ach_f = unit_launch * B_FWD / (ms_fwd * 1e-3) / 1e9
+        ach_a = unit_launch * B_ADJ / (ms_adj * 1e-3) / 1e9
+        ach = unit_launch * (B_FWD + B_ADJ) / ((ms_fwd + ms_adj) * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "acoustic_step_kernel (forward MODE 1 + adjoint MODE 2 pair)",
+                "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_cell_update": {"forward": B_FWD, "adjoint": B_ADJ},
+                "forward": {"ms_per_launch": round(ms_fwd, 5), "achieved": round(ach_f, 1), "frac": round(ach_f / peak, 4)},
+                "adjoint": {"ms_per_launch": round(ms_adj, 5), "achieved": round(ach_a, 1), "frac": round(ach_a / peak, 4)},
+                "kernel_share_of_step": round((ms_fwd + ms_adj) * nt * args.steps / ms, 4)}
+        prof = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(prof):
+            try:
+                roof["traffic"] = json.load(open(prof)).get(args.workload)
+            except Exception:
+                pass
+        line = {"metric": "FWI gradient Gcell-updates/s (fwd+adjoint)", "value": round(value, 3),
+                "unit": "Gcell-updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": bench_config(w, batch, world, args.workload), "roofline": roof,
+                "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline(w)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -103,3 +103,27 @@ def check(rc: int, what: str) -> None:
 
 def kernel_launches() -> int:
     return int(lib().fwi_kernel_launches())
+
+
+# ---- optional time-loop timing (bench.py's roofline leg) ---------------------------------------
+# When LOOP_TIMES is a list, every native time loop is bracketed by CUDA events recorded on the
+# stream the kernels are launched on; entries are (tag, start_event, end_event, n_launches).
+LOOP_TIMES = None
+
+
+def time_loop_begin(stream):
+    if LOOP_TIMES is None:
+        return None
+    import torch
+    ev = torch.cuda.Event(enable_timing=True)
+    ev.record(stream)
+    return ev
+
+
+def time_loop_end(stream, ev, tag, n_launches):
+    if ev is None:
+        return
+    import torch
+    end = torch.cuda.Event(enable_timing=True)
+    end.record(stream)
+    LOOP_TIMES.append((tag, ev, end, int(n_launches)))

@@ -98,11 +98,13 @@ class _Plan:
         b = _lib.AcousticBuffers(_ptr(self.w), _ptr(self.sigz), _ptr(self.sigy), _ptr(wave), _ptr(start),
                                  _ptr(icell), _ptr(icol), _ptr(inj_amp), _ptr(smp_cell), _ptr(smp_out),
                                  _ptr(q_write), _ptr(q_read), _ptr(image))
-        stream = torch.cuda.current_stream(self.dev).cuda_stream
+        cur = torch.cuda.current_stream(self.dev)
         with torch.cuda.device(self.dev):
             fn = _lib.lib().fwi_acoustic_backward if adjoint else _lib.lib().fwi_acoustic_forward
-            _lib.check(fn(C.byref(d), C.byref(b), C.c_void_p(stream)),
+            ev = _lib.time_loop_begin(cur)
+            _lib.check(fn(C.byref(d), C.byref(b), C.c_void_p(cur.cuda_stream)),
                        "fwi_acoustic_backward" if adjoint else "fwi_acoustic_forward")
+            _lib.time_loop_end(cur, ev, "acoustic_adj" if adjoint else "acoustic_fwd", nsteps)
         return smp_out
 
 

@@ -1,0 +1,94 @@
+"""The C-ABI library builds for sm_100a, loads without a GPU, and exports every symbol that
+include/fwi_b200.h declares.  No compute call is made here (there is no CPU path to call)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+import physicsbasedfwi2_b200 as pkg
+from physicsbasedfwi2_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "fwi_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(fwi_[a-z0-9_]+)\s*\(", src)))
+
+
+@pytest.fixture(scope="module")
+def so():
+    return ctypes.CDLL(pkg.build())
+
+
+def test_header_declares_entry_points():
+    syms = _declared_symbols()
+    for must in ("fwi_acoustic_get_layout", "fwi_acoustic_forward", "fwi_acoustic_backward",
+                 "fwi_last_error", "fwi_version", "fwi_kernel_launches", "fwi_device_ok"):
+        assert must in syms
+
+
+def test_library_exports_every_declared_symbol(so):
+    for name in _declared_symbols():
+        assert hasattr(so, name), f"{name} declared in include/fwi_b200.h but not exported"
+
+
+def test_version_and_error_string(so):
+    so.fwi_last_error.restype = ctypes.c_char_p
+    assert so.fwi_version() >= 3
+    assert so.fwi_last_error() is not None
+
+
+def test_layout_is_pure_host_code_and_checks_arguments():
+    L = pkg.lib()
+    d = _lib.AcousticDesc(124, 324, 4, 10, 10, 0, 0, 0, 0, 0, 0, 0, 10.0, 10.0, 1e-3)
+    lay = _lib.AcousticLayout()
+    assert L.fwi_acoustic_get_layout(ctypes.byref(d), ctypes.byref(lay)) == 0
+    assert lay.pitch % 32 == 0 and lay.pitch >= 324
+    assert lay.shot_stride == 124 * lay.pitch
+    assert lay.tiles_z * lay.tile_z >= 124 - 4 and lay.tiles_y * lay.tile_y >= 324 - 4
+    assert lay.wave_fields == 6
+    bad = _lib.AcousticDesc(124, 324, 5, 10, 10, 0, 0, 0, 0, 0, 0, 0, 10.0, 10.0, 1e-3)
+    assert L.fwi_acoustic_get_layout(ctypes.byref(bad), ctypes.byref(lay)) == -1
+    assert b"order" in L.fwi_last_error()
+
+
+def test_ctypes_structs_match_header_field_order():
+    src = open(os.path.join(ROOT, "include", "fwi_b200.h")).read()
+    for struct, cls in (("fwi_acoustic_desc", _lib.AcousticDesc), ("fwi_acoustic_layout", _lib.AcousticLayout),
+                        ("fwi_acoustic_buffers", _lib.AcousticBuffers)):
+        body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (struct, struct), src, flags=re.S).group(1)
+        body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+        names = []
+        for decl in body.split(";"):
+            decl = decl.strip()
+            if not decl:
+                continue
+            for part in decl.split(","):
+                names.append(re.findall(r"[A-Za-z_][A-Za-z0-9_]*", part)[-1])
+        assert names == [f[0] for f in cls._fields_], struct
+
+
+def test_product_refuses_cpu_tensors():
+    import torch
+    from physicsbasedfwi2_b200.scalar import Propagator
+    v = torch.full((20, 20), 1500.0)
+    prop = Propagator({"vp": v}, 10.0)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        prop(torch.zeros(10, 1, 1), torch.zeros(1, 1, 2), torch.zeros(1, 3, 2), 1e-3)
+
+
+def test_product_does_not_import_oracle():
+    import subprocess
+    import sys
+    code = ("import sys; import physicsbasedfwi2_b200, physicsbasedfwi2_b200.scalar, "
+            "physicsbasedfwi2_b200.distributed; "
+            "assert not any(m == 'oracle' or m.startswith('oracle.') for m in sys.modules), 'oracle imported'")
+    subprocess.check_call([sys.executable, "-c", code], cwd=ROOT)
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "physicsbasedfwi2_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".h", ".cuh")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in txt and "from oracle" not in txt, f

@@ -63,3 +63,27 @@ def test_shot_grouping_does_not_change_results(cuda_lib, spg):
     errs = _run_case(CASES[0], spg=spg)
     et, ev, es = errs["f32"]
     assert et <= TRACE_TOL and ev <= GRAD_TOL and es <= GRAD_TOL, errs
+
+
+def _golden():
+    import glob
+    import os
+    return sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+
+
+@pytest.mark.parametrize("path", _golden(), ids=lambda p: p.split("/")[-1][:-4])
+def test_cuda_matches_committed_golden_vectors(cuda_lib, path):
+    """Golden vectors from tests/golden/make_golden.py (torch-autograd oracle, fp64)."""
+    import numpy as np
+    from physicsbasedfwi2_b200.scalar import Propagator
+    z = np.load(path)
+    dev = torch.device("cuda:0")
+    dx = z["dx"].tolist()
+    vg = torch.from_numpy(z["v"]).to(dev).requires_grad_(True)
+    sg = torch.from_numpy(z["src"]).to(dev).requires_grad_(True)
+    prop = Propagator({"vp": vg}, dx, pml_width=int(z["pml"]), accuracy=int(z["order"]))
+    rec = prop(sg, torch.from_numpy(z["x_s"]).to(dev), torch.from_numpy(z["x_r"]).to(dev), float(z["dt"]))
+    (rec * torch.from_numpy(z["grad_rec"]).to(dev)).sum().backward()
+    assert K.rel_l2(rec, torch.from_numpy(z["rec"])) <= TRACE_TOL
+    assert K.rel_l2(vg.grad, torch.from_numpy(z["grad_v"])) <= GRAD_TOL
+    assert K.rel_l2(sg.grad, torch.from_numpy(z["grad_src"])) <= GRAD_TOL
