@@ -46,7 +46,7 @@ typedef struct fwi_acoustic_desc {
     int32_t order;            /* spatial accuracy: 2, 4, 6 or 8 */
     int32_t pml_width;        /* cells of PML on each of the four sides (0 = none) */
     int32_t n_shots;          /* shots advanced together by one call */
-    int32_t shots_per_group;  /* shots one CTA walks per launch (w / image amortisation); 0 = auto */
+    int32_t chunk_rows;       /* rows of one interior work unit (tuning; 0 = auto) */
     int32_t nsteps;           /* inner time steps */
     int32_t adjoint;          /* 0: n = 0..nsteps-1;  1: n = nsteps-1..0 (time-reversed driver) */
     int32_t n_inj;            /* injection points per shot (sources fwd / receivers adj) */
@@ -59,12 +59,13 @@ typedef struct fwi_acoustic_desc {
 /* Device memory layout chosen by the library for a descriptor (host POD, output). */
 typedef struct fwi_acoustic_layout {
     int32_t pitch;            /* floats per grid row in device arrays (multiple of 32) */
-    int32_t col0;             /* device column that holds padded column 0 */
+    int32_t col0;             /* device column that holds padded column 0 (first interior column is
+                                 128-byte aligned) */
     int64_t shot_stride;      /* floats per shot per field = nzp * pitch */
-    int32_t tile_z, tile_y;   /* CTA tile (cells) */
-    int32_t tiles_z, tiles_y; /* tiles over the computational region */
-    int32_t n_groups;         /* shot groups = image partial buffers */
+    int32_t n_images;         /* image partial buffers (one per shot: single-owner accumulation) */
     int32_t wave_fields;      /* number of [n_shots][nzp][pitch] fields in the workspace */
+    int32_t chunk_rows;       /* rows per interior work unit actually used */
+    int32_t units_per_shot;   /* warp work units per shot per step */
 } fwi_acoustic_layout;
 
 /* Buffers of one propagation (host struct of device pointers). */
@@ -73,15 +74,16 @@ typedef struct fwi_acoustic_buffers {
     const float *sigz;        /* [nzp]          PML profile along z */
     const float *sigy;        /* [pitch]        PML profile along y, device columns */
     float *wave;              /* [wave_fields][n_shots][nzp][pitch], zero on entry: u, u-, pz, pz+, py, py+ */
-    const int32_t *inj_tile_start; /* [n_shots][tiles_z*tiles_y + 1] offsets into the two lists below */
-    const int32_t *inj_cell;  /* [n_shots*n_inj] device cell (z*pitch + col), grouped by (shot, tile) */
+    const int32_t *inj_row_start; /* [n_shots][nzp + 1] absolute offsets into the two lists below:
+                                 entries of shot s in rows [z0, z1) are [start[s][z0], start[s][z1]) */
+    const int32_t *inj_cell;  /* [n_shots*n_inj] device cell (z*pitch + col), sorted by (shot, cell), stable */
     const int32_t *inj_col;   /* [n_shots*n_inj] column of inj_amp each entry reads */
     const float *inj_amp;     /* [nsteps][n_shots][n_inj] */
     const int32_t *smp_cell;  /* [n_shots][n_smp] device cell */
     float *smp_out;           /* [nsteps][n_shots][n_smp] */
     float *q_write;           /* [nsteps][n_shots][nzp][pitch] or NULL: snapshot of q per step */
     const float *q_read;      /* same layout or NULL: snapshots consumed by the imaging sum */
-    float *image;             /* [n_groups][nzp][pitch] or NULL: image += field * q_read */
+    float *image;             /* [n_images][nzp][pitch] or NULL: image[s] += field * q_read */
 } fwi_acoustic_buffers;
 
 /* Fills `out` for `desc`.  Replaces nothing in the reference (layout is private to deepwave

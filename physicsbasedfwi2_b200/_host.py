@@ -106,26 +106,24 @@ def replicate_pad_adjoint(gpad: torch.Tensor, pad: int) -> torch.Tensor:
     return g[:, pad:-pad].contiguous()
 
 
-def tile_lists(cells_dev: torch.Tensor, z: torch.Tensor, ycol: torch.Tensor, halo: int,
-               col_first: int, tile_z: int, tile_y: int, tiles_y: int, n_tiles: int):
-    """Groups the per-shot point list by the CTA tile that owns each point.
+def injection_lists(cells_dev: torch.Tensor, nzp: int, pitch: int):
+    """Sorts the per-shot point list by device cell so a work unit finds its points by row range.
 
-    cells_dev, z, ycol: [S, n] device cell / row / device column.  Returns
-    (start [S, n_tiles+1] int32 absolute offsets, cell [S*n] int32, col [S*n] int32) with the
-    entries of one (shot, tile) contiguous and in their original order (stable sort), so
-    duplicate points are applied in a fixed order.
+    cells_dev: [S, n] device cell (z*pitch + col).  Returns (row_start [S, nzp+1] int32 absolute
+    offsets into the flat lists, cell [S*n] int32 sorted by (shot, cell), col [S*n] int32 = index
+    of the entry within its shot before sorting).  The sort is stable, so duplicate points stay
+    adjacent and in their original order: the kernel applies them in that fixed order.
     """
     S, n = cells_dev.shape
     dev = cells_dev.device
     if n == 0:
-        z32 = torch.zeros(S * (n_tiles + 1), dtype=torch.int32, device=dev)
-        e = torch.zeros(1, dtype=torch.int32, device=dev)
-        return z32, e, e
-    tile = ((z - halo) // tile_z) * tiles_y + (ycol - col_first) // tile_y
-    key = (torch.arange(S, device=dev)[:, None] * n_tiles + tile).reshape(-1)
+        return (torch.zeros(S * (nzp + 1), dtype=torch.int32, device=dev),
+                torch.zeros(1, dtype=torch.int32, device=dev), torch.zeros(1, dtype=torch.int32, device=dev))
+    per_shot = nzp * pitch
+    key = (torch.arange(S, device=dev)[:, None] * per_shot + cells_dev).reshape(-1)
     skey, order = torch.sort(key, stable=True)
-    bounds = (torch.arange(S, device=dev)[:, None] * n_tiles
-              + torch.arange(n_tiles + 1, device=dev)[None, :]).reshape(-1)
+    bounds = (torch.arange(S, device=dev)[:, None] * per_shot
+              + torch.arange(nzp + 1, device=dev)[None, :] * pitch).reshape(-1)
     start = torch.searchsorted(skey, bounds, right=False).to(torch.int32)
     cell = cells_dev.reshape(-1)[order].to(torch.int32).contiguous()
     col = (order % n).to(torch.int32).contiguous()

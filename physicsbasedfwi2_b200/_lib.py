@@ -20,7 +20,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
 
 class AcousticDesc(C.Structure):
     _fields_ = [("nzp", C.c_int32), ("nyp", C.c_int32), ("order", C.c_int32),
-                ("pml_width", C.c_int32), ("n_shots", C.c_int32), ("shots_per_group", C.c_int32),
+                ("pml_width", C.c_int32), ("n_shots", C.c_int32), ("chunk_rows", C.c_int32),
                 ("nsteps", C.c_int32), ("adjoint", C.c_int32), ("n_inj", C.c_int32),
                 ("inj_scale_a", C.c_int32), ("n_smp", C.c_int32), ("smp_div_a", C.c_int32),
                 ("dz", C.c_double), ("dy", C.c_double), ("dt", C.c_double)]
@@ -28,13 +28,13 @@ class AcousticDesc(C.Structure):
 
 class AcousticLayout(C.Structure):
     _fields_ = [("pitch", C.c_int32), ("col0", C.c_int32), ("shot_stride", C.c_int64),
-                ("tile_z", C.c_int32), ("tile_y", C.c_int32), ("tiles_z", C.c_int32),
-                ("tiles_y", C.c_int32), ("n_groups", C.c_int32), ("wave_fields", C.c_int32)]
+                ("n_images", C.c_int32), ("wave_fields", C.c_int32), ("chunk_rows", C.c_int32),
+                ("units_per_shot", C.c_int32)]
 
 
 class AcousticBuffers(C.Structure):
     _fields_ = [("w", C.c_void_p), ("sigz", C.c_void_p), ("sigy", C.c_void_p),
-                ("wave", C.c_void_p), ("inj_tile_start", C.c_void_p), ("inj_cell", C.c_void_p),
+                ("wave", C.c_void_p), ("inj_row_start", C.c_void_p), ("inj_cell", C.c_void_p),
                 ("inj_col", C.c_void_p), ("inj_amp", C.c_void_p), ("smp_cell", C.c_void_p),
                 ("smp_out", C.c_void_p), ("q_write", C.c_void_p), ("q_read", C.c_void_p),
                 ("image", C.c_void_p)]

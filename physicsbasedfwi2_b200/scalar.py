@@ -30,7 +30,7 @@ class _Plan:
     """Everything about one call that does not depend on the direction of time."""
 
     def __init__(self, v: torch.Tensor, dx, dt: float, order: int, pml_width: int,
-                 vpmax: Optional[float], n_shots: int, shots_per_group: int = 0):
+                 vpmax: Optional[float], n_shots: int, chunk_rows: int = 0):
         if v.dim() != 2:
             raise RuntimeError(f"model['vp'] must be 2-D [nz, ny], got shape {tuple(v.shape)}")
         if not v.is_cuda:
@@ -48,7 +48,7 @@ class _Plan:
         self.vmax = float(vpmax) if vpmax is not None else float(v.detach().abs().max())
         self.ratio, self.dti = H.inner_step(float(dt), self.dz, self.dy, self.vmax)
         self.S = n_shots
-        self.spg = shots_per_group
+        self.chunk_rows = chunk_rows
 
         lay = _lib.AcousticLayout()
         d = self.desc(nsteps=0, adjoint=0, n_inj=0, n_smp=0)
@@ -56,7 +56,6 @@ class _Plan:
         self.lay = lay
         self.pitch, self.col0 = int(lay.pitch), int(lay.col0)
         self.stride = int(lay.shot_stride)
-        self.n_tiles = int(lay.tiles_z) * int(lay.tiles_y)
 
         vp = F.pad(v.detach()[None, None], (self.P,) * 4, mode="replicate")[0, 0]
         self.v_pad = vp
@@ -69,7 +68,7 @@ class _Plan:
         self.sigz, self.sigy = sz.to(self.dev), sy.to(self.dev)
 
     def desc(self, nsteps, adjoint, n_inj, n_smp) -> _lib.AcousticDesc:
-        return _lib.AcousticDesc(self.nzp, self.nyp, self.order, self.pw, self.S, self.spg, nsteps,
+        return _lib.AcousticDesc(self.nzp, self.nyp, self.order, self.pw, self.S, self.chunk_rows, nsteps,
                                  adjoint, n_inj, 1 if adjoint else 0, n_smp, 1 if adjoint else 0,
                                  self.dz, self.dy, self.dti)
 
@@ -82,10 +81,8 @@ class _Plan:
         cell = z * self.pitch + ycol
         return cell, z, ycol, bad
 
-    def lists(self, cell, z, ycol):
-        L = self.lay
-        return H.tile_lists(cell, z, ycol, self.h, self.col0 + self.h, int(L.tile_z), int(L.tile_y),
-                            int(L.tiles_y), self.n_tiles)
+    def lists(self, cell):
+        return H.injection_lists(cell, self.nzp, self.pitch)
 
     def run(self, *, nsteps, adjoint, inj, inj_amp, smp_cell, n_smp, q_write=None, q_read=None,
             image=None) -> torch.Tensor:
@@ -111,7 +108,7 @@ class _Plan:
 class _ScalarFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, v, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, loc_mode,
-                shots_per_group):
+                chunk_rows):
         if source_amplitudes.dim() != 3:
             raise RuntimeError("source_amplitudes must be [nt, n_shots, n_sources_per_shot]")
         nt, S, Ns = source_amplitudes.shape
@@ -120,7 +117,7 @@ class _ScalarFunction(torch.autograd.Function):
         if x_r.dim() != 3 or x_r.shape[0] != S or x_r.shape[2] != 2:
             raise RuntimeError(f"receiver_locations must be [{S}, n_receivers, 2], got {tuple(x_r.shape)}")
         R = int(x_r.shape[1])
-        plan = _Plan(v, dx, dt, order, pml_width, vpmax, S, shots_per_group)
+        plan = _Plan(v, dx, dt, order, pml_width, vpmax, S, chunk_rows)
         dev = plan.dev
         s_cell, s_z, s_y, bad_s = plan.points(x_s, "source", loc_mode)
         r_cell, r_z, r_y, bad_r = plan.points(x_r, "receiver", loc_mode)
@@ -134,7 +131,7 @@ class _ScalarFunction(torch.autograd.Function):
         if need_v:
             q = torch.empty(nti * S * plan.stride, dtype=torch.float32, device=dev)
         r32 = r_cell.to(torch.int32).contiguous()
-        rec = plan.run(nsteps=nti, adjoint=0, inj=plan.lists(s_cell, s_z, s_y), inj_amp=amp,
+        rec = plan.run(nsteps=nti, adjoint=0, inj=plan.lists(s_cell), inj_amp=amp,
                        smp_cell=r32, n_smp=R, q_write=q)
         out = rec[::plan.ratio].contiguous() if plan.ratio > 1 else rec
         ctx.plan = plan
@@ -160,13 +157,13 @@ class _ScalarFunction(torch.autograd.Function):
             g_in = g.contiguous()
         image = None
         if need_v:
-            image = torch.zeros(int(plan.lay.n_groups) * plan.stride, dtype=torch.float32, device=dev)
-        gs = plan.run(nsteps=nti, adjoint=1, inj=plan.lists(r_cell, r_z, r_y), inj_amp=g_in,
+            image = torch.zeros(int(plan.lay.n_images) * plan.stride, dtype=torch.float32, device=dev)
+        gs = plan.run(nsteps=nti, adjoint=1, inj=plan.lists(r_cell), inj_amp=g_in,
                       smp_cell=s_cell.to(torch.int32).contiguous(), n_smp=Ns,
                       q_read=ctx.q if need_v else None, image=image)
         grad_v = grad_s = None
         if need_v:
-            G = image.view(int(plan.lay.n_groups), plan.nzp, plan.pitch).sum(0)
+            G = image.view(int(plan.lay.n_images), plan.nzp, plan.pitch).sum(0)
             G = G[:, plan.col0:plan.col0 + plan.nyp].contiguous()
             # the source term of dJ/dw: mu/a sampled at the source cells times the wavelet
             flat = G.view(-1)
@@ -188,11 +185,11 @@ class Propagator(torch.nn.Module):
     key ``'vp'`` holding a float32 CUDA tensor [nz, ny]; ``dx`` a float or (dz, dy).
     ``pml_width`` (int, default 10), ``survey_pad`` (None or cells) and ``vpmax`` as in deepwave.
     Extensions: ``accuracy`` (2/4/6/8, default 4), ``loc_mode`` ('trunc' | 'round'),
-    ``shots_per_group`` (kernel tuning, 0 = auto).
+    ``chunk_rows`` (rows per interior work unit, kernel tuning, 0 = auto).
     """
 
     def __init__(self, model: dict, dx, pml_width=None, survey_pad=None, vpmax=None, *,
-                 accuracy: int = 4, loc_mode: str = "trunc", shots_per_group: int = 0):
+                 accuracy: int = 4, loc_mode: str = "trunc", chunk_rows: int = 0):
         super().__init__()
         if not isinstance(model, dict) or "vp" not in model:
             raise RuntimeError("model must be a dict with key 'vp'")
@@ -218,7 +215,7 @@ class Propagator(torch.nn.Module):
         self.vpmax = vpmax
         self.accuracy = accuracy
         self.loc_mode = loc_mode
-        self.shots_per_group = shots_per_group
+        self.chunk_rows = chunk_rows
 
     def forward(self, source_amplitudes: torch.Tensor, source_locations: torch.Tensor,
                 receiver_locations: torch.Tensor, dt: float) -> torch.Tensor:
@@ -227,7 +224,7 @@ class Propagator(torch.nn.Module):
         if self.survey_pad is not None:
             v, x_s, x_r = _crop_to_survey(v, self.dx, x_s, x_r, self.survey_pad)
         return _ScalarFunction.apply(v, source_amplitudes, x_s, x_r, float(dt), self.dx, self.accuracy,
-                                     self.pml_width, self.vpmax, self.loc_mode, self.shots_per_group)
+                                     self.pml_width, self.vpmax, self.loc_mode, self.chunk_rows)
 
 
 def _crop_to_survey(v, dx, x_s, x_r, survey_pad):

@@ -37,7 +37,7 @@ def test_library_exports_every_declared_symbol(so):
 
 def test_version_and_error_string(so):
     so.fwi_last_error.restype = ctypes.c_char_p
-    assert so.fwi_version() >= 3
+    assert so.fwi_version() >= 4
     assert so.fwi_last_error() is not None
 
 
@@ -46,10 +46,14 @@ def test_layout_is_pure_host_code_and_checks_arguments():
     d = _lib.AcousticDesc(124, 324, 4, 10, 10, 0, 0, 0, 0, 0, 0, 0, 10.0, 10.0, 1e-3)
     lay = _lib.AcousticLayout()
     assert L.fwi_acoustic_get_layout(ctypes.byref(d), ctypes.byref(lay)) == 0
-    assert lay.pitch % 32 == 0 and lay.pitch >= 324
+    assert lay.pitch % 32 == 0 and lay.pitch >= lay.col0 + 324
     assert lay.shot_stride == 124 * lay.pitch
-    assert lay.tiles_z * lay.tile_z >= 124 - 4 and lay.tiles_y * lay.tile_y >= 324 - 4
-    assert lay.wave_fields == 6
+    assert (lay.col0 + 2 * 2 + 10) % 32 == 0          # first interior column is 128-byte aligned
+    assert lay.n_images == 10 and lay.wave_fields == 6
+    assert lay.chunk_rows >= 2 and lay.units_per_shot >= 1
+    nopml = _lib.AcousticDesc(104, 304, 8, 0, 3, 0, 0, 0, 0, 0, 0, 0, 10.0, 10.0, 1e-3)
+    assert L.fwi_acoustic_get_layout(ctypes.byref(nopml), ctypes.byref(lay)) == 0
+    assert lay.wave_fields == 2 and (lay.col0 + 4) % 32 == 0
     bad = _lib.AcousticDesc(124, 324, 5, 10, 10, 0, 0, 0, 0, 0, 0, 0, 10.0, 10.0, 1e-3)
     assert L.fwi_acoustic_get_layout(ctypes.byref(bad), ctypes.byref(lay)) == -1
     assert b"order" in L.fwi_last_error()

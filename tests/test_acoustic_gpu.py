@@ -24,7 +24,7 @@ CASES = [
 ]
 
 
-def _run_case(c, spg=0):
+def _run_case(c, chunk_rows=0):
     from oracle import cpu_ref as O
     from physicsbasedfwi2_b200.scalar import Propagator
     v = K.layered_model(c["nz"], c["ny"], seed=1)
@@ -37,7 +37,7 @@ def _run_case(c, spg=0):
     dev = torch.device("cuda:0")
     vg = v.to(dev).requires_grad_(True)
     sg = src.to(dev).requires_grad_(True)
-    prop = Propagator({"vp": vg}, c["dx"], pml_width=c["pml"], accuracy=c["order"], shots_per_group=spg)
+    prop = Propagator({"vp": vg}, c["dx"], pml_width=c["pml"], accuracy=c["order"], chunk_rows=chunk_rows)
     rec = prop(sg, x_s.to(dev), x_r.to(dev), c["dt"])
     (rec * grad_rec.to(dev)).sum().backward()
 
@@ -49,20 +49,47 @@ def _run_case(c, spg=0):
     return out
 
 
+# fp32 round-off of the leapfrog recurrence itself (the fp32 and fp64 builds of the oracle differ
+# by this much): sanity bound for the comparison against the fp64 oracle
+F64_TRACE_TOL = 5e-5
+F64_GRAD_TOL = 2e-4
+
+
 @pytest.mark.parametrize("idx", range(len(CASES)))
 def test_traces_and_gradients_match_oracle(cuda_lib, idx):
     errs = _run_case(CASES[idx])
-    for name, (et, ev, es) in errs.items():
-        assert et <= TRACE_TOL, f"{name}: trace rel-L2 {et:.3e} > {TRACE_TOL}"
-        assert ev <= GRAD_TOL, f"{name}: grad_v rel-L2 {ev:.3e} > {GRAD_TOL}"
-        assert es <= GRAD_TOL, f"{name}: grad_src rel-L2 {es:.3e} > {GRAD_TOL}"
+    et, ev, es = errs["f32"]                   # same precision as the product: north_star tolerances
+    assert et <= TRACE_TOL, f"trace rel-L2 {et:.3e} > {TRACE_TOL}"
+    assert ev <= GRAD_TOL, f"grad_v rel-L2 {ev:.3e} > {GRAD_TOL}"
+    assert es <= GRAD_TOL, f"grad_src rel-L2 {es:.3e} > {GRAD_TOL}"
+    et, ev, es = errs["f64"]
+    assert et <= F64_TRACE_TOL and ev <= F64_GRAD_TOL and es <= F64_GRAD_TOL, errs
 
 
-@pytest.mark.parametrize("spg", [1, 2, 3])
-def test_shot_grouping_does_not_change_results(cuda_lib, spg):
-    errs = _run_case(CASES[0], spg=spg)
+@pytest.mark.parametrize("rows", [2, 6, 24, 1000])
+def test_unit_chunking_does_not_change_results(cuda_lib, rows):
+    errs = _run_case(CASES[0], chunk_rows=rows)
     et, ev, es = errs["f32"]
     assert et <= TRACE_TOL and ev <= GRAD_TOL and es <= GRAD_TOL, errs
+
+
+def test_duplicate_sources_and_receivers(cuda_lib):
+    """Two sources in one cell and repeated receivers: fixed-order accumulation."""
+    from oracle import cpu_ref as O
+    from physicsbasedfwi2_b200.scalar import Propagator
+    nz, ny, dx, nt, dt = 30, 70, 10.0, 80, 1e-3
+    v = K.layered_model(nz, ny, seed=5)
+    x_s = torch.tensor([[[50.0, 200.0], [50.0, 200.0], [120.0, 400.0]]])
+    x_r = torch.tensor([[[0.0, 100.0], [0.0, 100.0], [50.0, 200.0], [290.0, 690.0], [0.0, 0.0]]])
+    src = torch.randn(nt, 1, 3, generator=torch.Generator().manual_seed(1))
+    g = torch.randn(nt, 1, 5, generator=torch.Generator().manual_seed(2))
+    dev = torch.device("cuda:0")
+    vg = v.to(dev).requires_grad_(True)
+    sg = src.to(dev).requires_grad_(True)
+    rec = Propagator({"vp": vg}, dx)(sg, x_s.to(dev), x_r.to(dev), dt)
+    (rec * g.to(dev)).sum().backward()
+    r, gv, gs = O.acoustic_gradient(v, dx, src, x_s, x_r, dt, grad_rec=g, dtype=torch.float32)
+    assert K.rel_l2(rec, r) <= TRACE_TOL and K.rel_l2(vg.grad, gv) <= GRAD_TOL and K.rel_l2(sg.grad, gs) <= GRAD_TOL
 
 
 def _golden():

@@ -85,26 +85,26 @@ def test_replicate_pad_adjoint_is_the_transpose(pad):
     assert torch.allclose(H.replicate_pad_adjoint(r, pad), O.fold_replicate_pad(r, pad))
 
 
-def test_tile_lists_group_points_by_tile_in_stable_order():
-    S, n, halo, col_first, tz, ty, tiles_y, tiles_z = 2, 7, 2, 32, 16, 128, 3, 4
-    pitch = 448
+def test_injection_lists_sorted_by_cell_with_row_offsets():
+    S, n, nzp, pitch = 3, 9, 20, 64
     g = torch.Generator().manual_seed(0)
-    z = torch.randint(halo, halo + tz * tiles_z, (S, n), generator=g)
-    y = torch.randint(col_first, col_first + ty * tiles_y, (S, n), generator=g)
-    z[0, 3], y[0, 3] = z[0, 1], y[0, 1]                  # a duplicate point keeps its order
+    z = torch.randint(0, nzp, (S, n), generator=g)
+    y = torch.randint(0, pitch, (S, n), generator=g)
+    z[0, 5], y[0, 5] = z[0, 2], y[0, 2]                  # a duplicate point keeps its order
     cell = z * pitch + y
-    start, c, col = H.tile_lists(cell, z, y, halo, col_first, tz, ty, tiles_y, tiles_y * tiles_z)
-    n_tiles = tiles_y * tiles_z
-    start = start.reshape(S, n_tiles + 1)
+    start, c, col = H.injection_lists(cell, nzp, pitch)
+    start = start.reshape(S, nzp + 1)
     assert int(start[0, 0]) == 0 and int(start[-1, -1]) == S * n
     for s in range(S):
-        assert int(start[s, 0]) == s * n
-        for t in range(n_tiles):
-            for e in range(int(start[s, t]), int(start[s, t + 1])):
-                zz, yy = int(c[e]) // pitch, int(c[e]) % pitch
-                assert (zz - halo) // tz * tiles_y + (yy - col_first) // ty == t
-                assert int(cell[s, int(col[e])]) == int(c[e])
-            cols = [int(col[e]) for e in range(int(start[s, t]), int(start[s, t + 1]))]
-            assert cols == sorted(cols)
-    start0, c0, col0 = H.tile_lists(cell[:, :0], z[:, :0], y[:, :0], halo, col_first, tz, ty, tiles_y, n_tiles)
-    assert int(start0.abs().sum()) == 0
+        assert int(start[s, 0]) == s * n and int(start[s, nzp]) == (s + 1) * n
+        seg = c[s * n:(s + 1) * n].tolist()
+        assert seg == sorted(seg)
+        for e in range(s * n, (s + 1) * n):
+            assert int(cell[s, int(col[e])]) == int(c[e])
+        for row in range(nzp):
+            for e in range(int(start[s, row]), int(start[s, row + 1])):
+                assert int(c[e]) // pitch == row
+    dup = [e for e in range(n) if int(c[e]) == int(cell[0, 2])]
+    assert [int(col[e]) for e in dup] == [2, 5]
+    start0, c0, col0 = H.injection_lists(cell[:, :0], nzp, pitch)
+    assert int(start0.abs().sum()) == 0 and start0.numel() == S * (nzp + 1)
