@@ -1,6 +1,6 @@
 # dev aid: prints CUDA-vs-oracle errors per case (run under gpurun)
 import sys, os, time
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from tests.test_acoustic_gpu import CASES, _run_case
 for i, c in enumerate(CASES):

@@ -1,0 +1,99 @@
+#!/usr/bin/env python
+"""Turns the ncu artefacts a gpurun call brought back (gpurun_out/) into the text summaries kept
+under profiles/.   python scripts/ncu_summary.py <tag>   e.g. r01a"""
+import collections
+import csv
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "gpurun_out")
+PROF = os.path.join(ROOT, "profiles")
+
+KEEP = [
+    "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+    "dram__bytes_read.sum.per_second", "dram__bytes_write.sum.per_second",
+    "dram__throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct",
+    "l1tex__t_bytes.sum", "l1tex__t_sector_hit_rate.pct", "launch__grid_size", "launch__block_size",
+    "launch__registers_per_thread", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
+    "launch__waves_per_multiprocessor", "launch__shared_mem_per_block_static", "launch__shared_mem_per_block_dynamic",
+    "sm__warps_active.avg.pct_of_peak_sustained_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+    "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__cycles_active.avg",
+    "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+    "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "smsp__inst_executed.sum",
+]
+
+
+def launches(tag):
+    src = os.path.join(OUT, "launches.csv")
+    if not os.path.exists(src):
+        return
+    rows = [r for r in csv.reader(open(src)) if len(r) > 10]
+    hdr = rows[0]
+    ki, vi = hdr.index("Kernel Name"), hdr.index("Metric Value")
+    agg = collections.OrderedDict()
+    for r in rows[1:]:
+        try:
+            v = float(r[vi].replace(",", ""))
+        except ValueError:
+            continue
+        a = agg.setdefault(r[ki], [0, 0.0])
+        a[0] += 1
+        a[1] += v
+    tot = sum(a[1] for a in agg.values())
+    with open(os.path.join(PROF, f"{tag}_launches.txt"), "w") as f:
+        f.write("# ncu --metrics gpu__time_duration.sum --clock-control none (per-launch, cold-cache, serialised)\n")
+        f.write("# command: python bench.py --nt 40 --steps 1 --warmup 3 --no-cpu --no-e2e (first 400 launches)\n")
+        f.write(f"# total {tot / 1e3:.1f} us over {sum(a[0] for a in agg.values())} launches\n")
+        f.write("# count   total_us   share  avg_us  kernel\n")
+        for k, a in sorted(agg.items(), key=lambda x: -x[1][1]):
+            f.write(f"{a[0]:6d} {a[1] / 1e3:10.1f} {100 * a[1] / tot:6.1f}% {a[1] / a[0] / 1e3:7.2f}  {k[:110]}\n")
+
+
+def full(tag, name):
+    rep = os.path.join(OUT, name + ".ncu-rep")
+    if not os.path.exists(rep):
+        return None
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    hdr, units, vals = rows[0], rows[1], rows[2]
+    d = {h: (v, u) for h, u, v in zip(hdr, units, vals)}
+    with open(os.path.join(PROF, f"{tag}_{name}.txt"), "w") as f:
+        f.write(f"# ncu --set full --clock-control none --import-source on, one launch; {d.get('Kernel Name', ('', ''))[0]}\n")
+        for k in KEEP:
+            if k in d:
+                f.write(f"{k:70s} {d[k][0]:>16s} {d[k][1]}\n")
+        f.write("# warp stall reasons (pct of warp-active cycles) > 3%\n")
+        for h, (v, u) in d.items():
+            if "issue_stalled" in h and h.endswith("_per_warp_active.pct"):
+                try:
+                    if float(v.replace(",", "")) > 3:
+                        f.write(f"{h:90s} {v:>10s}\n")
+                except ValueError:
+                    pass
+
+    def num(k):
+        v, u = d[k]
+        x = float(v.replace(",", ""))
+        mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
+        return x * mult
+    return num("dram__bytes_read.sum") + num("dram__bytes_write.sum")
+
+
+if __name__ == "__main__":
+    tag = sys.argv[1]
+    os.makedirs(PROF, exist_ok=True)
+    launches(tag)
+    t = {n: full(tag, n) for n in ("fwd_full", "adj_full")}
+    print(t)
+    for n in ("bench.log", "pytest_gpu.log", "smoke.log"):
+        p = os.path.join(OUT, n)
+        if os.path.exists(p):
+            open(os.path.join(PROF, f"{tag}_{n}.txt"), "w").write(open(p).read())
+    if t["fwd_full"] and t["adj_full"]:
+        # dram bytes per launch of the forward + adjoint pair (what roofline.achieved is quoted over)
+        json.dump({"c2": {"forward_bytes_per_launch": t["fwd_full"], "adjoint_bytes_per_launch": t["adj_full"],
+                          "pair_bytes_per_launch": t["fwd_full"] + t["adj_full"], "source": f"profiles/{tag}_*_full.txt"}},
+                  open(os.path.join(PROF, "traffic.json"), "w"), indent=1)
