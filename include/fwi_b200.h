@@ -46,7 +46,7 @@ typedef struct fwi_acoustic_desc {
     int32_t order;            /* spatial accuracy: 2, 4, 6 or 8 */
     int32_t pml_width;        /* cells of PML on each of the four sides (0 = none) */
     int32_t n_shots;          /* shots advanced together by one call */
-    int32_t chunk_rows;       /* rows of one interior work unit (tuning; 0 = auto) */
+    int32_t chunk_rows;       /* cap on the rows of one work segment (tuning / tests; 0 = none) */
     int32_t nsteps;           /* inner time steps */
     int32_t adjoint;          /* 0: n = 0..nsteps-1;  1: n = nsteps-1..0 (time-reversed driver) */
     int32_t n_inj;            /* injection points per shot (sources fwd / receivers adj) */
@@ -64,8 +64,9 @@ typedef struct fwi_acoustic_layout {
     int64_t shot_stride;      /* floats per shot per field = nzp * pitch */
     int32_t n_images;         /* image partial buffers (one per shot: single-owner accumulation) */
     int32_t wave_fields;      /* number of [n_shots][nzp][pitch] fields in the workspace */
-    int32_t chunk_rows;       /* rows per interior work unit actually used */
-    int32_t units_per_shot;   /* warp work units per shot per step */
+    int32_t chunk_rows;       /* cap on segment rows actually used (0 = none) */
+    int32_t units_per_shot;   /* strip columns of work per shot per step */
+    int64_t unit_table_bytes; /* size of the work-table workspace fwi_acoustic_run needs */
 } fwi_acoustic_layout;
 
 /* Buffers of one propagation (host struct of device pointers). */
@@ -84,11 +85,19 @@ typedef struct fwi_acoustic_buffers {
     float *q_write;           /* [nsteps][n_shots][nzp][pitch] or NULL: snapshot of q per step */
     const float *q_read;      /* same layout or NULL: snapshots consumed by the imaging sum */
     float *image;             /* [n_images][nzp][pitch] or NULL: image[s] += field * q_read */
+    void *unit_table;         /* [unit_table_bytes] scratch: the library writes its work table here */
 } fwi_acoustic_buffers;
 
 /* Fills `out` for `desc`.  Replaces nothing in the reference (layout is private to deepwave
  * there); needed so a host can size and fill the arrays above. */
 int fwi_acoustic_get_layout(const fwi_acoustic_desc *desc, fwi_acoustic_layout *out);
+
+/* Host-only: cuts the work of one launch into `n_units` cost-balanced warp units exactly as
+ * fwi_acoustic_run does for a device with that many resident warps, checks that the segments tile
+ * the computational region, and reports the balance (estimated cost of the heaviest unit vs the
+ * mean).  Any output pointer may be NULL. */
+int fwi_acoustic_plan_stats(const fwi_acoustic_desc *desc, int n_units, int64_t *n_segments,
+                            int32_t *n_units_used, double *max_cost, double *mean_cost);
 
 /* Runs desc->nsteps steps.  Per step n:  smp_out[n] = field[smp_cell] (/a);  [image += field *
  * q_read[n]];  advance (writing q_write[n]);  field+[inj_cell] += coef * inj_amp[n].

@@ -29,7 +29,7 @@ class AcousticDesc(C.Structure):
 class AcousticLayout(C.Structure):
     _fields_ = [("pitch", C.c_int32), ("col0", C.c_int32), ("shot_stride", C.c_int64),
                 ("n_images", C.c_int32), ("wave_fields", C.c_int32), ("chunk_rows", C.c_int32),
-                ("units_per_shot", C.c_int32)]
+                ("units_per_shot", C.c_int32), ("unit_table_bytes", C.c_int64)]
 
 
 class AcousticBuffers(C.Structure):
@@ -37,7 +37,7 @@ class AcousticBuffers(C.Structure):
                 ("wave", C.c_void_p), ("inj_row_start", C.c_void_p), ("inj_cell", C.c_void_p),
                 ("inj_col", C.c_void_p), ("inj_amp", C.c_void_p), ("smp_cell", C.c_void_p),
                 ("smp_out", C.c_void_p), ("q_write", C.c_void_p), ("q_read", C.c_void_p),
-                ("image", C.c_void_p)]
+                ("image", C.c_void_p), ("unit_table", C.c_void_p)]
 
 
 def sources():

@@ -3,47 +3,62 @@
 // Replaces the time loop of deepwave.scalar.Propagator.forward / backward as called at
 // reference models/networks.py:5464 (forward) and :5491 (adjoint).  Not a port: deepwave's
 // kernels are one-thread-per-cell global-memory stencils.  Here the grid of one shot is cut
-// into WORK UNITS, each owned by ONE WARP that marches down z through a strip of columns:
+// into column strips and every WARP owns a contiguous run of strip rows (its "segments"), which
+// it marches down in z as its own software pipeline:
 //
-//   * the warp keeps the 2H+RPT rows of u it needs for the z-stencil in REGISTERS (a sliding
-//     window), so every u value is loaded from memory once per strip (no z-halo re-reads inside
-//     a unit) with 16-byte coalesced loads;
-//   * the y-neighbours of the centre row are exchanged through a per-warp shared-memory row
-//     (no block-level barrier anywhere: warps never wait for one another);
-//   * the operands of the next RPT rows (u, u-, v^2dt^2, snapshot) are prefetched into registers
-//     while the current rows are computed, which keeps enough bytes in flight per SM to cover
-//     HBM latency;
+//   * rows are brought from HBM/L2 into a per-warp shared-memory ring by TMA bulk copies
+//     (cp.async.bulk, completion on an mbarrier) issued DO rows ahead of the row being computed,
+//     so the bytes in flight per SM are set by the ring depth, not by registers or occupancy;
+//   * the 2H+1 rows of u needed by the z-stencil are kept in REGISTERS (a sliding window), the
+//     y-neighbours of the centre row are read from the ring (the row lands with a 4-column halo),
+//     so every operand crosses HBM once per step;
+//   * warps never wait for one another: no block-level barrier anywhere, each warp waits only on
+//     the mbarriers of its own ring;
 //   * the step fuses receiver sampling + stencil/PML update + source injection + snapshot write
-//     (forward) or snapshot read + imaging accumulation (adjoint): each field crosses HBM once
-//     per step.
+//     (forward) or snapshot read + imaging accumulation (adjoint);
+//   * the host cuts the work into exactly one cost-balanced unit per resident warp (a table of
+//     segments), so a launch is a single wave with no tail.
 //
-// Three unit types share the kernel: interior strips (128 columns, float4 per lane, no PML
-// arithmetic at all), top/bottom PML bands (128 columns, full PML update) and left/right PML
-// bands (32 columns, one column per lane).  PML units are listed first so the heavier ones start
-// early.  The layout puts the first interior column on a 128-byte boundary.
+// Three segment types share the kernel: interior strips (128 columns, float4 per lane, no PML
+// arithmetic at all, ring depth 4), top/bottom PML band strips (128 columns, full PML update, the
+// z-window of the PML memory variable lives in a second ring) and left/right PML band strips
+// (32 columns, direct loads).  The layout puts the first interior column on a 128-byte boundary.
 //
 // Arithmetic order per cell follows oracle/cpu_ref_impl.h (explicit fma, no contraction).
+#include <cuda.h>
+
+#include <algorithm>
 #include <type_traits>
+#include <vector>
 
 #include "common.h"
 
 namespace {
 
 constexpr int kNW = 4;        // warps per CTA (warps are independent; this is scheduling granularity)
+constexpr int kSegInt = 0, kSegBand = 1, kSegSide = 2;
+
+// one run of rows [zb, ze) of a column strip starting at device column x0 of shot s; only columns
+// in [cmin, cmax) are stored
+struct Seg {
+    int s, x0, zb, ze;
+    int type, cmin, cmax, pad;
+};
 
 struct StepParams {
     int nzp, pitch;
     int zs, ze, ys, ye;      // computational region (device coordinates, end exclusive)
-    int zlo, zhi, ylo, yhi;  // interior: sigma = 0 and no PML memory variable within reach
-    int xb;                  // first column of the top/bottom band strips (multiple of 4, <= ys)
-    int xr;                  // first column of the right band strips (multiple of 4, <= yhi)
     long long stride;        // floats per shot per field
     int S;
-    int pml;
-    // unit bookkeeping (per shot)
-    int tb_strips, tb_chunks, side_strips_l, side_strips_r, side_chunks, int_strips, int_chunks;
-    int bz, bzs, bzt;        // rows per interior chunk / per side-band chunk / per top-bottom chunk
-    int n_tb, n_side, n_int; // units per shot of each type
+    const Seg *segs;
+    const int *unit_start;   // [n_units + 1] segment ranges of the warp units
+    int n_units;
+    // TMA descriptors (2-D, rows x pitch, boxes of kRB rows): the wave workspace with 136- and
+    // 128-column boxes, w, the snapshots being read and the image; and the first row of each
+    // wavefield of this step inside the wave workspace / of this step's snapshot
+    CUtensorMap tm_wave_u, tm_wave_o, tm_w, tm_q, tm_g;
+    CUtensorMap ts_wave_u, ts_wave_o, ts_w, ts_q, ts_g;   // the same tensors with the narrow boxes of side strips
+    int row_u, row_um, row_pz, row_py, row_q;
     const float *u;
     float *um;
     const float *pz, *py;
@@ -66,8 +81,7 @@ struct F4 { float a[4]; };
 __device__ __forceinline__ F4 f4(const float4 t) { F4 r; r.a[0] = t.x; r.a[1] = t.y; r.a[2] = t.z; r.a[3] = t.w; return r; }
 __device__ __forceinline__ float4 t4(const F4 &r) { return make_float4(r.a[0], r.a[1], r.a[2], r.a[3]); }
 __device__ __forceinline__ F4 ld_nc(const float *p) { return f4(__ldg(reinterpret_cast<const float4 *>(p))); }
-__device__ __forceinline__ F4 ld_plain(const float *p) { return f4(*reinterpret_cast<const float4 *>(p)); }
-__device__ __forceinline__ F4 ld_stream(const float *p) { return f4(__ldcs(reinterpret_cast<const float4 *>(p))); }
+__device__ __forceinline__ F4 lds4(const float *p) { return f4(*reinterpret_cast<const float4 *>(p)); }
 // masked store of 4 values starting at device column `col` of row pointer `row`
 template <bool STREAM>
 __device__ __forceinline__ void st_masked(float *row, int col, const F4 &v, int cmin, int cmax, bool rowok) {
@@ -85,235 +99,481 @@ __device__ __forceinline__ void st_masked(float *row, int col, const F4 &v, int 
         }
 }
 
-// ring of u rows when the next block is prefetched: >= 2H + 2*RPT rows, an even number of blocks
-__host__ __device__ constexpr int ring_rows(int H, int RPT) { return (2 * H + 2 * RPT + 2 * RPT - 1) / (2 * RPT) * (2 * RPT); }
+// ---- mbarrier / TMA bulk copy (per-warp pipelines) -------------------------------------------
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+// global -> shared TMA tile copy of one box of the 2-D tensor `tm` whose corner is (x, y)
+__device__ __forceinline__ void tma_g2s(float *dst, const CUtensorMap *tm, int x, int y, unsigned bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+            smem_u32(dst)),
+        "l"(tm), "r"(x), "r"(y), "r"(bar)
+        : "memory");
+}
 
-// One warp marches down z through a strip of columns of shot s.  The 32 lanes form 32/LW lane
-// groups of LW lanes; group g owns columns [x0, x0 + 4*LW) and rows [zb + g*gstep, ... + nrows),
-// clipped to zend; only columns in [cmin, cmax) are stored.  Every lane owns one float4 per row.
-//   LW = 32: one strip of 128 columns (interior strips, top/bottom PML bands)
-//   LW =  8: four row-chunks of a 32-column strip side by side (left/right PML bands)
+// ---- per-warp shared-memory budget ------------------------------------------------------------
+constexpr int kRB = 4;        // rows per TMA box / ring block (>= H)
+constexpr int kRowU = 136;    // a ring row of u / py: 4-column halo | 128 own columns | 4-column halo
+constexpr int kRowO = 128;    // a ring row of everything else
+constexpr int kBlkU = kRB * kRowU, kBlkO = kRB * kRowO;   // floats per ring block
+constexpr int kDOInt = 3;     // ring depth (blocks in flight) of interior segments
+constexpr int kDOBand = 1;    // ring depth of top/bottom band segments
+constexpr int kBarFloats = 32;  // 8 mbarriers at the head of the warp's region (keeps blocks 128-byte aligned)
+
+// operand blocks fetched per iteration by side strips: u-, w (+ snapshot, image in the adjoint)
+__host__ __device__ constexpr int n_ops(int MODE) { return MODE == 2 ? 4 : 2; }
+// ... and by 128-column strips, which read w (shared by all shots, L2 resident) with plain loads
+__host__ __device__ constexpr int n_ops_ring(int MODE) { return MODE == 2 ? 3 : 1; }
+__host__ __device__ constexpr int ring_floats(int MODE, bool PML, int DO) {
+    return (DO + 1) * kBlkU + DO * n_ops_ring(MODE) * kBlkO + (PML ? (DO + 2) * kBlkO + DO * kBlkU : 0);
+}
+constexpr int kSideU = 40, kSideO = 32;          // ring row widths of side strips
+constexpr int kSideBlkU = kRB * kSideU, kSideBlkO = kRB * kSideO;
+constexpr int kDOSide = 3;
+__host__ __device__ constexpr int side_ring_floats(int MODE) {
+    return (kDOSide + 2) * (kSideBlkU + kSideBlkO) + kDOSide * (n_ops(MODE) * kSideBlkO + kSideBlkU);
+}
+__host__ __device__ constexpr int cmax_i(int a, int b) { return a > b ? a : b; }
+__host__ __device__ constexpr int warp_smem_floats(int MODE) {
+    return kBarFloats + cmax_i(cmax_i(ring_floats(MODE, false, kDOInt), ring_floats(MODE, true, kDOBand)),
+                               side_ring_floats(MODE));
+}
+
+// ---- injection into the freshly written field: points of shot s inside rows [zb, ze), columns
+// [c_lo, c_hi); lanes lx of LW take the list entries round robin ----
+__device__ __forceinline__ void inject(const StepParams &p, const int s, float *__restrict__ um, const int zb,
+                                       const int ze, const int c_lo, const int c_hi, const int lx, const int LW) {
+    const int *rs = p.inj_row_start + (size_t)s * (p.nzp + 1);
+    const int base = s * p.n_inj;
+    const int zq = min(zb, ze);
+    const int e0 = __ldg(rs + zq), e1 = __ldg(rs + ze);
+    for (int e = e0 + lx; e < e1; e += LW) {
+        const int cell = __ldg(p.inj_cell + e);
+        const int zc = cell / p.pitch, yc = cell - zc * p.pitch;
+        if (yc < c_lo || yc >= c_hi) continue;
+        if (e > base && __ldg(p.inj_cell + e - 1) == cell) continue;  // not the head of its run
+        float coef = __ldg(p.w + cell);
+        if (p.inj_scale_a) {
+            const float hs = p.hdt * (__ldg(p.sigz + zc) + __ldg(p.sigy + yc));
+            coef = (1.0f / (1.0f + hs)) * coef;
+        }
+        float val = um[cell];
+        for (int k = e; k < base + p.n_inj && __ldg(p.inj_cell + k) == cell; ++k)
+            val = fmaf(coef, __ldg(p.inj_amp + base + __ldg(p.inj_col + k)), val);
+        um[cell] = val;
+    }
+}
+
+// One warp marches down z through rows [zb, ze) of the 128-column strip at x0 of shot sg.s in blocks
+// of kRB rows, fed by TMA tile copies into its shared-memory ring `sm`; bar0 + 8*i, i < DO, are the
+// ring mbarriers, bar0 + 8*DO the prologue mbarrier, `phase` holds their parity bits.
+// Ring blocks (k = block index, b = iteration block, rows relative to the segment start zb):
+//   u   block k: rows [H - kRB + k*kRB, +kRB)      k = 0 prologue, k = b + 1 arrives with iteration b
+//   pz  block k: rows [H - 2kRB + k*kRB, +kRB)     k = 0, 1 prologue, k = b + 2 arrives with iteration b
+//   operands (u-, w, snapshot, image) and py block b: rows [b*kRB, +kRB)
 // MODE 0: advance only.  MODE 1: advance and write q (forward with gradient).
 // MODE 2: read q, accumulate the image, advance (adjoint with model gradient).
-// ROT: the z loop is unrolled over one period of the register ring so that the sliding window of
-// u rows never moves between registers (hot interior path); otherwise the window is shifted.
-template <int H, int MODE, bool PML, int RPT, int LW, bool ROT>
-__device__ __forceinline__ void march(const StepParams &p, const int s, const int x0, const int zb0,
-                                      const int gstep, const int nrows, const int zend,
-                                      const int cmin, const int cmax, float *sm) {
-    constexpr int SW = 4 * LW + 8;              // shared row of one lane group: halo | own | halo
-    constexpr int WR = ROT ? ring_rows(H, RPT) : 2 * H + RPT;
-    constexpr int PER = ROT ? WR / RPT : 1;
+template <int H, int MODE, bool PML, int DO>
+__device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, float *sm, const unsigned bar0,
+                                           unsigned &phase) {
+    static_assert(H <= kRB, "a ring block must hold the stencil half width");
+    constexpr int RB = kRB;
+    constexpr int DUB = DO + 1, DPB = DO + 2;
+    constexpr int NOPS = n_ops_ring(MODE);
+    float *const U = sm;
+    float *const OPS = U + DUB * kBlkU;
+    float *const PZ = OPS + DO * NOPS * kBlkO;
+    float *const PY = PZ + DPB * kBlkO;
     const int lane = threadIdx.x & 31;
-    const int lx = lane % LW, grp = lane / LW;
-    const int zb = zb0 + grp * gstep;
-    const int ze = min(zend, zb + nrows);       // this lane group's end row (stores only)
-    const int col = x0 + 4 * lx;                // true column (store mask)
-    const int colL = min(col, p.pitch - 4);     // column used for loads (always in range)
-    const int zmax = p.ze - 1;                  // last computational row: loads are clamped to it
+    const int s = sg.s, x0 = sg.x0, zb = sg.zb, ze = sg.ze;
+    const int nblk = (ze - zb + RB - 1) / RB;
+    const int col = x0 + 4 * lane;
+    const int colL = min(col, p.pitch - 4);
     const size_t sb = (size_t)s * p.stride;
     const float *__restrict__ u = p.u + sb;
     float *__restrict__ um = p.um + sb;
-    // halo float4 this lane fetches for the y-stencil (first lane: left of the strip, last: right)
-    const bool hl = (lx == 0) || (lx == LW - 1);
-    const int hcol = (lx == 0) ? x0 - 4 : min(x0 + 4 * LW, p.pitch - 4);
-    float *srow = sm + grp * (2 * SW);
+    const int srow = s * p.nzp;          // first tensor row of this shot inside a field
+    constexpr unsigned tx_blk = 4u * (kBlkU + NOPS * kBlkO + (PML ? kBlkO + kBlkU : 0));
 
-    F4 W[WR];
+    // lane 0: the copies of the iteration block whose first centre row is z0 into operand slot so
+    // (which names the barrier too), u slot su and pz slot sp
+    auto issue = [&](const int z0, const int so, const int su, const int sp) {
+        const unsigned bar = bar0 + 8u * so;
+        mbar_expect_tx(bar, tx_blk);
+        tma_g2s(U + su * kBlkU, &p.tm_wave_u, x0 - 4, p.row_u + srow + z0 + H, bar);
+        float *o = OPS + so * NOPS * kBlkO;
+        tma_g2s(o, &p.tm_wave_o, x0, p.row_um + srow + z0, bar);
+        if (MODE == 2) {
+            tma_g2s(o + kBlkO, &p.tm_q, x0, p.row_q + srow + z0, bar);
+            tma_g2s(o + 2 * kBlkO, &p.tm_g, x0, srow + z0, bar);
+        }
+        if (PML) {
+            tma_g2s(PZ + sp * kBlkO, &p.tm_wave_o, x0, p.row_pz + srow + z0 + H, bar);
+            tma_g2s(PY + so * kBlkU, &p.tm_wave_u, x0 - 4, p.row_py + srow + z0, bar);
+        }
+    };
+
+    // ---- prologue: u block 0, pz blocks 0 and 1, and the first DO iteration blocks ----
+    const unsigned barP = bar0 + 8u * DO;
+    if (lane == 0) {
+        mbar_expect_tx(barP, 4u * (kBlkU + (PML ? 2 * kBlkO : 0)));
+        tma_g2s(U, &p.tm_wave_u, x0 - 4, p.row_u + srow + zb + H - RB, barP);
+        if (PML) {
+            tma_g2s(PZ, &p.tm_wave_o, x0, p.row_pz + srow + zb + H - 2 * RB, barP);
+            tma_g2s(PZ + kBlkO, &p.tm_wave_o, x0, p.row_pz + srow + zb + H - RB, barP);
+        }
+        for (int j = 0; j < DO && j < nblk; ++j) issue(zb + j * RB, j, (j + 1) % DUB, (j + 2) % DPB);
+    }
+
+    // sliding window: inside iteration block b (first centre row z0), W[i] = u row z0 - H + i
+    F4 W[2 * H + RB];
 #pragma unroll
-    for (int i = 0; i < 2 * H; ++i) W[i] = ld_nc(u + min(zb - H + i, zmax + H) * p.pitch + colL);
-
+    for (int k = 0; k < 2 * H - RB; ++k) W[RB + k] = ld_nc(u + (size_t)(zb - H + k) * p.pitch + colL);
     F4 sy;
 #pragma unroll
     for (int j = 0; j < 4; ++j) sy.a[j] = PML ? __ldg(p.sigy + colL + j) : 0.f;
+    // w = v^2 dt^2 is shared by all shots and stays in L2: plain loads, one block ahead
+    const int zlast = p.ze - 1;
+    F4 wc[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) wc[r] = ld_nc(p.w + (size_t)min(zb + r, zlast) * p.pitch + colL);
+    mbar_wait(barP, (phase >> DO) & 1u);
+    phase ^= 1u << DO;
+#pragma unroll
+    for (int k = (2 * H - RB > 0 ? 2 * H - RB : 0); k < 2 * H; ++k)
+        W[RB + k] = lds4(U + (k - 2 * H + RB) * kRowU + 4 + 4 * lane);
 
-    // operands of the centre rows of a block (two sets: the block being computed / being fetched)
-    F4 oM[2][RPT], oW[2][RPT], oQ[2][RPT];
-    float4 oHal[2][RPT];
-    // issues the loads of the block starting at row z: its RPT new window rows go to ring slots
-    // slot0 + r, its centre-row operands to set `par`
-    auto fetch = [&](const int z, auto slot_tag, auto par_tag) {
-        constexpr int slot0 = decltype(slot_tag)::value, par = decltype(par_tag)::value;
+    int so = 0;                  // operand / barrier slot of this iteration block
+    int su_prev = 0, su = 1 % DUB;   // u slots of blocks b and b + 1
+    int sp0 = 0, sp1 = 1, sp2 = 2 % DPB;   // pz slots of blocks b, b + 1, b + 2
+    for (int b = 0; b < nblk; ++b) {
+        const int z0 = zb + b * RB;
+        mbar_wait(bar0 + 8u * so, (phase >> so) & 1u);
+        phase ^= 1u << so;
 #pragma unroll
-        for (int r = 0; r < RPT; ++r) {
-            const int off = min(z + r, zmax) * p.pitch;
-            W[(slot0 + r) % WR] = ld_nc(u + off + H * p.pitch + colL);
-            oM[par][r] = ld_plain(um + off + colL);
-            oW[par][r] = ld_nc(p.w + off + colL);
-            if (MODE == 2) oQ[par][r] = ld_stream(p.qr + sb + off + colL);
-            if (hl) oHal[par][r] = __ldg(reinterpret_cast<const float4 *>(u + off + hcol));
-        }
-    };
-    const int zstop = zb + nrows;
-    if constexpr (ROT) fetch(zb, std::integral_constant<int, 2 * H>{}, std::integral_constant<int, 0>{});
+        for (int k = 0; k < 2 * H; ++k) W[k] = W[k + RB];
+#pragma unroll
+        for (int r = 0; r < RB; ++r) W[2 * H + r] = lds4(U + su * kBlkU + r * kRowU + 4 + 4 * lane);
+        const float *const pzb[3] = {PZ + sp0 * kBlkO, PZ + sp1 * kBlkO, PZ + sp2 * kBlkO};
 
-    // one block of RPT rows starting at row z; the ring slot of window row i is (base + i) % WR
-    auto block = [&](const int z, auto base_tag, auto par_tag) {
-        constexpr int base = decltype(base_tag)::value, par = decltype(par_tag)::value;
-        if constexpr (ROT) {
-            // prefetch the next block while this one is computed
-            if (z + RPT < zstop)
-                fetch(z + RPT, std::integral_constant<int, (base + 2 * H + RPT) % WR>{},
-                      std::integral_constant<int, par ^ 1>{});
-        } else {
-            fetch(z, std::integral_constant<int, 2 * H>{}, std::integral_constant<int, 0>{});
-        }
-        F4 (&cM)[RPT] = oM[par];
-        F4 (&cW)[RPT] = oW[par];
-        F4 (&cQ)[RPT] = oQ[par];
-        float4 (&cHal)[RPT] = oHal[par];
 #pragma unroll
-        for (int r = 0; r < RPT; ++r) {
-            const int row = z + r;
-            const bool rowok = row < ze;
-            const F4 &C = W[(base + H + r) % WR];
-            // ---- y-neighbours of the centre row through the lane group's shared row ----
-            float *sbuf = srow + (r & 1) * SW;
-            *reinterpret_cast<float4 *>(sbuf + 4 + 4 * lx) = t4(C);
-            if (hl) *reinterpret_cast<float4 *>(sbuf + (lx == 0 ? 0 : 4 + 4 * LW)) = cHal[r];
-            __syncwarp();
-            float v[12];
-            {
-                const float4 L = *reinterpret_cast<const float4 *>(sbuf + 4 * lx);
-                const float4 R = *reinterpret_cast<const float4 *>(sbuf + 4 * lx + 8);
-                v[0] = L.x; v[1] = L.y; v[2] = L.z; v[3] = L.w;
-                v[8] = R.x; v[9] = R.y; v[10] = R.z; v[11] = R.w;
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) v[4 + j] = C.a[j];
-
-            F4 lap;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                float l = p.c0 * v[4 + j];
-#pragma unroll
-                for (int k = 1; k <= H; ++k) l = fmaf(p.cy2[k], v[4 + j - k] + v[4 + j + k], l);
-#pragma unroll
-                for (int k = 1; k <= H; ++k)
-                    l = fmaf(p.cz2[k], W[(base + H + r - k) % WR].a[j] + W[(base + H + r + k) % WR].a[j], l);
-                lap.a[j] = l;
-            }
-
-            F4 un, qv;
-            const int off = min(row, zmax) * p.pitch;
-            if (!PML) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    qv.a[j] = lap.a[j];
-                    un.a[j] = fmaf(cW[r].a[j], lap.a[j], fmaf(2.0f, v[4 + j], -cM[r].a[j]));
-                }
-            } else {
-                const float sz = __ldg(p.sigz + min(row, zmax));
-                const float *__restrict__ pz = p.pz + sb + off;
-                const float *__restrict__ py = p.py + sb + off;
-                const F4 pzc = ld_nc(pz + colL);
-                F4 dpz;
-#pragma unroll
-                for (int j = 0; j < 4; ++j) dpz.a[j] = 0.f;
-#pragma unroll
-                for (int k = 1; k <= H; ++k) {
-                    const F4 a = ld_nc(pz + k * p.pitch + colL), b = ld_nc(pz - k * p.pitch + colL);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) dpz.a[j] = fmaf(p.cz1[k], a.a[j] - b.a[j], dpz.a[j]);
-                }
-                float pyv[12];
+        for (int r = 0; r < RB; ++r) {
+            const int row = z0 + r;
+            if (row < ze) {
+                const size_t off = (size_t)row * p.pitch;
+                // the centre row sits H rows above the bottom of the window: u block b or b + 1
+                const float *uc = (r < H) ? U + su_prev * kBlkU + (r - H + RB) * kRowU : U + su * kBlkU + (r - H) * kRowU;
+                float v[12];
                 {
-                    const F4 t0 = ld_nc(py + colL - 4), t1 = ld_nc(py + colL);
-                    const F4 t2 = ld_nc(py + min(colL + 4, p.pitch - 4));
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) { pyv[j] = t0.a[j]; pyv[4 + j] = t1.a[j]; pyv[8 + j] = t2.a[j]; }
+                    const float4 L = *reinterpret_cast<const float4 *>(uc + 4 * lane);
+                    const float4 R = *reinterpret_cast<const float4 *>(uc + 8 + 4 * lane);
+                    v[0] = L.x; v[1] = L.y; v[2] = L.z; v[3] = L.w;
+                    v[8] = R.x; v[9] = R.y; v[10] = R.z; v[11] = R.w;
                 }
-                F4 pzn, pyn;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float uc = v[4 + j];
-                    float duz = 0.f, dpy = 0.f, duy = 0.f;
+                for (int q = 0; q < 4; ++q) v[4 + q] = W[r + H].a[q];
+                const float *o = OPS + so * NOPS * kBlkO + r * kRowO + 4 * lane;
+                const F4 cM = lds4(o), cW = wc[r];
+
+                F4 lap;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    float l = p.c0 * v[4 + q];
+#pragma unroll
+                    for (int k = 1; k <= H; ++k) l = fmaf(p.cy2[k], v[4 + q - k] + v[4 + q + k], l);
+#pragma unroll
+                    for (int k = 1; k <= H; ++k) l = fmaf(p.cz2[k], W[r + H - k].a[q] + W[r + H + k].a[q], l);
+                    lap.a[q] = l;
+                }
+
+                F4 un, qv;
+                if (!PML) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        qv.a[q] = lap.a[q];
+                        un.a[q] = fmaf(cW.a[q], lap.a[q], fmaf(2.0f, v[4 + q], -cM.a[q]));
+                    }
+                } else {
+                    const float sz = __ldg(p.sigz + row);
+                    // pz row (row + d) sits at local index r + d - H + 2 RB of the three live pz blocks
+                    auto pzrow = [&](const int d) -> const float * {
+                        const int l = r + d - H + 2 * RB;
+                        return pzb[l / RB] + (l % RB) * kRowO + 4 * lane;
+                    };
+                    const F4 pzc = lds4(pzrow(0));
+                    F4 dpz;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) dpz.a[q] = 0.f;
 #pragma unroll
                     for (int k = 1; k <= H; ++k) {
-                        duz = fmaf(p.cz1[k], W[(base + H + r + k) % WR].a[j] - W[(base + H + r - k) % WR].a[j], duz);
-                        dpy = fmaf(p.cy1[k], pyv[4 + j + k] - pyv[4 + j - k], dpy);
-                        duy = fmaf(p.cy1[k], v[4 + j + k] - v[4 + j - k], duy);
-                    }
-                    const float q = (lap.a[j] + dpz.a[j]) + dpy;
-                    const float hs = p.hdt * (sz + sy.a[j]);
-                    const float a = 1.0f / (1.0f + hs);
-                    const float cu = a * fmaf(-p.dt2, sz * sy.a[j], 2.0f);
-                    const float cum = a * (hs - 1.0f);
-                    const float aw = a * cW[r].a[j];
-                    qv.a[j] = q;
-                    un.a[j] = fmaf(aw, q, fmaf(cu, uc, cum * cM[r].a[j]));
-                    pzn.a[j] = fmaf(p.dt * (sy.a[j] - sz), duz, fmaf(-p.dt, sz, 1.0f) * pzc.a[j]);
-                    pyn.a[j] = fmaf(p.dt * (sz - sy.a[j]), duy, fmaf(-p.dt, sy.a[j], 1.0f) * pyv[4 + j]);
-                }
-                st_masked<false>(p.pzn + sb + off, col, pzn, cmin, cmax, rowok);
-                st_masked<false>(p.pyn + sb + off, col, pyn, cmin, cmax, rowok);
-            }
-            st_masked<false>(um + off, col, un, cmin, cmax, rowok);
-            if (MODE == 1) st_masked<true>(p.qw + sb + off, col, qv, cmin, cmax, rowok);
-            if (MODE == 2) {
-                // image of this shot: G += field * q_read (single owner per cell: deterministic)
-                F4 g = ld_plain(p.G + sb + off + colL);
+                        const F4 a = lds4(pzrow(k)), bb = lds4(pzrow(-k));
 #pragma unroll
-                for (int j = 0; j < 4; ++j) g.a[j] = fmaf(v[4 + j], cQ[r].a[j], g.a[j]);
-                st_masked<false>(p.G + sb + off, col, g, cmin, cmax, rowok);
+                        for (int q = 0; q < 4; ++q) dpz.a[q] = fmaf(p.cz1[k], a.a[q] - bb.a[q], dpz.a[q]);
+                    }
+                    float pyv[12];
+                    {
+                        const float *pr = PY + so * kBlkU + r * kRowU + 4 * lane;
+                        const F4 t0 = lds4(pr), t1 = lds4(pr + 4), t2 = lds4(pr + 8);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) { pyv[q] = t0.a[q]; pyv[4 + q] = t1.a[q]; pyv[8 + q] = t2.a[q]; }
+                    }
+                    F4 pzn, pyn;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float uc0 = v[4 + q];
+                        float duz = 0.f, dpy = 0.f, duy = 0.f;
+#pragma unroll
+                        for (int k = 1; k <= H; ++k) {
+                            duz = fmaf(p.cz1[k], W[r + H + k].a[q] - W[r + H - k].a[q], duz);
+                            dpy = fmaf(p.cy1[k], pyv[4 + q + k] - pyv[4 + q - k], dpy);
+                            duy = fmaf(p.cy1[k], v[4 + q + k] - v[4 + q - k], duy);
+                        }
+                        const float qq = (lap.a[q] + dpz.a[q]) + dpy;
+                        const float hs = p.hdt * (sz + sy.a[q]);
+                        const float a = 1.0f / (1.0f + hs);
+                        const float cu = a * fmaf(-p.dt2, sz * sy.a[q], 2.0f);
+                        const float cum = a * (hs - 1.0f);
+                        const float aw = a * cW.a[q];
+                        qv.a[q] = qq;
+                        un.a[q] = fmaf(aw, qq, fmaf(cu, uc0, cum * cM.a[q]));
+                        pzn.a[q] = fmaf(p.dt * (sy.a[q] - sz), duz, fmaf(-p.dt, sz, 1.0f) * pzc.a[q]);
+                        pyn.a[q] = fmaf(p.dt * (sz - sy.a[q]), duy, fmaf(-p.dt, sy.a[q], 1.0f) * pyv[4 + q]);
+                    }
+                    st_masked<false>(p.pzn + sb + off, col, pzn, sg.cmin, sg.cmax, true);
+                    st_masked<false>(p.pyn + sb + off, col, pyn, sg.cmin, sg.cmax, true);
+                }
+                st_masked<false>(um + off, col, un, sg.cmin, sg.cmax, true);
+                if (MODE == 1) st_masked<true>(p.qw + sb + off, col, qv, sg.cmin, sg.cmax, true);
+                if (MODE == 2) {
+                    // image of this shot: G += field * q_read (single owner per cell: deterministic)
+                    const F4 cQ = lds4(o + kBlkO);
+                    F4 g = lds4(o + 2 * kBlkO);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) g.a[q] = fmaf(v[4 + q], cQ.a[q], g.a[q]);
+                    st_masked<false>(p.G + sb + off, col, g, sg.cmin, sg.cmax, true);
+                }
             }
         }
-    };
 
-    if constexpr (ROT) {
-        int z = zb;
-        while (z < zstop) {
-            // one period of the ring: PER blocks, window slots are compile-time constants
-            auto run = [&](auto self, auto ph_tag) -> void {
-                constexpr int ph = decltype(ph_tag)::value;
-                if constexpr (ph < PER) {
-                    if (z < zstop) {
-                        block(z, std::integral_constant<int, (ph * RPT) % WR>{}, std::integral_constant<int, ph & 1>{});
-                        z += RPT;
-                        self(self, std::integral_constant<int, ph + 1>{});
-                    }
-                }
-            };
-            run(run, std::integral_constant<int, 0>{});
-        }
-    } else {
-        for (int z = zb; z < zstop; z += RPT) {
-            block(z, std::integral_constant<int, 0>{}, std::integral_constant<int, 0>{});
+        // ---- refill: the slots this iteration block has finished with take block b + DO ----
+        __syncwarp();
+        if (lane == 0 && b + DO < nblk) issue(z0 + DO * RB, so, su_prev, sp0);
+        if (b + 1 < nblk) {
 #pragma unroll
-            for (int i = 0; i < 2 * H; ++i) W[i] = W[i + RPT];
+            for (int r = 0; r < RB; ++r) wc[r] = ld_nc(p.w + (size_t)min(z0 + RB + r, zlast) * p.pitch + colL);
         }
+        if (++so == DO) so = 0;
+        su_prev = su;
+        if (++su == DUB) su = 0;
+        sp0 = sp1; sp1 = sp2;
+        if (++sp2 == DPB) sp2 = 0;
     }
 
-    // ---- injection into the freshly written field: points of this shot inside this lane group ----
     if (p.n_inj > 0) {
         __syncwarp();  // orders this warp's stores above before the read-modify-writes below
-        const int *rs = p.inj_row_start + (size_t)s * (p.nzp + 1);
-        const int base = s * p.n_inj;
-        const int zq = min(zb, ze);
-        const int e0 = __ldg(rs + zq), e1 = __ldg(rs + ze);
-        const int c_lo = max(cmin, x0), c_hi = min(cmax, x0 + 4 * LW);
-        for (int e = e0 + lx; e < e1; e += LW) {
-            const int cell = __ldg(p.inj_cell + e);
-            const int zc = cell / p.pitch, yc = cell - zc * p.pitch;
-            if (yc < c_lo || yc >= c_hi) continue;
-            if (e > base && __ldg(p.inj_cell + e - 1) == cell) continue;  // not the head of its run
-            float coef = __ldg(p.w + cell);
-            if (p.inj_scale_a) {
-                const float hs = p.hdt * (__ldg(p.sigz + zc) + __ldg(p.sigy + yc));
-                coef = (1.0f / (1.0f + hs)) * coef;
-            }
-            float val = um[cell];
-            for (int k = e; k < base + p.n_inj && __ldg(p.inj_cell + k) == cell; ++k)
-                val = fmaf(coef, __ldg(p.inj_amp + base + __ldg(p.inj_col + k)), val);
-            um[cell] = val;
-        }
+        inject(p, s, um, zb, ze, max(sg.cmin, x0), min(sg.cmax, x0 + 128), lane, 32);
     }
+    __syncwarp();
+}
+
+// Left/right PML band strips (32 columns), also TMA fed.  The 32 lanes form 4 lane groups of 8
+// lanes; lane group g computes row z0 + g of every block of kRB = 4 rows, so a block iteration
+// covers 4 rows x 32 columns.  Nothing is kept in registers between blocks: the z-windows of u and
+// pz are read from rings that hold three live blocks (rows z0 - kRB .. z0 + 2 kRB) plus DO in
+// flight.  Block k of the u / pz rings holds rows [(k - 1) kRB, k kRB) relative to zb.
+
+template <int H, int MODE>
+__device__ __forceinline__ void march_side(const StepParams &p, const Seg &sg, float *sm, const unsigned bar0,
+                                           unsigned &phase) {
+    constexpr int RB = kRB, DO = kDOSide, D = DO + 2;
+    constexpr int NOPS = n_ops(MODE);
+    float *const U = sm;
+    float *const PZ = U + D * kSideBlkU;
+    float *const OPS = PZ + D * kSideBlkO;
+    float *const PY = OPS + DO * NOPS * kSideBlkO;
+    const int lane = threadIdx.x & 31;
+    const int lx = lane & 7, grp = lane >> 3;
+    const int s = sg.s, x0 = sg.x0, zb = sg.zb, ze = sg.ze, cmin = sg.cmin, cmax = sg.cmax;
+    const int nblk = (ze - zb + RB - 1) / RB;
+    const int col = x0 + 4 * lx;
+    const int colL = min(col, p.pitch - 4);
+    const size_t sb = (size_t)s * p.stride;
+    float *__restrict__ um = p.um + sb;
+    const int srow = s * p.nzp;
+    constexpr unsigned tx_blk = 4u * (kSideBlkU + kSideBlkO + NOPS * kSideBlkO + kSideBlkU);
+
+    auto issue = [&](const int z0, const int so, const int sk) {
+        const unsigned bar = bar0 + 8u * so;
+        mbar_expect_tx(bar, tx_blk);
+        tma_g2s(U + sk * kSideBlkU, &p.ts_wave_u, x0 - 4, p.row_u + srow + z0 + RB, bar);
+        tma_g2s(PZ + sk * kSideBlkO, &p.ts_wave_o, x0, p.row_pz + srow + z0 + RB, bar);
+        float *o = OPS + so * NOPS * kSideBlkO;
+        tma_g2s(o, &p.ts_wave_o, x0, p.row_um + srow + z0, bar);
+        tma_g2s(o + kSideBlkO, &p.ts_w, x0, z0, bar);
+        if (MODE == 2) {
+            tma_g2s(o + 2 * kSideBlkO, &p.ts_q, x0, p.row_q + srow + z0, bar);
+            tma_g2s(o + 3 * kSideBlkO, &p.ts_g, x0, srow + z0, bar);
+        }
+        tma_g2s(PY + so * kSideBlkU, &p.ts_wave_u, x0 - 4, p.row_py + srow + z0, bar);
+    };
+
+    const unsigned barP = bar0 + 8u * 4;
+    if (lane == 0) {
+        mbar_expect_tx(barP, 4u * 2 * (kSideBlkU + kSideBlkO));
+        tma_g2s(U, &p.ts_wave_u, x0 - 4, p.row_u + srow + zb - RB, barP);
+        tma_g2s(U + kSideBlkU, &p.ts_wave_u, x0 - 4, p.row_u + srow + zb, barP);
+        tma_g2s(PZ, &p.ts_wave_o, x0, p.row_pz + srow + zb - RB, barP);
+        tma_g2s(PZ + kSideBlkO, &p.ts_wave_o, x0, p.row_pz + srow + zb, barP);
+        for (int j = 0; j < DO && j < nblk; ++j) issue(zb + j * RB, j, (j + 2) % D);
+    }
+    F4 sy;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) sy.a[j] = __ldg(p.sigy + colL + j);
+    mbar_wait(barP, (phase >> 4) & 1u);
+    phase ^= 1u << 4;
+
+    int so = 0, s0 = 0;          // operand slot; ring slot of block b (rows z0 - RB ..)
+    for (int b = 0; b < nblk; ++b) {
+        const int z0 = zb + b * RB;
+        mbar_wait(bar0 + 8u * so, (phase >> so) & 1u);
+        phase ^= 1u << so;
+        const int row = z0 + grp;
+        // ring row of (row + d): local index l = grp + d + RB inside the three live blocks
+        auto urow = [&](const int d) -> const float * {
+            const int l = grp + d + RB;
+            int sl = s0 + (l >> 2);
+            if (sl >= D) sl -= D;
+            return U + sl * kSideBlkU + (l & 3) * kSideU + 4 * lx;
+        };
+        auto pzrow = [&](const int d) -> const float * {
+            const int l = grp + d + RB;
+            int sl = s0 + (l >> 2);
+            if (sl >= D) sl -= D;
+            return PZ + sl * kSideBlkO + (l & 3) * kSideO + 4 * lx;
+        };
+        float v[12];
+        {
+            const float *uc = urow(0);
+            const F4 t0 = lds4(uc), t1 = lds4(uc + 4), t2 = lds4(uc + 8);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { v[q] = t0.a[q]; v[4 + q] = t1.a[q]; v[8 + q] = t2.a[q]; }
+        }
+        const float *o = OPS + so * NOPS * kSideBlkO + grp * kSideO + 4 * lx;
+        const F4 cM = lds4(o), cW = lds4(o + kSideBlkO);
+        F4 lap, duz4, dpz;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            float l = p.c0 * v[4 + q];
+#pragma unroll
+            for (int k = 1; k <= H; ++k) l = fmaf(p.cy2[k], v[4 + q - k] + v[4 + q + k], l);
+            lap.a[q] = l;
+            duz4.a[q] = 0.f;
+            dpz.a[q] = 0.f;
+        }
+#pragma unroll
+        for (int k = 1; k <= H; ++k) {
+            const F4 up = lds4(urow(k) + 4), dn = lds4(urow(-k) + 4);
+            const F4 a = lds4(pzrow(k)), bb = lds4(pzrow(-k));
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                lap.a[q] = fmaf(p.cz2[k], dn.a[q] + up.a[q], lap.a[q]);
+                duz4.a[q] = fmaf(p.cz1[k], up.a[q] - dn.a[q], duz4.a[q]);
+                dpz.a[q] = fmaf(p.cz1[k], a.a[q] - bb.a[q], dpz.a[q]);
+            }
+        }
+        const F4 pzc = lds4(pzrow(0));
+        float pyv[12];
+        {
+            const float *pr = PY + so * kSideBlkU + grp * kSideU + 4 * lx;
+            const F4 t0 = lds4(pr), t1 = lds4(pr + 4), t2 = lds4(pr + 8);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { pyv[q] = t0.a[q]; pyv[4 + q] = t1.a[q]; pyv[8 + q] = t2.a[q]; }
+        }
+        const bool rowok = row < ze;
+        const float sz = __ldg(p.sigz + min(row, p.ze - 1));
+        const size_t off = (size_t)min(row, p.ze - 1) * p.pitch;
+        F4 un, qv, pzn, pyn;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float uc0 = v[4 + q];
+            float dpy = 0.f, duy = 0.f;
+#pragma unroll
+            for (int k = 1; k <= H; ++k) {
+                dpy = fmaf(p.cy1[k], pyv[4 + q + k] - pyv[4 + q - k], dpy);
+                duy = fmaf(p.cy1[k], v[4 + q + k] - v[4 + q - k], duy);
+            }
+            const float qq = (lap.a[q] + dpz.a[q]) + dpy;
+            const float hs = p.hdt * (sz + sy.a[q]);
+            const float a = 1.0f / (1.0f + hs);
+            const float cu = a * fmaf(-p.dt2, sz * sy.a[q], 2.0f);
+            const float cum = a * (hs - 1.0f);
+            const float aw = a * cW.a[q];
+            qv.a[q] = qq;
+            un.a[q] = fmaf(aw, qq, fmaf(cu, uc0, cum * cM.a[q]));
+            pzn.a[q] = fmaf(p.dt * (sy.a[q] - sz), duz4.a[q], fmaf(-p.dt, sz, 1.0f) * pzc.a[q]);
+            pyn.a[q] = fmaf(p.dt * (sz - sy.a[q]), duy, fmaf(-p.dt, sy.a[q], 1.0f) * pyv[4 + q]);
+        }
+        st_masked<false>(p.pzn + sb + off, col, pzn, cmin, cmax, rowok);
+        st_masked<false>(p.pyn + sb + off, col, pyn, cmin, cmax, rowok);
+        st_masked<false>(um + off, col, un, cmin, cmax, rowok);
+        if (MODE == 1) st_masked<true>(p.qw + sb + off, col, qv, cmin, cmax, rowok);
+        if (MODE == 2) {
+            const F4 cQ = lds4(o + 2 * kSideBlkO);
+            F4 g = lds4(o + 3 * kSideBlkO);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) g.a[q] = fmaf(v[4 + q], cQ.a[q], g.a[q]);
+            st_masked<false>(p.G + sb + off, col, g, cmin, cmax, rowok);
+        }
+
+        __syncwarp();
+        if (lane == 0 && b + DO < nblk) issue(z0 + DO * RB, so, s0);
+        if (++so == DO) so = 0;
+        if (++s0 == D) s0 = 0;
+    }
+
+    if (p.n_inj > 0) {
+        __syncwarp();
+        inject(p, s, um, zb, ze, max(cmin, x0), min(cmax, x0 + 32), lane, 32);
+    }
+    __syncwarp();
 }
 
 template <int H, int MODE, int OCC>
 __global__ void __launch_bounds__(kNW * 32, OCC) acoustic_step_kernel(const __grid_constant__ StepParams p) {
-    __shared__ __align__(16) float smem[kNW][2 * (32 * 4 + 8) + 64];
-    const int tid = threadIdx.x, warp = tid >> 5;
+    extern __shared__ __align__(128) float smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    // Programmatic dependent launch: this grid may become resident while the previous step is
+    // still draining.  Let the next step do the same, set up the warp's barriers, then wait for
+    // the previous step's stores before reading any wavefield.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    float *wsm = smem + (size_t)warp * warp_smem_floats(MODE);
+    const unsigned bar0 = smem_u32(wsm);
+    if (lane == 0) {
+#pragma unroll
+        for (int b = 0; b < 8; ++b) mbar_init(bar0 + 8u * b, 1u);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 
     // ---- sampling duty: record the current field at the sampling cells (before the step) ----
     {
@@ -331,46 +591,31 @@ __global__ void __launch_bounds__(kNW * 32, OCC) acoustic_step_kernel(const __gr
         }
     }
 
-    // ---- unit decode: [top/bottom bands | side bands | interior], each shot-major ----
-    int id = blockIdx.x * kNW + warp;
-    float *sm = smem[warp];
-    const int tb_total = p.S * p.n_tb, side_total = p.S * p.n_side, int_total = p.S * p.n_int;
-    if (id < tb_total) {
-        const int s = id / p.n_tb, t = id - s * p.n_tb;
-        const int bc = t / p.tb_strips, strip = t - bc * p.tb_strips;
-        const int band = bc / p.tb_chunks, chunk = bc - band * p.tb_chunks;
-        const int zb = (band ? p.zhi : p.zs) + chunk * p.bzt;
-        march<H, MODE, true, 1, 32, false>(p, s, p.xb + 128 * strip, zb, 0, p.bzt, band ? p.ze : p.zlo,
-                                           p.ys, p.ye, sm);
-        return;
-    }
-    id -= tb_total;
-    if (id < side_total) {
-        // four row-chunks of one 32-column strip per warp (8 lanes x float4 each)
-        const int s = id / p.n_side, t = id - s * p.n_side;
-        const int per_chunk = p.side_strips_l + p.side_strips_r;
-        const int chunk = t / per_chunk, k = t - chunk * per_chunk;
-        const int zb = p.zlo + chunk * (4 * p.bzs);
-        if (k < p.side_strips_l)
-            march<H, MODE, true, 1, 8, false>(p, s, p.xb + 32 * k, zb, p.bzs, p.bzs, p.zhi, p.ys, p.ylo, sm);
-        else
-            march<H, MODE, true, 1, 8, false>(p, s, p.xr + 32 * (k - p.side_strips_l), zb, p.bzs, p.bzs,
-                                              p.zhi, p.yhi, p.ye, sm);
-        return;
-    }
-    id -= side_total;
-    if (id < int_total) {
-        const int s = id / p.n_int, t = id - s * p.n_int;
-        const int chunk = t / p.int_strips, strip = t - chunk * p.int_strips;
-        const int zb = p.zlo + chunk * p.bz;
-        march<H, MODE, false, 2, 32, true>(p, s, p.ylo + 128 * strip, zb, 0, p.bz, p.zhi, p.ylo, p.yhi, sm);
+    const int unit = blockIdx.x * kNW + warp;
+    if (unit >= p.n_units) return;
+    const int g0 = __ldg(p.unit_start + unit), g1 = __ldg(p.unit_start + unit + 1);
+    if (g0 >= g1) return;
+
+    unsigned phase = 0;
+    float *ring = wsm + kBarFloats;
+    for (int g = g0; g < g1; ++g) {
+        Seg sg;
+        {
+            const int4 a = __ldg(reinterpret_cast<const int4 *>(p.segs + g));
+            const int4 b = __ldg(reinterpret_cast<const int4 *>(p.segs + g) + 1);
+            sg.s = a.x; sg.x0 = a.y; sg.zb = a.z; sg.ze = a.w;
+            sg.type = b.x; sg.cmin = b.y; sg.cmax = b.z; sg.pad = 0;
+        }
+        if (sg.type == kSegInt) march_ring<H, MODE, false, kDOInt>(p, sg, ring, bar0, phase);
+        else if (sg.type == kSegBand) march_ring<H, MODE, true, kDOBand>(p, sg, ring, bar0, phase);
+        else march_side<H, MODE>(p, sg, ring, bar0, phase);
     }
 }
 
 }  // namespace
 
 // ------------------------------------------------------------------------------------------
-// Host side: layout, argument checks, the time loop.
+// Host side: layout, argument checks, the work table, the time loop.
 // ------------------------------------------------------------------------------------------
 namespace {
 
@@ -380,6 +625,10 @@ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 int env_int(const char *name, int dflt) {
     const char *e = getenv(name);
     return e ? atoi(e) : dflt;
+}
+double env_dbl(const char *name, double dflt) {
+    const char *e = getenv(name);
+    return e ? atof(e) : dflt;
 }
 
 int check_desc(const fwi_acoustic_desc *d) {
@@ -399,30 +648,42 @@ int check_desc(const fwi_acoustic_desc *d) {
     return FWI_OK;
 }
 
+// A column of work: rows [z0, z1) of one strip of one shot.
+struct Col {
+    int s, type, x0, z0, z1, cmin, cmax;
+};
+
 // Geometry shared by get_layout and run.
 struct Geom {
     int h, F, col0, pitch;
     int zs, ze, ys, ye, zlo, zhi, ylo, yhi, xb, xr;
-    int tb_strips, tb_chunks, side_l, side_r, side_chunks, int_strips, int_chunks, bz, bzs, bzt;
-    int n_tb, n_side, n_int;
+    int tb_strips, side_l, side_r, int_strips;
+    int max_rows;     // cap on the rows of one segment (chunk_rows; 0 = none)
 };
+
+constexpr int kMaxUnits = 16384;   // bound on resident warps of any device this could run on
 
 Geom make_geom(const fwi_acoustic_desc *d) {
     Geom g;
     g.h = d->order / 2;
     g.F = d->pml_width > 0 ? d->pml_width + g.h : 0;  // frame: sigma != 0 or PML memory within reach
-    // first interior column on a 128-byte boundary, at least 4 spare columns on the left
+    // first interior column on a 128-byte boundary; band strips start a whole number of 128-byte
+    // lines to its left and at least 4 columns into the row
     const int lead = g.h + g.F;
-    g.col0 = round_up(lead + 4, 32) - lead;
+    const int back = round_up(g.F, 32);
+    int ylo = round_up(lead + 4, 32);
+    while (ylo - back < 4) ylo += 32;
+    g.col0 = ylo - lead;
     g.pitch = round_up(g.col0 + d->nyp + 8, 32);
     g.zs = g.h; g.ze = d->nzp - g.h;
     g.ys = g.col0 + g.h; g.ye = g.col0 + d->nyp - g.h;
     g.zlo = g.zs + g.F; g.zhi = g.ze - g.F;
     g.ylo = g.ys + g.F; g.yhi = g.ye - g.F;
-    g.xb = g.ylo - round_up(g.F, 4);
+    if (g.zhi < g.zlo) g.zlo = g.zhi = (g.zs + g.ze) / 2;      // model thinner than the frame: bands meet
+    if (g.yhi < g.ylo) g.ylo = g.yhi = (g.ys + g.ye) / 2 / 4 * 4;
+    g.xb = ylo - back;
     g.xr = g.yhi / 4 * 4;
-    const int rows = g.zhi - g.zlo, cols = g.yhi - g.ylo;
-    g.int_strips = ceil_div(cols, 128);
+    g.int_strips = ceil_div(g.yhi - g.ylo, 128);
     if (g.F > 0) {
         g.tb_strips = ceil_div(g.ye - g.xb, 128);
         g.side_l = ceil_div(g.ylo - g.xb, 32);
@@ -430,45 +691,224 @@ Geom make_geom(const fwi_acoustic_desc *d) {
     } else {
         g.tb_strips = g.side_l = g.side_r = 0;
     }
-    // interior chunk height: enough units to fill the machine (148 SMs x 12 resident warps),
-    // but not so short that the 2H-row window prologue dominates
-    int bz = d->chunk_rows > 0 ? d->chunk_rows : env_int("FWI_B200_BZ", 0);
-    if (bz <= 0) {
-        const int target = env_int("FWI_B200_UNITS", 148 * 12 * 2);
-        int chunks = ceil_div(target, d->n_shots * g.int_strips);
-        if (chunks < 1) chunks = 1;
-        bz = ceil_div(rows, chunks);
-        if (bz < 24) bz = 24;
-    }
-    if (bz > rows) bz = rows;
-    bz = round_up(bz, 2);
-    g.bz = bz;
-    g.int_chunks = ceil_div(rows, bz);
-    g.bzs = env_int("FWI_B200_BZS", 8);
-    g.bzt = env_int("FWI_B200_BZT", 8);
-    g.side_chunks = g.F > 0 ? ceil_div(rows, 4 * g.bzs) : 0;  // a warp marches 4 row-chunks side by side
-    g.tb_chunks = g.F > 0 ? ceil_div(g.F, g.bzt) : 0;
-    g.n_tb = 2 * g.tb_chunks * g.tb_strips;
-    g.n_side = g.side_chunks * (g.side_l + g.side_r);
-    g.n_int = g.int_chunks * g.int_strips;
+    g.max_rows = d->chunk_rows > 0 ? d->chunk_rows : env_int("FWI_B200_BZ", 0);
     return g;
 }
 
+// every column of work of one launch: side strips, then band strips, then interior strips
+// Every column of work of one launch: side strips, then band strips, then interior strips.  With
+// piece_rows > 0 the side and interior columns are cut into pieces of that many rows and listed
+// row-chunk major (all strips of a shot at the same rows are neighbours in the list), so that the
+// warps of a CTA, which take consecutive list entries, stream adjacent strips of the same rows:
+// their 512-byte row reads then merge into multi-KB contiguous runs in DRAM pages and L2 lines.
+void list_columns(const fwi_acoustic_desc *d, const Geom &g, std::vector<Col> &cols, int piece_rows = 0) {
+    cols.clear();
+    const int rows = g.zhi - g.zlo;
+    const int pr = piece_rows > 0 ? piece_rows : std::max(rows, 1);
+    const int n_pieces = rows > 0 ? ceil_div(rows, pr) : 0;
+    if (g.F > 0)
+        for (int s = 0; s < d->n_shots; ++s)
+            for (int c = 0; c < n_pieces; ++c) {
+                const int z0 = g.zlo + c * pr, z1 = std::min(g.zhi, z0 + pr);
+                for (int k = 0; k < g.side_l; ++k) cols.push_back({s, kSegSide, g.xb + 32 * k, z0, z1, g.ys, g.ylo});
+                for (int k = 0; k < g.side_r; ++k) cols.push_back({s, kSegSide, g.xr + 32 * k, z0, z1, g.yhi, g.ye});
+            }
+    if (g.F > 0)
+        for (int s = 0; s < d->n_shots; ++s) {
+            if (g.zlo > g.zs)
+                for (int k = 0; k < g.tb_strips; ++k) cols.push_back({s, kSegBand, g.xb + 128 * k, g.zs, g.zlo, g.ys, g.ye});
+            if (g.ze > g.zhi)
+                for (int k = 0; k < g.tb_strips; ++k) cols.push_back({s, kSegBand, g.xb + 128 * k, g.zhi, g.ze, g.ys, g.ye});
+        }
+    for (int s = 0; s < d->n_shots; ++s)
+        for (int c = 0; c < n_pieces; ++c) {
+            const int z0 = g.zlo + c * pr, z1 = std::min(g.zhi, z0 + pr);
+            for (int k = 0; k < g.int_strips; ++k) cols.push_back({s, kSegInt, g.ylo + 128 * k, z0, z1, g.ylo, g.yhi});
+        }
+}
+
+// bound on the segments of any work table for these (uncut) columns
+int64_t max_segments(const std::vector<Col> &cols, const Geom &g) {
+    int64_t n = 0;
+    for (const Col &c : cols) n += g.max_rows > 0 ? ceil_div(c.z1 - c.z0, g.max_rows) : 1;
+    return 2 * n + 3 * (int64_t)kMaxUnits + 8;
+}
+
+struct CostModel {
+    double band, side, seg;
+    int min_rows;
+    double rate(int type) const { return type == kSegInt ? 1.0 : (type == kSegBand ? band : side); }
+};
+
+CostModel cost_model(const Geom &g) {
+    CostModel c;
+    c.band = env_dbl("FWI_B200_COST_BAND", 2.5);   // cost of a band row relative to an interior row
+    c.side = env_dbl("FWI_B200_COST_SIDE", 1.5);   // cost of one row of a side segment (4 rows per iteration)
+    c.seg = env_dbl("FWI_B200_COST_SEG", 6.0);     // prologue of a segment, in interior rows
+    c.min_rows = env_int("FWI_B200_MINROWS", 4);
+    if (g.max_rows > 0) c.min_rows = std::min(c.min_rows, g.max_rows);
+    if (c.min_rows < 1) c.min_rows = 1;
+    return c;
+}
+
+// Walks the columns in order, filling units up to capacity T; returns the number of units used.
+int fill_units(const std::vector<Col> &cols, const Geom &g, const CostModel &cm, double T, std::vector<Seg> *segs,
+               std::vector<int> *unit_start) {
+    if (segs) segs->clear();
+    if (unit_start) unit_start->assign(1, 0);
+    double cur = 0;
+    int n_segs = 0, units = 0;
+    for (const Col &c : cols) {
+        const double r = cm.rate(c.type);
+        int z = c.z0;
+        while (z < c.z1) {
+            const int left = c.z1 - z;
+            int n = (int)((T - cur - cm.seg) / r + 1e-9);
+            if (n < std::min(cm.min_rows, left)) {
+                if (cur > 0) {      // close the unit and retry with an empty one
+                    ++units;
+                    if (unit_start) unit_start->push_back(n_segs);
+                    cur = 0;
+                    continue;
+                }
+                n = std::min(cm.min_rows, left);
+            }
+            n = std::min(n, left);
+            if (g.max_rows > 0) n = std::min(n, g.max_rows);
+            if (segs) segs->push_back({c.s, c.x0, z, z + n, c.type, c.cmin, c.cmax, 0});
+            ++n_segs;
+            cur += n * r + cm.seg;
+            z += n;
+        }
+    }
+    if (cur > 0) {
+        ++units;
+        if (unit_start) unit_start->push_back(n_segs);
+    }
+    return units;
+}
+
+// Cuts the work of one launch into segments and deals them to at most `n_units` warp units: the
+// smallest unit capacity for which a contiguous fill of the (row-chunk major) column list needs no
+// more than n_units units (bisection).
+void build_units(const fwi_acoustic_desc *d, const Geom &g, int n_units, std::vector<Col> &cols,
+                 std::vector<Seg> &segs, std::vector<int> &unit_start) {
+    const CostModel cm = cost_model(g);
+    list_columns(d, g, cols);
+    double total = 0;
+    for (const Col &c : cols) total += (c.z1 - c.z0) * cm.rate(c.type) + cm.seg;
+    const double min_unit = 24.0;     // small problems: fewer, fuller units
+    if (total / n_units < min_unit) n_units = std::max(1, (int)(total / min_unit));
+    if (env_int("FWI_B200_PIECES", 0)) {
+        // pieces of about one unit's worth of interior rows
+        const int piece = std::max(cm.min_rows, (int)(total / n_units - cm.seg + 0.5));
+        list_columns(d, g, cols, piece);
+        total = 0;
+        for (const Col &c : cols) total += (c.z1 - c.z0) * cm.rate(c.type) + cm.seg;
+    }
+    double lo = total / n_units, hi = 2.0 * lo + cm.seg + cm.min_rows * std::max(cm.band, std::max(cm.side, 1.0)) + 64.0;
+    while (fill_units(cols, g, cm, hi, nullptr, nullptr) > n_units) hi *= 2.0;
+    for (int it = 0; it < 24; ++it) {
+        const double mid = 0.5 * (lo + hi);
+        if (fill_units(cols, g, cm, mid, nullptr, nullptr) <= n_units) hi = mid;
+        else lo = mid;
+    }
+    fill_units(cols, g, cm, hi, &segs, &unit_start);
+    if (unit_start.size() < 2) unit_start.push_back((int)segs.size());
+}
+
+// ---- TMA descriptors ----------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+
+// 2-D fp32 tensor [rows][pitch] at `base`, boxes of kRB rows x `box_cols` columns, zero fill outside
+int make_map(CUtensorMap *tm, const float *base, int64_t rows, int pitch, int box_cols) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) {
+        fwi::set_error("cuTensorMapEncodeTiled is not available from this driver");
+        return FWI_ERR_CUDA;
+    }
+    const cuuint64_t gdim[2] = {(cuuint64_t)pitch, (cuuint64_t)rows};
+    const cuuint64_t gstride[1] = {(cuuint64_t)pitch * sizeof(float)};
+    const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)kRB};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), gdim, gstride, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        fwi::set_error("cuTensorMapEncodeTiled failed (%d) for a [%lld][%d] tensor", (int)r, (long long)rows, pitch);
+        return FWI_ERR_CUDA;
+    }
+    return FWI_OK;
+}
+
 template <int H, int MODE>
-cudaError_t launch_step(const StepParams &p, int blocks, cudaStream_t st) {
-    static const int occ = env_int("FWI_B200_OCC", 3);
-    if (occ == 3) acoustic_step_kernel<H, MODE, 3><<<blocks, kNW * 32, 0, st>>>(p);
-    else acoustic_step_kernel<H, MODE, 4><<<blocks, kNW * 32, 0, st>>>(p);
-    return cudaGetLastError();
+struct Launcher {
+    static constexpr int kOcc = MODE == 2 ? 2 : 3;   // resident CTAs per SM the register budget is cut for
+    static constexpr size_t smem_bytes() { return (size_t)kNW * warp_smem_floats(MODE) * sizeof(float); }
+    // resident CTAs per SM of this kernel on the current device (cached per device)
+    static int resident_ctas(int *sms) {
+        static int cached_dev = -1, cached_occ = 0, cached_sms = 0;
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev != cached_dev) {
+            auto kern = acoustic_step_kernel<H, MODE, kOcc>;
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes());
+            int occ = 0;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kNW * 32, smem_bytes());
+            cudaDeviceGetAttribute(&cached_sms, cudaDevAttrMultiProcessorCount, dev);
+            cached_occ = occ;
+            cached_dev = dev;
+        }
+        *sms = cached_sms;
+        return cached_occ;
+    }
+    static cudaError_t launch(const StepParams &p, int blocks, cudaStream_t st) {
+        static const int pdl = env_int("FWI_B200_PDL", 1);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(blocks);
+        cfg.blockDim = dim3(kNW * 32);
+        cfg.dynamicSmemBytes = smem_bytes();
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = pdl ? 1 : 0;
+        return cudaLaunchKernelEx(&cfg, acoustic_step_kernel<H, MODE, kOcc>, p);
+    }
+};
+
+template <int MODE>
+int resident_h(int h, int *sms) {
+    switch (h) {
+    case 1: return Launcher<1, MODE>::resident_ctas(sms);
+    case 2: return Launcher<2, MODE>::resident_ctas(sms);
+    case 3: return Launcher<3, MODE>::resident_ctas(sms);
+    default: return Launcher<4, MODE>::resident_ctas(sms);
+    }
 }
 
 template <int MODE>
 cudaError_t launch_h(int h, const StepParams &p, int blocks, cudaStream_t st) {
     switch (h) {
-    case 1: return launch_step<1, MODE>(p, blocks, st);
-    case 2: return launch_step<2, MODE>(p, blocks, st);
-    case 3: return launch_step<3, MODE>(p, blocks, st);
-    default: return launch_step<4, MODE>(p, blocks, st);
+    case 1: return Launcher<1, MODE>::launch(p, blocks, st);
+    case 2: return Launcher<2, MODE>::launch(p, blocks, st);
+    case 3: return Launcher<3, MODE>::launch(p, blocks, st);
+    default: return Launcher<4, MODE>::launch(p, blocks, st);
     }
 }
 
@@ -479,13 +919,53 @@ extern "C" int fwi_acoustic_get_layout(const fwi_acoustic_desc *desc, fwi_acoust
     if (rc != FWI_OK) return rc;
     FWI_CHECK_ARG(out != nullptr, "layout output is NULL");
     const Geom g = make_geom(desc);
+    std::vector<Col> cols;
+    list_columns(desc, g, cols);
     out->pitch = g.pitch;
     out->col0 = g.col0;
     out->shot_stride = (int64_t)desc->nzp * g.pitch;
     out->n_images = desc->n_shots;
     out->wave_fields = desc->pml_width > 0 ? 6 : 2;
-    out->chunk_rows = g.bz;
-    out->units_per_shot = g.n_tb + g.n_side + g.n_int;
+    out->chunk_rows = g.max_rows;
+    out->units_per_shot = (int32_t)(cols.size() / desc->n_shots);
+    out->unit_table_bytes = max_segments(cols, g) * (int64_t)sizeof(Seg) + (kMaxUnits + 1) * (int64_t)sizeof(int);
+    return FWI_OK;
+}
+
+extern "C" int fwi_acoustic_plan_stats(const fwi_acoustic_desc *desc, int n_units, int64_t *n_segments,
+                                       int32_t *n_units_used, double *max_cost, double *mean_cost) {
+    int rc = check_desc(desc);
+    if (rc != FWI_OK) return rc;
+    FWI_CHECK_ARG(n_units >= 1 && n_units <= kMaxUnits, "n_units out of range");
+    const Geom g = make_geom(desc);
+    std::vector<Col> cols;
+    std::vector<Seg> segs;
+    std::vector<int> unit_start;
+    build_units(desc, g, n_units, cols, segs, unit_start);
+    // every computational cell must be covered exactly once: check by area
+    int64_t area = 0;
+    for (const Seg &sg : segs) {
+        const int w = sg.type == kSegSide ? 32 : 128;
+        const int c0 = std::max(sg.cmin, sg.x0), c1 = std::min(sg.cmax, sg.x0 + w);
+        if (c1 > c0) area += (int64_t)(c1 - c0) * (sg.ze - sg.zb);
+    }
+    const int64_t want = (int64_t)desc->n_shots * (g.ze - g.zs) * (g.ye - g.ys);
+    FWI_CHECK_ARG(area == want, "internal: segments cover %lld cells, computational region has %lld",
+                  (long long)area, (long long)want);
+    const CostModel cm = cost_model(g);
+    double mx = 0, sum = 0;
+    const int nu = (int)unit_start.size() - 1;
+    for (int u = 0; u < nu; ++u) {
+        double c = 0;
+        for (int k = unit_start[u]; k < unit_start[u + 1]; ++k)
+            c += (segs[k].ze - segs[k].zb) * cm.rate(segs[k].type) + cm.seg;
+        mx = std::max(mx, c);
+        sum += c;
+    }
+    if (n_segments) *n_segments = (int64_t)segs.size();
+    if (n_units_used) *n_units_used = nu;
+    if (max_cost) *max_cost = mx;
+    if (mean_cost) *mean_cost = nu ? sum / nu : 0;
     return FWI_OK;
 }
 
@@ -494,6 +974,7 @@ extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_b
     if (rc != FWI_OK) return rc;
     FWI_CHECK_ARG(b != nullptr, "buffers struct is NULL");
     FWI_CHECK_ARG(b->w && b->wave, "w and wave must not be NULL");
+    FWI_CHECK_ARG(b->unit_table, "unit_table workspace must not be NULL");
     FWI_CHECK_ARG(d->pml_width == 0 || (b->sigz && b->sigy), "sigz/sigy required when pml_width > 0");
     FWI_CHECK_ARG(!d->smp_div_a || (b->sigz && b->sigy), "sigz/sigy required when smp_div_a is set");
     FWI_CHECK_ARG(!d->inj_scale_a || (b->sigz && b->sigy), "sigz/sigy required when inj_scale_a is set");
@@ -503,22 +984,44 @@ extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_b
     FWI_CHECK_ARG(!(b->q_write && b->q_read), "q_write and q_read are mutually exclusive");
     FWI_CHECK_ARG(!b->q_read || b->image, "image required with q_read");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (d->nsteps == 0) return FWI_OK;
 
     const Geom g = make_geom(d);
     const int h = g.h;
+    const int mode = b->q_read ? 2 : (b->q_write ? 1 : 0);
+
+    // ---- work table: one cost-balanced unit per resident warp ----
+    int sms = 0;
+    const int occ = mode == 2 ? resident_h<2>(h, &sms) : (mode == 1 ? resident_h<1>(h, &sms) : resident_h<0>(h, &sms));
+    if (occ <= 0 || sms <= 0) {
+        fwi::set_error("acoustic step kernel cannot be resident on this device (occupancy %d): %s", occ,
+                       cudaGetErrorString(cudaGetLastError()));
+        return FWI_ERR_CUDA;
+    }
+    int n_units = std::min(kMaxUnits, sms * occ * kNW);
+    const int units_env = env_int("FWI_B200_UNITS", 0);
+    if (units_env > 0) n_units = std::min(kMaxUnits, units_env);
+    thread_local std::vector<Col> cols;
+    thread_local std::vector<Seg> segs;
+    thread_local std::vector<int> unit_start;
+    build_units(d, g, n_units, cols, segs, unit_start);
+    list_columns(d, g, cols);
+    n_units = (int)unit_start.size() - 1;
+    FWI_CHECK_ARG((int64_t)segs.size() <= max_segments(cols, g), "internal: work table overflow");
+    Seg *d_segs = static_cast<Seg *>(b->unit_table);
+    int *d_units = reinterpret_cast<int *>(d_segs + max_segments(cols, g));
+    FWI_CHECK_CUDA(cudaMemcpyAsync(d_segs, segs.data(), segs.size() * sizeof(Seg), cudaMemcpyHostToDevice, st));
+    FWI_CHECK_CUDA(cudaMemcpyAsync(d_units, unit_start.data(), unit_start.size() * sizeof(int),
+                                   cudaMemcpyHostToDevice, st));
+    // (pageable source: cudaMemcpyAsync returns once the host data has been staged, so the vectors
+    // may be reused by the next call)
 
     StepParams p;
     p.nzp = d->nzp; p.pitch = g.pitch;
     p.zs = g.zs; p.ze = g.ze; p.ys = g.ys; p.ye = g.ye;
-    p.zlo = g.zlo; p.zhi = g.zhi; p.ylo = g.ylo; p.yhi = g.yhi;
-    p.xb = g.xb; p.xr = g.xr;
     p.stride = (long long)d->nzp * g.pitch;
     p.S = d->n_shots;
-    p.pml = d->pml_width > 0;
-    p.tb_strips = g.tb_strips; p.tb_chunks = g.tb_chunks; p.bzt = g.bzt; p.side_strips_l = g.side_l; p.side_strips_r = g.side_r;
-    p.side_chunks = g.side_chunks; p.int_strips = g.int_strips; p.int_chunks = g.int_chunks;
-    p.bz = g.bz; p.bzs = g.bzs;
-    p.n_tb = g.n_tb; p.n_side = g.n_side; p.n_int = g.n_int;
+    p.segs = d_segs; p.unit_start = d_units; p.n_units = n_units;
     p.w = b->w; p.sigz = b->sigz; p.sigy = b->sigy;
     p.inj_row_start = b->inj_row_start; p.inj_cell = b->inj_cell; p.inj_col = b->inj_col;
     p.n_inj = d->n_inj; p.inj_scale_a = d->inj_scale_a;
@@ -535,16 +1038,47 @@ extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_b
     p.dt = (float)d->dt; p.dt2 = p.dt * p.dt; p.hdt = 0.5f * p.dt;
 
     const size_t fld = (size_t)d->n_shots * p.stride;
+    const int fld_rows = d->n_shots * d->nzp;
+    const int n_fields = d->pml_width > 0 ? 6 : 2;
+    FWI_CHECK_ARG((int64_t)d->nsteps * fld_rows < (int64_t)1 << 31, "snapshot tensor has too many rows for one TMA descriptor");
+    if ((rc = make_map(&p.tm_wave_u, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kRowU)) != FWI_OK) return rc;
+    if ((rc = make_map(&p.tm_wave_o, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kRowO)) != FWI_OK) return rc;
+    if ((rc = make_map(&p.tm_w, b->w, d->nzp, g.pitch, kRowO)) != FWI_OK) return rc;
+    if (mode == 2) {
+        if ((rc = make_map(&p.tm_q, b->q_read, (int64_t)d->nsteps * fld_rows, g.pitch, kRowO)) != FWI_OK) return rc;
+        if ((rc = make_map(&p.tm_g, b->image, fld_rows, g.pitch, kRowO)) != FWI_OK) return rc;
+    } else {
+        p.tm_q = p.tm_w;
+        p.tm_g = p.tm_w;
+    }
+    if (d->pml_width > 0) {
+        if ((rc = make_map(&p.ts_wave_u, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kSideU)) != FWI_OK) return rc;
+        if ((rc = make_map(&p.ts_wave_o, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kSideO)) != FWI_OK) return rc;
+        if ((rc = make_map(&p.ts_w, b->w, d->nzp, g.pitch, kSideO)) != FWI_OK) return rc;
+        if (mode == 2) {
+            if ((rc = make_map(&p.ts_q, b->q_read, (int64_t)d->nsteps * fld_rows, g.pitch, kSideO)) != FWI_OK) return rc;
+            if ((rc = make_map(&p.ts_g, b->image, fld_rows, g.pitch, kSideO)) != FWI_OK) return rc;
+        } else {
+            p.ts_q = p.ts_w;
+            p.ts_g = p.ts_w;
+        }
+    } else {
+        p.ts_wave_u = p.ts_wave_o = p.ts_w = p.ts_q = p.ts_g = p.tm_w;
+    }
     float *u = b->wave, *um = b->wave + fld;
     float *pz = nullptr, *pzn = nullptr, *py = nullptr, *pyn = nullptr;
-    if (p.pml) { pz = b->wave + 2 * fld; pzn = b->wave + 3 * fld; py = b->wave + 4 * fld; pyn = b->wave + 5 * fld; }
+    if (d->pml_width > 0) { pz = b->wave + 2 * fld; pzn = b->wave + 3 * fld; py = b->wave + 4 * fld; pyn = b->wave + 5 * fld; }
 
-    const int mode = b->q_read ? 2 : (b->q_write ? 1 : 0);
-    const long long units = (long long)d->n_shots * (g.n_tb + g.n_side + g.n_int);
-    const int blocks = (int)((units + kNW - 1) / kNW);
+    // the sampling duty needs enough threads even when the stencil work is tiny
+    int blocks = ceil_div(n_units, kNW);
     for (int it = 0; it < d->nsteps; ++it) {
         const int n = d->adjoint ? d->nsteps - 1 - it : it;
         p.u = u; p.um = um; p.pz = pz; p.pzn = pzn; p.py = py; p.pyn = pyn;
+        p.row_u = (int)((u - b->wave) / g.pitch);
+        p.row_um = (int)((um - b->wave) / g.pitch);
+        p.row_pz = pz ? (int)((pz - b->wave) / g.pitch) : 0;
+        p.row_py = py ? (int)((py - b->wave) / g.pitch) : 0;
+        p.row_q = n * fld_rows;
         p.qw = b->q_write ? b->q_write + (size_t)n * fld : nullptr;
         p.qr = b->q_read ? b->q_read + (size_t)n * fld : nullptr;
         p.G = b->image;

@@ -92,9 +92,10 @@ class _Plan:
         wave = torch.zeros(int(self.lay.wave_fields) * self.S * self.stride, dtype=torch.float32, device=self.dev)
         smp_out = torch.empty(nsteps, self.S, n_smp, dtype=torch.float32, device=self.dev)
         start, icell, icol = inj
+        table = torch.empty(int(self.lay.unit_table_bytes), dtype=torch.uint8, device=self.dev)
         b = _lib.AcousticBuffers(_ptr(self.w), _ptr(self.sigz), _ptr(self.sigy), _ptr(wave), _ptr(start),
                                  _ptr(icell), _ptr(icol), _ptr(inj_amp), _ptr(smp_cell), _ptr(smp_out),
-                                 _ptr(q_write), _ptr(q_read), _ptr(image))
+                                 _ptr(q_write), _ptr(q_read), _ptr(image), _ptr(table))
         cur = torch.cuda.current_stream(self.dev)
         with torch.cuda.device(self.dev):
             fn = _lib.lib().fwi_acoustic_backward if adjoint else _lib.lib().fwi_acoustic_forward

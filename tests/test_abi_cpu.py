@@ -37,7 +37,7 @@ def test_library_exports_every_declared_symbol(so):
 
 def test_version_and_error_string(so):
     so.fwi_last_error.restype = ctypes.c_char_p
-    assert so.fwi_version() >= 4
+    assert so.fwi_version() >= 5
     assert so.fwi_last_error() is not None
 
 
@@ -50,7 +50,7 @@ def test_layout_is_pure_host_code_and_checks_arguments():
     assert lay.shot_stride == 124 * lay.pitch
     assert (lay.col0 + 2 * 2 + 10) % 32 == 0          # first interior column is 128-byte aligned
     assert lay.n_images == 10 and lay.wave_fields == 6
-    assert lay.chunk_rows >= 2 and lay.units_per_shot >= 1
+    assert lay.chunk_rows == 0 and lay.units_per_shot >= 1 and lay.unit_table_bytes > 0
     nopml = _lib.AcousticDesc(104, 304, 8, 0, 3, 0, 0, 0, 0, 0, 0, 0, 10.0, 10.0, 1e-3)
     assert L.fwi_acoustic_get_layout(ctypes.byref(nopml), ctypes.byref(lay)) == 0
     assert lay.wave_fields == 2 and (lay.col0 + 4) % 32 == 0
@@ -96,3 +96,25 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".h", ".cuh")):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in txt and "from oracle" not in txt, f
+
+
+@pytest.mark.parametrize("shape", [
+    (799, 2349, 8, 20, 6, 0), (799, 2349, 8, 20, 1, 0), (124, 324, 4, 10, 10, 0), (124, 324, 4, 10, 10, 2),
+    (58, 139, 4, 0, 2, 0), (40, 64, 8, 6, 2, 0), (30, 30, 8, 10, 1, 0), (1549, 3549, 8, 20, 2, 7),
+])
+def test_work_table_tiles_the_grid_and_is_balanced(shape):
+    """Host-only planner: the segments cover every computational cell exactly once (checked inside
+    the library by area) and the heaviest warp unit is within 10 % of the mean."""
+    L = pkg.lib()
+    L.fwi_acoustic_plan_stats.argtypes = [ctypes.POINTER(_lib.AcousticDesc), ctypes.c_int,
+                                          ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int32),
+                                          ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+    nzp, nyp, order, pml, S, chunk = shape
+    d = _lib.AcousticDesc(nzp, nyp, order, pml, S, chunk, 0, 0, 0, 0, 0, 0, 10.0, 10.0, 1e-3)
+    ns, nu, mx, mean = ctypes.c_int64(), ctypes.c_int32(), ctypes.c_double(), ctypes.c_double()
+    rc = L.fwi_acoustic_plan_stats(ctypes.byref(d), 148 * 16, ctypes.byref(ns), ctypes.byref(nu),
+                                   ctypes.byref(mx), ctypes.byref(mean))
+    assert rc == 0, L.fwi_last_error()
+    assert 1 <= nu.value <= 148 * 16 and ns.value >= nu.value
+    if chunk == 0:
+        assert mx.value <= 1.1 * mean.value + 6.0
