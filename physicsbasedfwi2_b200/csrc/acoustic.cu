@@ -35,7 +35,10 @@
 
 namespace {
 
-constexpr int kNW = 4;        // warps per CTA (warps are independent; this is scheduling granularity)
+// warps per CTA and resident CTAs per SM (warps are independent; this is scheduling granularity):
+// forward 2 x 6 warps with a 3-deep ring, adjoint (more operands per row) 3 x 3 warps, 2-deep
+__host__ __device__ constexpr int warps_per_cta(int MODE) { return MODE == 2 ? 3 : 6; }
+__host__ __device__ constexpr int ctas_per_sm(int MODE) { return MODE == 2 ? 3 : 2; }
 constexpr int kSegInt = 0, kSegBand = 1, kSegSide = 2;
 
 // one run of rows [zb, ze) of a column strip starting at device column x0 of shot s; only columns
@@ -53,6 +56,7 @@ struct StepParams {
     const Seg *segs;
     const int *unit_start;   // [n_units + 1] segment ranges of the warp units
     int n_units;
+    unsigned long long *trace;   // dev aid (FWI_B200_TRACE): [n_units][2] start / end %globaltimer of each unit
     // TMA descriptors (2-D, rows x pitch, boxes of kRB rows): the wave workspace with 136- and
     // 128-column boxes, w, the snapshots being read and the image; and the first row of each
     // wavefield of this step inside the wave workspace / of this step's snapshot
@@ -133,7 +137,7 @@ constexpr int kRB = 4;        // rows per TMA box / ring block (>= H)
 constexpr int kRowU = 136;    // a ring row of u / py: 4-column halo | 128 own columns | 4-column halo
 constexpr int kRowO = 128;    // a ring row of everything else
 constexpr int kBlkU = kRB * kRowU, kBlkO = kRB * kRowO;   // floats per ring block
-constexpr int kDOInt = 3;     // ring depth (blocks in flight) of interior segments
+__host__ __device__ constexpr int do_int(int MODE) { return MODE == 2 ? 2 : 3; }   // ring depth (blocks in flight) of interior segments
 constexpr int kDOBand = 1;    // ring depth of top/bottom band segments
 constexpr int kBarFloats = 32;  // 8 mbarriers at the head of the warp's region (keeps blocks 128-byte aligned)
 
@@ -151,8 +155,9 @@ __host__ __device__ constexpr int side_ring_floats(int MODE) {
     return (kDOSide + 2) * (kSideBlkU + kSideBlkO) + kDOSide * (n_ops(MODE) * kSideBlkO + kSideBlkU);
 }
 __host__ __device__ constexpr int cmax_i(int a, int b) { return a > b ? a : b; }
+constexpr int kWRing = 2 * kBlkO;   // w = v^2 dt^2 blocks (L2 resident: one block of lead is enough), own mbarriers 6, 7
 __host__ __device__ constexpr int warp_smem_floats(int MODE) {
-    return kBarFloats + cmax_i(cmax_i(ring_floats(MODE, false, kDOInt), ring_floats(MODE, true, kDOBand)),
+    return kBarFloats + kWRing + cmax_i(cmax_i(ring_floats(MODE, false, do_int(MODE)), ring_floats(MODE, true, kDOBand)),
                                side_ring_floats(MODE));
 }
 
@@ -191,8 +196,8 @@ __device__ __forceinline__ void inject(const StepParams &p, const int s, float *
 // MODE 0: advance only.  MODE 1: advance and write q (forward with gradient).
 // MODE 2: read q, accumulate the image, advance (adjoint with model gradient).
 template <int H, int MODE, bool PML, int DO>
-__device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, float *sm, const unsigned bar0,
-                                           unsigned &phase) {
+__device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, float *sm, float *WR,
+                                           const unsigned bar0, unsigned &phase) {
     static_assert(H <= kRB, "a ring block must hold the stencil half width");
     constexpr int RB = kRB;
     constexpr int DUB = DO + 1, DPB = DO + 2;
@@ -240,6 +245,8 @@ __device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, f
             tma_g2s(PZ + kBlkO, &p.tm_wave_o, x0, p.row_pz + srow + zb + H - RB, barP);
         }
         for (int j = 0; j < DO && j < nblk; ++j) issue(zb + j * RB, j, (j + 1) % DUB, (j + 2) % DPB);
+        mbar_expect_tx(bar0 + 8u * 6, 4u * kBlkO);
+        tma_g2s(WR, &p.tm_w, x0, zb, bar0 + 8u * 6);
     }
 
     // sliding window: inside iteration block b (first centre row z0), W[i] = u row z0 - H + i
@@ -249,11 +256,6 @@ __device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, f
     F4 sy;
 #pragma unroll
     for (int j = 0; j < 4; ++j) sy.a[j] = PML ? __ldg(p.sigy + colL + j) : 0.f;
-    // w = v^2 dt^2 is shared by all shots and stays in L2: plain loads, one block ahead
-    const int zlast = p.ze - 1;
-    F4 wc[RB];
-#pragma unroll
-    for (int r = 0; r < RB; ++r) wc[r] = ld_nc(p.w + (size_t)min(zb + r, zlast) * p.pitch + colL);
     mbar_wait(barP, (phase >> DO) & 1u);
     phase ^= 1u << DO;
 #pragma unroll
@@ -265,8 +267,18 @@ __device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, f
     int sp0 = 0, sp1 = 1, sp2 = 2 % DPB;   // pz slots of blocks b, b + 1, b + 2
     for (int b = 0; b < nblk; ++b) {
         const int z0 = zb + b * RB;
+        // w of the next block goes to the other half of its two-block ring (its last reader was
+        // iteration b - 1), on its own barrier
+        const int wsl = b & 1;
+        if (lane == 0 && b + 1 < nblk) {
+            const unsigned wbar = bar0 + 8u * (6 + (wsl ^ 1));
+            mbar_expect_tx(wbar, 4u * kBlkO);
+            tma_g2s(WR + (wsl ^ 1) * kBlkO, &p.tm_w, x0, z0 + RB, wbar);
+        }
         mbar_wait(bar0 + 8u * so, (phase >> so) & 1u);
         phase ^= 1u << so;
+        mbar_wait(bar0 + 8u * (6 + wsl), (phase >> (6 + wsl)) & 1u);
+        phase ^= 1u << (6 + wsl);
 #pragma unroll
         for (int k = 0; k < 2 * H; ++k) W[k] = W[k + RB];
 #pragma unroll
@@ -290,7 +302,7 @@ __device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, f
 #pragma unroll
                 for (int q = 0; q < 4; ++q) v[4 + q] = W[r + H].a[q];
                 const float *o = OPS + so * NOPS * kBlkO + r * kRowO + 4 * lane;
-                const F4 cM = lds4(o), cW = wc[r];
+                const F4 cM = lds4(o), cW = lds4(WR + wsl * kBlkO + r * kRowO + 4 * lane);
 
                 F4 lap;
 #pragma unroll
@@ -375,10 +387,6 @@ __device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, f
         // ---- refill: the slots this iteration block has finished with take block b + DO ----
         __syncwarp();
         if (lane == 0 && b + DO < nblk) issue(z0 + DO * RB, so, su_prev, sp0);
-        if (b + 1 < nblk) {
-#pragma unroll
-            for (int r = 0; r < RB; ++r) wc[r] = ld_nc(p.w + (size_t)min(z0 + RB + r, zlast) * p.pitch + colL);
-        }
         if (++so == DO) so = 0;
         su_prev = su;
         if (++su == DUB) su = 0;
@@ -555,8 +563,8 @@ __device__ __forceinline__ void march_side(const StepParams &p, const Seg &sg, f
     __syncwarp();
 }
 
-template <int H, int MODE, int OCC>
-__global__ void __launch_bounds__(kNW * 32, OCC) acoustic_step_kernel(const __grid_constant__ StepParams p) {
+template <int H, int MODE>
+__global__ void __launch_bounds__(warps_per_cta(MODE) * 32, ctas_per_sm(MODE)) acoustic_step_kernel(const __grid_constant__ StepParams p) {
     extern __shared__ __align__(128) float smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
@@ -572,43 +580,61 @@ __global__ void __launch_bounds__(kNW * 32, OCC) acoustic_step_kernel(const __gr
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
+    // everything that does not depend on the previous step is fetched before the wait: the warp's
+    // unit, its first segment, the cell of its first sampling item
+    // consecutive units share a CTA: PML units (listed first) end up grouped on the same SMs, which
+    // measured faster than mixing them with interior units (their shallow rings lose the competition)
+    const int unit = blockIdx.x * warps_per_cta(MODE) + warp;
+    int g0 = 0, g1 = 0;
+    if (unit < p.n_units) { g0 = __ldg(p.unit_start + unit); g1 = __ldg(p.unit_start + unit + 1); }
+    int4 sa = make_int4(0, 0, 0, 0), sb4 = sa;
+    if (g0 < g1) {
+        sa = __ldg(reinterpret_cast<const int4 *>(p.segs + g0));
+        sb4 = __ldg(reinterpret_cast<const int4 *>(p.segs + g0) + 1);
+    }
+    const int total_smp = p.S * p.n_smp;
+    const int item0 = blockIdx.x * blockDim.x + tid;
+    int cell0 = 0;
+    if (item0 < total_smp) cell0 = __ldg(p.smp_cell + item0);
     __syncwarp();
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
     // ---- sampling duty: record the current field at the sampling cells (before the step) ----
-    {
-        const int total = p.S * p.n_smp;
-        for (int item = blockIdx.x * (kNW * 32) + tid; item < total; item += gridDim.x * (kNW * 32)) {
-            const int s = item / p.n_smp;
-            const int cell = __ldg(p.smp_cell + item);
-            float val = __ldg(p.u + (size_t)s * p.stride + cell);
-            if (p.smp_div_a) {
-                const int z = cell / p.pitch, y = cell - z * p.pitch;
-                const float hs = p.hdt * (__ldg(p.sigz + z) + __ldg(p.sigy + y));
-                val = val * (1.0f + hs);
-            }
-            p.smp_out[item] = val;
+    for (int item = item0; item < total_smp; item += gridDim.x * blockDim.x) {
+        const int s = item / p.n_smp;
+        const int cell = item == item0 ? cell0 : __ldg(p.smp_cell + item);
+        float val = __ldg(p.u + (size_t)s * p.stride + cell);
+        if (p.smp_div_a) {
+            const int z = cell / p.pitch, y = cell - z * p.pitch;
+            const float hs = p.hdt * (__ldg(p.sigz + z) + __ldg(p.sigy + y));
+            val = val * (1.0f + hs);
         }
+        p.smp_out[item] = val;
     }
-
-    const int unit = blockIdx.x * kNW + warp;
-    if (unit >= p.n_units) return;
-    const int g0 = __ldg(p.unit_start + unit), g1 = __ldg(p.unit_start + unit + 1);
     if (g0 >= g1) return;
 
+    unsigned long long t_start = 0;
+    if (p.trace) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
     unsigned phase = 0;
-    float *ring = wsm + kBarFloats;
+    float *const wring = wsm + kBarFloats;
+    float *const ring = wring + kWRing;
     for (int g = g0; g < g1; ++g) {
-        Seg sg;
-        {
-            const int4 a = __ldg(reinterpret_cast<const int4 *>(p.segs + g));
-            const int4 b = __ldg(reinterpret_cast<const int4 *>(p.segs + g) + 1);
-            sg.s = a.x; sg.x0 = a.y; sg.zb = a.z; sg.ze = a.w;
-            sg.type = b.x; sg.cmin = b.y; sg.cmax = b.z; sg.pad = 0;
+        if (g > g0) {
+            sa = __ldg(reinterpret_cast<const int4 *>(p.segs + g));
+            sb4 = __ldg(reinterpret_cast<const int4 *>(p.segs + g) + 1);
         }
-        if (sg.type == kSegInt) march_ring<H, MODE, false, kDOInt>(p, sg, ring, bar0, phase);
-        else if (sg.type == kSegBand) march_ring<H, MODE, true, kDOBand>(p, sg, ring, bar0, phase);
+        Seg sg;
+        sg.s = sa.x; sg.x0 = sa.y; sg.zb = sa.z; sg.ze = sa.w;
+        sg.type = sb4.x; sg.cmin = sb4.y; sg.cmax = sb4.z; sg.pad = 0;
+        if (sg.type == kSegInt) march_ring<H, MODE, false, do_int(MODE)>(p, sg, ring, wring, bar0, phase);
+        else if (sg.type == kSegBand) march_ring<H, MODE, true, kDOBand>(p, sg, ring, wring, bar0, phase);
         else march_side<H, MODE>(p, sg, ring, bar0, phase);
+    }
+    if (p.trace && lane == 0) {
+        unsigned long long t_end;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+        p.trace[2 * unit] = t_start;
+        p.trace[2 * unit + 1] = t_end;
     }
 }
 
@@ -740,11 +766,13 @@ struct CostModel {
     double rate(int type) const { return type == kSegInt ? 1.0 : (type == kSegBand ? band : side); }
 };
 
-CostModel cost_model(const Geom &g) {
+// Relative costs measured on B200 with the per-unit trace (FWI_B200_TRACE): a band row takes
+// 3.0x (forward) / 3.4x (adjoint) the time of an interior row, a side-strip row about 1.0x.
+CostModel cost_model(const Geom &g, int mode = 1) {
     CostModel c;
-    c.band = env_dbl("FWI_B200_COST_BAND", 2.5);   // cost of a band row relative to an interior row
-    c.side = env_dbl("FWI_B200_COST_SIDE", 1.5);   // cost of one row of a side segment (4 rows per iteration)
-    c.seg = env_dbl("FWI_B200_COST_SEG", 6.0);     // prologue of a segment, in interior rows
+    c.band = env_dbl("FWI_B200_COST_BAND", mode == 2 ? 3.4 : 3.0);   // cost of a band row relative to an interior row
+    c.side = env_dbl("FWI_B200_COST_SIDE", 1.0);   // cost of one row of a side segment
+    c.seg = env_dbl("FWI_B200_COST_SEG", mode == 2 ? 9.0 : 6.0);     // prologue of a segment, in interior rows
     c.min_rows = env_int("FWI_B200_MINROWS", 4);
     if (g.max_rows > 0) c.min_rows = std::min(c.min_rows, g.max_rows);
     if (c.min_rows < 1) c.min_rows = 1;
@@ -792,8 +820,8 @@ int fill_units(const std::vector<Col> &cols, const Geom &g, const CostModel &cm,
 // smallest unit capacity for which a contiguous fill of the (row-chunk major) column list needs no
 // more than n_units units (bisection).
 void build_units(const fwi_acoustic_desc *d, const Geom &g, int n_units, std::vector<Col> &cols,
-                 std::vector<Seg> &segs, std::vector<int> &unit_start) {
-    const CostModel cm = cost_model(g);
+                 std::vector<Seg> &segs, std::vector<int> &unit_start, int mode = 1) {
+    const CostModel cm = cost_model(g, mode);
     list_columns(d, g, cols);
     double total = 0;
     for (const Col &c : cols) total += (c.z1 - c.z0) * cm.rate(c.type) + cm.seg;
@@ -857,7 +885,7 @@ int make_map(CUtensorMap *tm, const float *base, int64_t rows, int pitch, int bo
 
 template <int H, int MODE>
 struct Launcher {
-    static constexpr int kOcc = MODE == 2 ? 2 : 3;   // resident CTAs per SM the register budget is cut for
+    static constexpr int kNW = warps_per_cta(MODE);
     static constexpr size_t smem_bytes() { return (size_t)kNW * warp_smem_floats(MODE) * sizeof(float); }
     // resident CTAs per SM of this kernel on the current device (cached per device)
     static int resident_ctas(int *sms) {
@@ -865,7 +893,7 @@ struct Launcher {
         int dev = 0;
         cudaGetDevice(&dev);
         if (dev != cached_dev) {
-            auto kern = acoustic_step_kernel<H, MODE, kOcc>;
+            auto kern = acoustic_step_kernel<H, MODE>;
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes());
             int occ = 0;
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kNW * 32, smem_bytes());
@@ -888,7 +916,7 @@ struct Launcher {
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr;
         cfg.numAttrs = pdl ? 1 : 0;
-        return cudaLaunchKernelEx(&cfg, acoustic_step_kernel<H, MODE, kOcc>, p);
+        return cudaLaunchKernelEx(&cfg, acoustic_step_kernel<H, MODE>, p);
     }
 };
 
@@ -998,13 +1026,14 @@ extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_b
                        cudaGetErrorString(cudaGetLastError()));
         return FWI_ERR_CUDA;
     }
+    const int kNW = warps_per_cta(mode);
     int n_units = std::min(kMaxUnits, sms * occ * kNW);
     const int units_env = env_int("FWI_B200_UNITS", 0);
     if (units_env > 0) n_units = std::min(kMaxUnits, units_env);
     thread_local std::vector<Col> cols;
     thread_local std::vector<Seg> segs;
     thread_local std::vector<int> unit_start;
-    build_units(d, g, n_units, cols, segs, unit_start);
+    build_units(d, g, n_units, cols, segs, unit_start, mode);
     list_columns(d, g, cols);
     n_units = (int)unit_start.size() - 1;
     FWI_CHECK_ARG((int64_t)segs.size() <= max_segments(cols, g), "internal: work table overflow");
@@ -1069,7 +1098,14 @@ extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_b
     float *pz = nullptr, *pzn = nullptr, *py = nullptr, *pyn = nullptr;
     if (d->pml_width > 0) { pz = b->wave + 2 * fld; pzn = b->wave + 3 * fld; py = b->wave + 4 * fld; pyn = b->wave + 5 * fld; }
 
-    // the sampling duty needs enough threads even when the stencil work is tiny
+    // dev aid: per-unit start / end times of the last launch, dumped to the file named by FWI_B200_TRACE
+    static const char *trace_path = getenv("FWI_B200_TRACE");
+    p.trace = nullptr;
+    if (trace_path) {
+        static unsigned long long *d_trace = nullptr;
+        if (!d_trace) cudaMalloc(&d_trace, 2 * sizeof(unsigned long long) * kMaxUnits);
+        p.trace = d_trace;
+    }
     int blocks = ceil_div(n_units, kNW);
     for (int it = 0; it < d->nsteps; ++it) {
         const int n = d->adjoint ? d->nsteps - 1 - it : it;
@@ -1096,6 +1132,28 @@ extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_b
         float *t = u; u = um; um = t;
         t = pz; pz = pzn; pzn = t;
         t = py; py = pyn; pyn = t;
+    }
+    if (p.trace) {
+        std::vector<unsigned long long> tr(2 * (size_t)n_units);
+        cudaStreamSynchronize(st);
+        cudaMemcpy(tr.data(), p.trace, tr.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+        if (FILE *f = fopen(trace_path, mode == 2 ? "a" : "w")) {
+            unsigned long long t0 = ~0ull;
+            for (int k = 0; k < n_units; ++k) t0 = std::min(t0, tr[2 * k]);
+            const CostModel cm = cost_model(g, mode);
+            for (int k = 0; k < n_units; ++k) {
+                int ni = 0, nb = 0, ns = 0;
+                double cost = 0;
+                for (int q = unit_start[k]; q < unit_start[k + 1]; ++q) {
+                    const int rows = segs[q].ze - segs[q].zb;
+                    (segs[q].type == kSegInt ? ni : segs[q].type == kSegBand ? nb : ns) += rows;
+                    cost += rows * cm.rate(segs[q].type) + cm.seg;
+                }
+                fprintf(f, "%d %d %llu %llu %d %d %d %d %.1f\n", mode, k, tr[2 * k] - t0, tr[2 * k + 1] - t0,
+                        unit_start[k + 1] - unit_start[k], ni, nb, ns, cost);
+            }
+            fclose(f);
+        }
     }
     return FWI_OK;
 }
