@@ -39,11 +39,16 @@ WORKLOADS = {
     "c2": dict(nz=751, ny=2301, dx=4.0, order=8, pml=20, nt=3000, dt=4e-4, freq=15.0, n_rec=576,
                rec_stride=4, z_acq=2, survey_shots=256, vmin=1500.0, vmax=4200.0),
     # BASELINE.json configs[0] (the reference's own CPU-runnable case) - parity-test sized
+    # BASELINE.json configs[2]: elastic-Marmousi-sized vp / vs / rho (the AutoElFullRho path), explosive sources,
+    # two-component receivers; vs = vp / sqrt(3) with a 24-row water layer, rho = 310 vp^0.25 (Gardner)
+    "c3": dict(nz=376, ny=1151, dx=10.0, order=4, pml=10, nt=3000, dt=1e-3, freq=8.0, n_rec=370, rec_stride=3,
+               z_acq=4, survey_shots=128, vmin=1500.0, vmax=4200.0, elastic=True),
     "c1": dict(nz=100, ny=300, dx=10.0, order=4, pml=10, nt=1000, dt=1e-3, freq=15.0, n_rec=101,
                rec_stride=3, z_acq=0, survey_shots=10, vmin=1500.0, vmax=3500.0),
 }
 
 B_FWD, B_ADJ = 20.0, 28.0   # algorithmic bytes per cell-update at k = 1: 16 + 4 / 16 + 4 + 8
+B_FWD_EL, B_ADJ_EL = 80.0, 120.0   # elastic: 60 + 5*4 snapshot write / 60 + 5*4 read + 5*8 image RMW
 
 
 def synth_model(w, seed=1):
@@ -208,7 +213,7 @@ def run_reference(args, w):
 
 
 def bench_config(w, batch, world, name):
-    return {"workload": f"{name}: 2-D acoustic {w['nz']}x{w['ny']} dx={w['dx']}m order {w['order']} "
+    return {"workload": f"{name}: 2-D {'elastic P-SV' if w.get('elastic') else 'acoustic'} {w['nz']}x{w['ny']} dx={w['dx']}m order {w['order']} "
                         f"pml {w['pml']} nt {w['nt']} dt {w['dt']} {w['freq']}Hz Ricker, "
                         f"{w['n_rec']} receivers/shot, fwd+adjoint gradient (MSE), snapshot every step",
             "shots_per_gpu_per_step": batch, "shots_per_step": batch * world,
@@ -265,7 +270,7 @@ def main():
     nz, ny, nt = w["nz"], w["ny"], w["nt"]
     # shots per step: one q snapshot per inner step per shot must fit HBM next to the wavefields
     P = w["pml"] + w["order"] // 2
-    per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nt + 8)
+    per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nt + 8) * (5 if w.get("elastic") else 1)
     free, _ = torch.cuda.mem_get_info(dev)
     batch = args.shots or max(1, min(6, int(0.88 * free // per_shot)))
 
@@ -273,7 +278,8 @@ def main():
     x_s_h, x_r_h = synth_survey(w, batch, first_shot=rank * batch)
     src_h = ricker(w["freq"], nt, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1).repeat(1, batch, 1).contiguous().pin_memory()
     gen = torch.Generator().manual_seed(2 + rank)
-    obs_h = torch.randn(nt, batch, w["n_rec"], generator=gen).mul_(1e-3).pin_memory()   # "observed" data
+    obs_shape = (2, nt, batch, w["n_rec"]) if w.get("elastic") else (nt, batch, w["n_rec"])
+    obs_h = torch.randn(*obs_shape, generator=gen).mul_(1e-3).pin_memory()   # "observed" data
     x_s_h, x_r_h = x_s_h.pin_memory(), x_r_h.pin_memory()
     grad_h = torch.empty(nz, ny).pin_memory()
     loss_h = torch.empty(1).pin_memory()
@@ -281,7 +287,14 @@ def main():
     def gradient(v_d, src_d, xs_d, xr_d, obs_d):
         """The call sequence of the reference (models/networks.py:5449,5464,5476,5491)."""
         v_d = v_d.detach().requires_grad_(True)
-        prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"])
+        if w.get("elastic"):
+            vs_d = v_d.detach() / math.sqrt(3.0)
+            vs_d[:24] = 0.0
+            rho_d = 310.0 * v_d.detach() ** 0.25
+            prop = pkg.Propagator({"vp": v_d, "vs": vs_d, "rho": rho_d}, w["dx"], pml_width=w["pml"],
+                                  accuracy=w["order"], vpmax=w["vmax"])
+        else:
+            prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"])
         rec = prop(src_d, xs_d, xr_d, w["dt"])
         loss = 0.5 * ((rec - obs_d) ** 2).sum()
         loss.backward()
@@ -335,8 +348,8 @@ def main():
     launches = pkg.kernel_launches() - n0
     loops = _lib.LOOP_TIMES
     _lib.LOOP_TIMES = None
-    t_fwd = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag == "acoustic_fwd"]
-    t_adj = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag == "acoustic_adj"]
+    t_fwd = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag.endswith("_fwd")]
+    t_adj = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag.endswith("_adj")]
     ms_fwd, ms_adj = sum(t_fwd) / len(t_fwd), sum(t_adj) / len(t_adj)      # ms per launch
 
     cells = nz * ny
@@ -356,13 +369,16 @@ def main():
     if rank == 0:
         peak, peak_src = hbm_peak()
         unit_launch = cells * batch                   # cell-updates one launch performs
-        ach_f = unit_launch * B_FWD / (ms_fwd * 1e-3) / 1e9
-        ach_a = unit_launch * B_ADJ / (ms_adj * 1e-3) / 1e9
-        ach = unit_launch * (B_FWD + B_ADJ) / ((ms_fwd + ms_adj) * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": "acoustic_step_kernel (forward MODE 1 + adjoint MODE 2 pair)",
+        bf, ba = (B_FWD_EL, B_ADJ_EL) if w.get("elastic") else (B_FWD, B_ADJ)
+        ach_f = unit_launch * bf / (ms_fwd * 1e-3) / 1e9
+        ach_a = unit_launch * ba / (ms_adj * 1e-3) / 1e9
+        ach = unit_launch * (bf + ba) / ((ms_fwd + ms_adj) * 1e-3) / 1e9
+        kname = ("elastic step (f1 + f2 forward, b2a + b2b + b1a + b1b adjoint; one time step = one 'launch')"
+                 if w.get("elastic") else "acoustic_step_kernel (forward MODE 1 + adjoint MODE 2 pair)")
+        roof = {"bound": "hbm", "kernel": kname,
                 "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
                 "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_cell_update": {"forward": B_FWD, "adjoint": B_ADJ},
+                "algorithmic_bytes_per_cell_update": {"forward": bf, "adjoint": ba},
                 "forward": {"ms_per_launch": round(ms_fwd, 5), "achieved": round(ach_f, 1), "frac": round(ach_f / peak, 4)},
                 "adjoint": {"ms_per_launch": round(ms_adj, 5), "achieved": round(ach_a, 1), "frac": round(ach_a / peak, 4)},
                 "kernel_share_of_step": round((ms_fwd + ms_adj) * nt * args.steps / ms, 4)}
@@ -378,7 +394,7 @@ def main():
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": bench_config(w, batch, world, args.workload), "roofline": roof,
                 "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}
-        if world == 1 and not args.no_cpu:
+        if world == 1 and not args.no_cpu and not w.get("elastic"):
             line["cpu_baseline"] = cpu_baseline(w)
         print(json.dumps(line), flush=True)
     if world > 1:

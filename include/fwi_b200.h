@@ -109,6 +109,45 @@ int fwi_acoustic_run(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *
 int fwi_acoustic_forward(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);
 int fwi_acoustic_backward(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);
 
+/* ---- elastic (2-D P-SV, velocity-stress staggered grid, C-PML) -------------------------- */
+/* Replaces what the reference reaches through pyapi_denise: Denise.grad(model, src, rec)
+ * (models/networks.py:9173) = elastic forward + adjoint + correlation, gradients read back at
+ * :9185-9188.  Scheme: oracle/elastic_ref.py.  Arrays are plain row-major [nzp][nyp] (no pitch). */
+
+typedef struct fwi_elastic_desc {
+    int32_t nzp, nyp;         /* padded grid extents (z slow, y fast) */
+    int32_t order;            /* staggered-grid accuracy: 2, 4, 6 or 8 */
+    int32_t pml_width;        /* cells of C-PML on each side (0 = none) */
+    int32_t n_shots;
+    int32_t nsteps;           /* inner time steps */
+    int32_t n_src;            /* explosive sources per shot */
+    int32_t n_rec;            /* two-component receivers per shot */
+    double dz, dy, dt;
+} fwi_elastic_desc;
+
+typedef struct fwi_elastic_buffers {
+    const float *l2m, *lam, *mu, *by, *bz; /* [nzp][nyp] lambda+2mu, lambda at (i,j); mu at (i+1/2,j+1/2);
+                                 buoyancy at (i,j+1/2) and (i+1/2,j) */
+    const float *prof_z;      /* [4][nzp] C-PML a, b at integer nodes, a, b at half nodes, along z */
+    const float *prof_y;      /* [4][nyp] likewise along y */
+    float *wave;              /* [13][n_shots][nzp][nyp], zero on entry: vy vz sxx szz syz psi0..7
+                                 (backward: their adjoint variables) */
+    const int32_t *src_cell;  /* [n_shots][n_src] cell = z*nyp + y */
+    const float *src_amp;     /* [nsteps][n_shots][n_src] (forward) */
+    const int32_t *rec_cell;  /* [n_shots][n_rec] */
+    float *rec_out;           /* [2][nsteps][n_shots][n_rec]: vy, vz recorded before each step (forward) */
+    float *snap;              /* [nsteps][5][n_shots][nzp][nyp] fy fz e1 e2 e3: written by forward when not
+                                 NULL, read by backward */
+    float *scratch;           /* [4][n_shots][nzp][nyp] zero on entry (backward) */
+    float *grad;              /* [5][n_shots][nzp][nyp] zero on entry: images for l2m lam mu by bz (backward) */
+    const float *grad_rec;    /* [2][nsteps][n_shots][n_rec] dJ/d(rec_out) (backward) */
+    float *grad_src;          /* [nsteps][n_shots][n_src] dJ/d(src_amp) (backward) */
+} fwi_elastic_buffers;
+
+int64_t fwi_elastic_wave_floats(const fwi_elastic_desc *desc);   /* floats in `wave`; -1 on a bad descriptor */
+int fwi_elastic_forward(const fwi_elastic_desc *desc, const fwi_elastic_buffers *buf, void *stream);
+int fwi_elastic_backward(const fwi_elastic_desc *desc, const fwi_elastic_buffers *buf, void *stream);
+
 /* ---- common ---------------------------------------------------------------------------- */
 
 const char *fwi_last_error(void);     /* thread-local, never NULL */

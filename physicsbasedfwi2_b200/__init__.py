@@ -7,6 +7,16 @@ sm_100a CUDA behind the C ABI in include/fwi_b200.h; there is no CPU fallback.
 """
 from . import wavelets  # noqa: F401
 from . import scalar  # noqa: F401
+from . import elastic  # noqa: F401
 from ._lib import build, kernel_launches, lib  # noqa: F401
 
-__all__ = ["scalar", "wavelets", "build", "lib", "kernel_launches"]
+
+def Propagator(model: dict, dx, *args, **kwargs):
+    """``Propagator({'vp'[, 'vs', 'rho']}, dx)``: the scalar (acoustic) propagator for a ``{'vp'}``
+    model, the elastic one when ``'vs'`` and ``'rho'`` are given too."""
+    if isinstance(model, dict) and ("vs" in model or "rho" in model):
+        return elastic.Propagator(model, dx, *args, **kwargs)
+    return scalar.Propagator(model, dx, *args, **kwargs)
+
+
+__all__ = ["scalar", "elastic", "wavelets", "Propagator", "build", "lib", "kernel_launches"]

@@ -40,6 +40,18 @@ class AcousticBuffers(C.Structure):
                 ("image", C.c_void_p), ("unit_table", C.c_void_p)]
 
 
+class ElasticDesc(C.Structure):
+    _fields_ = [("nzp", C.c_int32), ("nyp", C.c_int32), ("order", C.c_int32), ("pml_width", C.c_int32),
+                ("n_shots", C.c_int32), ("nsteps", C.c_int32), ("n_src", C.c_int32), ("n_rec", C.c_int32),
+                ("dz", C.c_double), ("dy", C.c_double), ("dt", C.c_double)]
+
+
+class ElasticBuffers(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("l2m", "lam", "mu", "by", "bz", "prof_z", "prof_y", "wave", "src_cell",
+                                          "src_amp", "rec_cell", "rec_out", "snap", "scratch", "grad", "grad_rec",
+                                          "grad_src")]
+
+
 def sources():
     return [os.path.join(_CSRC, s) for s in _SOURCES if os.path.exists(os.path.join(_CSRC, s))]
 
@@ -90,6 +102,11 @@ def lib() -> C.CDLL:
     L.fwi_acoustic_get_layout.argtypes = [C.POINTER(AcousticDesc), C.POINTER(AcousticLayout)]
     for name in ("fwi_acoustic_run", "fwi_acoustic_forward", "fwi_acoustic_backward"):
         getattr(L, name).argtypes = [C.POINTER(AcousticDesc), C.POINTER(AcousticBuffers), C.c_void_p]
+        getattr(L, name).restype = C.c_int
+    L.fwi_elastic_wave_floats.argtypes = [C.POINTER(ElasticDesc)]
+    L.fwi_elastic_wave_floats.restype = C.c_int64
+    for name in ("fwi_elastic_forward", "fwi_elastic_backward"):
+        getattr(L, name).argtypes = [C.POINTER(ElasticDesc), C.POINTER(ElasticBuffers), C.c_void_p]
         getattr(L, name).restype = C.c_int
     _lib = L
     return L

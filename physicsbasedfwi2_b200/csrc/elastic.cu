@@ -1,0 +1,354 @@
+// 2-D P-SV elastic velocity-stress propagator (staggered grid, C-PML) for sm_100a: forward and
+// exact discrete adjoint.
+//
+// Replaces what the reference reaches through pyapi_denise.Denise.grad(model, src, rec)
+// (reference models/networks.py:9173, gradients read back at :9185-9188): the elastic forward
+// modelling, the adjoint modelling and the correlation into gradients.  DENISE does this on CPUs
+// with MPI and files; here one call advances all shots of a batch on the GPU, tensors in / tensors
+// out.  Scheme and notation: oracle/elastic_ref.py (the CPU restatement the tests check against).
+//
+// Fields per shot on the padded grid [nzp][nyp]: vy, vz, sxx, szz, syz and eight C-PML memory
+// variables (one per spatial derivative).  A time step is two kernels, F1 (velocities from stress
+// derivatives) and F2 (stresses from velocity derivatives): each reads only fields the other one
+// writes, so both update in place.  With `snap` the forward pass stores the five fields the
+// imaging condition needs (fy, fz: the force terms; e1, e2, e3: the strain rates).
+// The adjoint of a step is four kernels: B2a / B1a are pointwise (adjoint of the parameter
+// multiplications and of the memory-variable recursions, imaging sums, and the fields Y that the
+// transposed difference operators act on), B2b / B1b gather (D+)^T = -D-, (D-)^T = -D+ of Y.
+// One thread per cell; these kernels are HBM/L2 bound and use no tensor cores.
+#include "common.h"
+
+namespace {
+
+struct EParams {
+    int nzp, nyp, S, h, pml;
+    long long cells;            // nzp * nyp
+    float dt;
+    float cz[4], cy[4];         // staggered coefficients c_k / dz, c_k / dy
+    const float *l2m, *lam, *mu, *by, *bz;
+    const float *pz, *py;       // profiles [4][nzp] / [4][nyp]: a, b at integer nodes, a, b at half nodes
+    float *f[13];               // vy vz sxx szz syz psi0..psi7 (adjoint pass: their adjoints)
+    float *snap;                // this step's [5][S][cells]: fy fz e1 e2 e3 (NULL: not stored / read)
+    float *scratch;             // [4][S][cells]
+    float *grad;                // [5][S][cells]: l2m lam mu by bz images
+};
+
+constexpr int VY = 0, VZ = 1, SXX = 2, SZZ = 3, SYZ = 4, PSI = 5;
+
+template <int H>
+__device__ __forceinline__ float dplus(const float *f, long long i, long long st, const float *c) {
+    float s = c[0] * (__ldg(f + i + st) - __ldg(f + i));
+#pragma unroll
+    for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (__ldg(f + i + k * st) - __ldg(f + i - (k - 1) * st));
+    return s;
+}
+template <int H>
+__device__ __forceinline__ float dminus(const float *f, long long i, long long st, const float *c) {
+    float s = c[0] * (__ldg(f + i) - __ldg(f + i - st));
+#pragma unroll
+    for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (__ldg(f + i + (k - 1) * st) - __ldg(f + i - k * st));
+    return s;
+}
+
+#define ELASTIC_CELL()                                                              \
+    const int j = blockIdx.x * blockDim.x + threadIdx.x + p.h;                      \
+    const int i = blockIdx.y * blockDim.y + threadIdx.y + p.h;                      \
+    const int s = blockIdx.z;                                                       \
+    if (i >= p.nzp - p.h || j >= p.nyp - p.h) return;                               \
+    const long long c0 = (long long)i * p.nyp + j;                                  \
+    const long long o = (long long)s * p.cells + c0;                                \
+    const long long fs = (long long)p.S * p.cells;                                  \
+    const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1); \
+    const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1); \
+    (void)fs; (void)ypml; (void)zpml;
+
+// profile accessors: row 0 a, 1 b (integer nodes), 2 a, 3 b (half nodes)
+#define AZ(i) __ldg(p.pz + (i))
+#define BZ(i) __ldg(p.pz + p.nzp + (i))
+#define AZH(i) __ldg(p.pz + 2 * p.nzp + (i))
+#define BZH(i) __ldg(p.pz + 3 * p.nzp + (i))
+#define AY(j) __ldg(p.py + (j))
+#define BY(j) __ldg(p.py + p.nyp + (j))
+#define AYH(j) __ldg(p.py + 2 * p.nyp + (j))
+#define BYH(j) __ldg(p.py + 3 * p.nyp + (j))
+
+// ---- forward ------------------------------------------------------------------------------
+template <int H, bool SAVE>
+__global__ void __launch_bounds__(256) elastic_f1(const EParams p) {
+    ELASTIC_CELL();
+    const float *sxx = p.f[SXX] + (long long)s * p.cells, *szz = p.f[SZZ] + (long long)s * p.cells,
+                *syz = p.f[SYZ] + (long long)s * p.cells;
+    float d1 = dplus<H>(sxx, c0, 1, p.cy), d2 = dminus<H>(syz, c0, p.nyp, p.cz);
+    float d3 = dminus<H>(syz, c0, 1, p.cy), d4 = dplus<H>(szz, c0, p.nyp, p.cz);
+    if (ypml) {
+        float q0 = BYH(j) * p.f[PSI + 0][o] + AYH(j) * d1; p.f[PSI + 0][o] = q0; d1 = d1 + q0;
+        float q2 = BY(j) * p.f[PSI + 2][o] + AY(j) * d3; p.f[PSI + 2][o] = q2; d3 = d3 + q2;
+    }
+    if (zpml) {
+        float q1 = BZ(i) * p.f[PSI + 1][o] + AZ(i) * d2; p.f[PSI + 1][o] = q1; d2 = d2 + q1;
+        float q3 = BZH(i) * p.f[PSI + 3][o] + AZH(i) * d4; p.f[PSI + 3][o] = q3; d4 = d4 + q3;
+    }
+    const float fy = d1 + d2, fz = d3 + d4;
+    p.f[VY][o] = p.f[VY][o] + (p.dt * __ldg(p.by + c0)) * fy;
+    p.f[VZ][o] = p.f[VZ][o] + (p.dt * __ldg(p.bz + c0)) * fz;
+    if (SAVE) {
+        __stcs(p.snap + o, fy);
+        __stcs(p.snap + fs + o, fz);
+    }
+}
+
+template <int H, bool SAVE>
+__global__ void __launch_bounds__(256) elastic_f2(const EParams p) {
+    ELASTIC_CELL();
+    const float *vy = p.f[VY] + (long long)s * p.cells, *vz = p.f[VZ] + (long long)s * p.cells;
+    float d5 = dminus<H>(vy, c0, 1, p.cy), d6 = dminus<H>(vz, c0, p.nyp, p.cz);
+    float d7 = dplus<H>(vy, c0, p.nyp, p.cz), d8 = dplus<H>(vz, c0, 1, p.cy);
+    if (ypml) {
+        float q4 = BY(j) * p.f[PSI + 4][o] + AY(j) * d5; p.f[PSI + 4][o] = q4; d5 = d5 + q4;
+        float q7 = BYH(j) * p.f[PSI + 7][o] + AYH(j) * d8; p.f[PSI + 7][o] = q7; d8 = d8 + q7;
+    }
+    if (zpml) {
+        float q5 = BZ(i) * p.f[PSI + 5][o] + AZ(i) * d6; p.f[PSI + 5][o] = q5; d6 = d6 + q5;
+        float q6 = BZH(i) * p.f[PSI + 6][o] + AZH(i) * d7; p.f[PSI + 6][o] = q6; d7 = d7 + q6;
+    }
+    const float e1 = d5, e2 = d6, e3 = d7 + d8;
+    const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
+    p.f[SXX][o] = p.f[SXX][o] + p.dt * (l2m * e1 + lam * e2);
+    p.f[SZZ][o] = p.f[SZZ][o] + p.dt * (lam * e1 + l2m * e2);
+    p.f[SYZ][o] = p.f[SYZ][o] + (p.dt * mu) * e3;
+    if (SAVE) {
+        __stcs(p.snap + 2 * fs + o, e1);
+        __stcs(p.snap + 3 * fs + o, e2);
+        __stcs(p.snap + 4 * fs + o, e3);
+    }
+}
+
+// ---- adjoint ------------------------------------------------------------------------------
+// adjoint of F2, pointwise part (stress nodes)
+__global__ void __launch_bounds__(256) elastic_b2a(const EParams p) {
+    ELASTIC_CELL();
+    const float asxx = p.f[SXX][o], aszz = p.f[SZZ][o], asyz = p.f[SYZ][o];
+    const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
+    const float ae1 = p.dt * (l2m * asxx + lam * aszz), ae2 = p.dt * (lam * asxx + l2m * aszz), ae3 = (p.dt * mu) * asyz;
+    const float e1 = __ldcs(p.snap + 2 * fs + o), e2 = __ldcs(p.snap + 3 * fs + o), e3 = __ldcs(p.snap + 4 * fs + o);
+    p.grad[o] = p.grad[o] + p.dt * (asxx * e1 + aszz * e2);
+    p.grad[fs + o] = p.grad[fs + o] + p.dt * (asxx * e2 + aszz * e1);
+    p.grad[2 * fs + o] = p.grad[2 * fs + o] + p.dt * (asyz * e3);
+    float y1 = ae1, y2 = ae2, y3 = ae3, y4 = ae3;
+    if (ypml) {
+        const float x4 = ae1 + p.f[PSI + 4][o]; p.f[PSI + 4][o] = BY(j) * x4; y1 = ae1 + AY(j) * x4;
+        const float x7 = ae3 + p.f[PSI + 7][o]; p.f[PSI + 7][o] = BYH(j) * x7; y4 = ae3 + AYH(j) * x7;
+    }
+    if (zpml) {
+        const float x5 = ae2 + p.f[PSI + 5][o]; p.f[PSI + 5][o] = BZ(i) * x5; y2 = ae2 + AZ(i) * x5;
+        const float x6 = ae3 + p.f[PSI + 6][o]; p.f[PSI + 6][o] = BZH(i) * x6; y3 = ae3 + AZH(i) * x6;
+    }
+    p.scratch[o] = y1;
+    p.scratch[fs + o] = y2;
+    p.scratch[2 * fs + o] = y3;
+    p.scratch[3 * fs + o] = y4;
+}
+
+// adjoint of F2, transposed differences (velocity nodes):
+//   avy += (D-y)^T Y1 + (D+z)^T Y3 = -D+y Y1 - D-z Y3;  avz += -D+z Y2 - D-y Y4
+template <int H>
+__global__ void __launch_bounds__(256) elastic_b2b(const EParams p) {
+    ELASTIC_CELL();
+    const float *y1 = p.scratch + (long long)s * p.cells, *y2 = y1 + fs, *y3 = y2 + fs, *y4 = y3 + fs;
+    p.f[VY][o] = p.f[VY][o] - (dplus<H>(y1, c0, 1, p.cy) + dminus<H>(y3, c0, p.nyp, p.cz));
+    p.f[VZ][o] = p.f[VZ][o] - (dplus<H>(y2, c0, p.nyp, p.cz) + dminus<H>(y4, c0, 1, p.cy));
+}
+
+// adjoint of F1, pointwise part (velocity nodes)
+__global__ void __launch_bounds__(256) elastic_b1a(const EParams p) {
+    ELASTIC_CELL();
+    const float avy = p.f[VY][o], avz = p.f[VZ][o];
+    const float agy = (p.dt * __ldg(p.by + c0)) * avy, agz = (p.dt * __ldg(p.bz + c0)) * avz;
+    const float fy = __ldcs(p.snap + o), fz = __ldcs(p.snap + fs + o);
+    p.grad[3 * fs + o] = p.grad[3 * fs + o] + p.dt * (avy * fy);
+    p.grad[4 * fs + o] = p.grad[4 * fs + o] + p.dt * (avz * fz);
+    float y1 = agy, y2 = agy, y3 = agz, y4 = agz;
+    if (ypml) {
+        const float x0 = agy + p.f[PSI + 0][o]; p.f[PSI + 0][o] = BYH(j) * x0; y1 = agy + AYH(j) * x0;
+        const float x2 = agz + p.f[PSI + 2][o]; p.f[PSI + 2][o] = BY(j) * x2; y3 = agz + AY(j) * x2;
+    }
+    if (zpml) {
+        const float x1 = agy + p.f[PSI + 1][o]; p.f[PSI + 1][o] = BZ(i) * x1; y2 = agy + AZ(i) * x1;
+        const float x3 = agz + p.f[PSI + 3][o]; p.f[PSI + 3][o] = BZH(i) * x3; y4 = agz + AZH(i) * x3;
+    }
+    p.scratch[o] = y1;
+    p.scratch[fs + o] = y2;
+    p.scratch[2 * fs + o] = y3;
+    p.scratch[3 * fs + o] = y4;
+}
+
+// adjoint of F1, transposed differences (stress nodes):
+//   asxx += (D+y)^T Y1 = -D-y Y1;  asyz += (D-z)^T Y2 + (D-y)^T Y3 = -D+z Y2 - D+y Y3;  aszz += -D-z Y4
+template <int H>
+__global__ void __launch_bounds__(256) elastic_b1b(const EParams p) {
+    ELASTIC_CELL();
+    const float *y1 = p.scratch + (long long)s * p.cells, *y2 = y1 + fs, *y3 = y2 + fs, *y4 = y3 + fs;
+    p.f[SXX][o] = p.f[SXX][o] - dminus<H>(y1, c0, 1, p.cy);
+    p.f[SYZ][o] = p.f[SYZ][o] - (dplus<H>(y2, c0, p.nyp, p.cz) + dplus<H>(y3, c0, 1, p.cy));
+    p.f[SZZ][o] = p.f[SZZ][o] - dminus<H>(y4, c0, p.nyp, p.cz);
+}
+
+// ---- point kernels: one thread per shot walks that shot's list (fixed order: deterministic) ----
+// out[k][s][r] = field_k[s][cell[s][r]] for k = 0 (a) and 1 (b), scaled
+__global__ void elastic_sample2(const float *a, const float *b, long long cells, int S, int n, const int *cell,
+                                float *out_a, float *out_b, float scale) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S * n) return;
+    const int s = t / n;
+    const long long c = (long long)s * cells + __ldg(cell + t);
+    out_a[t] = scale * a[c];
+    if (out_b) out_b[t] = scale * b[c];
+}
+// sum-sample: out[s][r] = scale * (a + b)[cell]
+__global__ void elastic_sample_sum(const float *a, const float *b, long long cells, int S, int n, const int *cell,
+                                   float *out, float scale) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S * n) return;
+    const int s = t / n;
+    const long long c = (long long)s * cells + __ldg(cell + t);
+    out[t] = scale * (a[c] + b[c]);
+}
+// a[cell] += scale * amp_a, b[cell] += scale * amp_b
+__global__ void elastic_inject2(float *a, float *b, long long cells, int S, int n, const int *cell,
+                                const float *amp_a, const float *amp_b, float scale) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    for (int r = 0; r < n; ++r) {
+        const long long c = (long long)s * cells + __ldg(cell + s * n + r);
+        a[c] = a[c] + scale * __ldg(amp_a + s * n + r);
+        b[c] = b[c] + scale * __ldg(amp_b + s * n + r);
+    }
+}
+
+int check(const fwi_elastic_desc *d) {
+    FWI_CHECK_ARG(d != nullptr, "descriptor is NULL");
+    FWI_CHECK_ARG(d->order == 2 || d->order == 4 || d->order == 6 || d->order == 8,
+                  "order must be 2, 4, 6 or 8 (got %d)", d->order);
+    const int h = d->order / 2;
+    FWI_CHECK_ARG(d->pml_width >= 0, "pml_width must be >= 0");
+    FWI_CHECK_ARG(d->nzp > 2 * (h + d->pml_width) && d->nyp > 2 * (h + d->pml_width), "padded grid %dx%d too small",
+                  d->nzp, d->nyp);
+    FWI_CHECK_ARG(d->n_shots >= 1 && d->nsteps >= 0 && d->n_src >= 0 && d->n_rec >= 0, "bad counts");
+    FWI_CHECK_ARG(d->dz > 0 && d->dy > 0 && d->dt != 0, "dz, dy must be > 0 and dt != 0");
+    return FWI_OK;
+}
+
+const double kStag[5][4] = {{0, 0, 0, 0},
+                            {1.0, 0, 0, 0},
+                            {9.0 / 8.0, -1.0 / 24.0, 0, 0},
+                            {75.0 / 64.0, -25.0 / 384.0, 3.0 / 640.0, 0},
+                            {1225.0 / 1024.0, -245.0 / 3072.0, 49.0 / 5120.0, -5.0 / 7168.0}};
+
+void fill(EParams &p, const fwi_elastic_desc *d, const fwi_elastic_buffers *b) {
+    p.nzp = d->nzp; p.nyp = d->nyp; p.S = d->n_shots; p.h = d->order / 2; p.pml = d->pml_width;
+    p.cells = (long long)d->nzp * d->nyp;
+    p.dt = (float)d->dt;
+    for (int k = 0; k < 4; ++k) {
+        p.cz[k] = (float)(kStag[p.h][k] * (1.0 / d->dz));
+        p.cy[k] = (float)(kStag[p.h][k] * (1.0 / d->dy));
+    }
+    p.l2m = b->l2m; p.lam = b->lam; p.mu = b->mu; p.by = b->by; p.bz = b->bz;
+    p.pz = b->prof_z; p.py = b->prof_y;
+    const long long fld = (long long)d->n_shots * p.cells;
+    for (int k = 0; k < 13; ++k) p.f[k] = b->wave + k * fld;
+    p.scratch = b->scratch; p.grad = b->grad; p.snap = nullptr;
+}
+
+#define ELASTIC_LAUNCH_H(kern, ...)                                      \
+    switch (p.h) {                                                       \
+    case 1: kern<1, ##__VA_ARGS__><<<grid, block, 0, st>>>(p); break;    \
+    case 2: kern<2, ##__VA_ARGS__><<<grid, block, 0, st>>>(p); break;    \
+    case 3: kern<3, ##__VA_ARGS__><<<grid, block, 0, st>>>(p); break;    \
+    default: kern<4, ##__VA_ARGS__><<<grid, block, 0, st>>>(p); break;   \
+    }
+
+}  // namespace
+
+extern "C" int64_t fwi_elastic_wave_floats(const fwi_elastic_desc *d) {
+    if (check(d) != FWI_OK) return -1;
+    return 13ll * d->n_shots * d->nzp * d->nyp;
+}
+
+extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_buffers *b, void *stream) {
+    int rc = check(d);
+    if (rc != FWI_OK) return rc;
+    FWI_CHECK_ARG(b && b->l2m && b->lam && b->mu && b->by && b->bz && b->prof_z && b->prof_y && b->wave,
+                  "parameter grids, profiles and wave workspace must not be NULL");
+    FWI_CHECK_ARG(d->n_src == 0 || (b->src_cell && b->src_amp), "src_cell/src_amp required when n_src > 0");
+    FWI_CHECK_ARG(d->n_rec == 0 || (b->rec_cell && b->rec_out), "rec_cell/rec_out required when n_rec > 0");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    EParams p;
+    fill(p, d, b);
+    const dim3 block(32, 8);
+    const dim3 grid((d->nyp - 2 * p.h + 31) / 32, (d->nzp - 2 * p.h + 7) / 8, d->n_shots);
+    const long long fld = (long long)d->n_shots * p.cells;
+    const long long nrec = (long long)d->n_shots * d->n_rec, nsrc = (long long)d->n_shots * d->n_src;
+    for (int n = 0; n < d->nsteps; ++n) {
+        if (d->n_rec) {
+            elastic_sample2<<<(unsigned)((nrec + 127) / 128), 128, 0, st>>>(
+                p.f[VY], p.f[VZ], p.cells, d->n_shots, d->n_rec, b->rec_cell, b->rec_out + n * nrec,
+                b->rec_out + ((long long)d->nsteps + n) * nrec, 1.0f);
+            fwi::count_launch();
+        }
+        p.snap = b->snap ? b->snap + (long long)n * 5 * fld : nullptr;
+        if (p.snap) {
+            ELASTIC_LAUNCH_H(elastic_f1, true);
+            ELASTIC_LAUNCH_H(elastic_f2, true);
+        } else {
+            ELASTIC_LAUNCH_H(elastic_f1, false);
+            ELASTIC_LAUNCH_H(elastic_f2, false);
+        }
+        fwi::count_launch(2);
+        if (d->n_src) {
+            elastic_inject2<<<(d->n_shots + 63) / 64, 64, 0, st>>>(p.f[SXX], p.f[SZZ], p.cells, d->n_shots, d->n_src,
+                                                                  b->src_cell, b->src_amp + n * nsrc,
+                                                                  b->src_amp + n * nsrc, p.dt);
+            fwi::count_launch();
+        }
+        FWI_CHECK_CUDA(cudaGetLastError());
+    }
+    return FWI_OK;
+}
+
+extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic_buffers *b, void *stream) {
+    int rc = check(d);
+    if (rc != FWI_OK) return rc;
+    FWI_CHECK_ARG(b && b->l2m && b->lam && b->mu && b->by && b->bz && b->prof_z && b->prof_y && b->wave,
+                  "parameter grids, profiles and wave workspace must not be NULL");
+    FWI_CHECK_ARG(b->snap && b->scratch && b->grad, "snap, scratch and grad are required by the adjoint pass");
+    FWI_CHECK_ARG(d->n_rec == 0 || (b->rec_cell && b->grad_rec), "rec_cell/grad_rec required when n_rec > 0");
+    FWI_CHECK_ARG(d->n_src == 0 || (b->src_cell && b->grad_src), "src_cell/grad_src required when n_src > 0");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    EParams p;
+    fill(p, d, b);
+    const dim3 block(32, 8);
+    const dim3 grid((d->nyp - 2 * p.h + 31) / 32, (d->nzp - 2 * p.h + 7) / 8, d->n_shots);
+    const long long fld = (long long)d->n_shots * p.cells;
+    const long long nrec = (long long)d->n_shots * d->n_rec, nsrc = (long long)d->n_shots * d->n_src;
+    for (int n = d->nsteps - 1; n >= 0; --n) {
+        if (d->n_src) {
+            elastic_sample_sum<<<(unsigned)((nsrc + 127) / 128), 128, 0, st>>>(
+                p.f[SXX], p.f[SZZ], p.cells, d->n_shots, d->n_src, b->src_cell, b->grad_src + n * nsrc, p.dt);
+            fwi::count_launch();
+        }
+        p.snap = const_cast<float *>(b->snap) + (long long)n * 5 * fld;
+        elastic_b2a<<<grid, block, 0, st>>>(p);
+        ELASTIC_LAUNCH_H(elastic_b2b);
+        elastic_b1a<<<grid, block, 0, st>>>(p);
+        ELASTIC_LAUNCH_H(elastic_b1b);
+        fwi::count_launch(4);
+        if (d->n_rec) {
+            elastic_inject2<<<(d->n_shots + 63) / 64, 64, 0, st>>>(
+                p.f[VY], p.f[VZ], p.cells, d->n_shots, d->n_rec, b->rec_cell, b->grad_rec + n * nrec,
+                b->grad_rec + ((long long)d->nsteps + n) * nrec, 1.0f);
+            fwi::count_launch();
+        }
+        FWI_CHECK_CUDA(cudaGetLastError());
+    }
+    return FWI_OK;
+}

@@ -1,0 +1,219 @@
+"""Elastic (2-D P-SV, vp / vs / rho) propagator on the B200 kernels, behind the deepwave-style call.
+
+The reference computes its elastic gradients with the external C/MPI code DENISE through files and
+``mpirun`` (``d.grad(model_init, src, rec)`` models/networks.py:9173, gradients read back at
+:9185-9188, consumed by ``fake_Vp.backward(vp_grad)`` / ``fake_Vs.backward(vs_grad)``
+models/AutoElFullRhoMar22_model.py:438,445).  Here the same physics (velocity-stress staggered grid,
+C-PML, explosive sources, two-component receivers) is a ``torch.autograd.Function``:
+
+    prop = Propagator({'vp': vp, 'vs': vs, 'rho': rho}, dx)
+    rec = prop(source_amplitudes, x_s, x_r, dt)        # [2, nt, shots, receivers]: v_y, v_z
+    loss(rec, ...).backward()                            # -> vp.grad, vs.grad, rho.grad, src.grad
+
+The time loops run in libfwi_b200.so (fwi_elastic_forward / fwi_elastic_backward); the chain rule
+from the five effective-parameter grids to (vp, vs, rho) is plain torch autograd.  No CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import _host as H
+from . import _lib
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def cpml_profiles(n_pad: int, h: int, pml_width: int, d: float, dt: float, vmax: float, pml_freq: float) -> torch.Tensor:
+    """[4, n_pad] float32 (CPU): a, b at integer nodes, a, b at half nodes (Komatitsch-Martin
+    recursive-convolution coefficients, quadratic damping ramp, linear alpha ramp)."""
+    out = torch.zeros(4, n_pad, dtype=torch.float64)
+    out[1] = 1.0
+    out[3] = 1.0
+    if pml_width > 0:
+        for row, half in ((0, 0.0), (2, 0.5)):
+            pos = torch.arange(n_pad, dtype=torch.float64) + half
+            lo = (h + pml_width) - pos
+            hi = pos - (n_pad - h - pml_width - 1)
+            depth = torch.clamp(torch.maximum(lo, hi), min=0.0, max=float(pml_width)) / pml_width
+            d0 = 3.0 * vmax * math.log(1000.0) / (2.0 * pml_width * d)
+            dd = d0 * depth ** 2
+            alpha = math.pi * pml_freq * (1.0 - depth)
+            b = torch.exp(-(dd + alpha) * dt)
+            out[row] = torch.where(dd > 0, dd / (dd + alpha).clamp_min(1e-30) * (b - 1.0), torch.zeros_like(b))
+            out[row + 1] = b
+    return out.float()
+
+
+def effective_parameters(vp_pad, vs_pad, rho_pad):
+    """(l2m, lam, mu_yz, by, bz) on the padded grid; differentiable torch ops."""
+    mu = rho_pad * vs_pad * vs_pad
+    l2m = rho_pad * vp_pad * vp_pad
+    lam = l2m - 2.0 * mu
+
+    def sh(x, dz, dy):
+        if dz:
+            x = torch.cat([x[1:], x[-1:]], 0)
+        if dy:
+            x = torch.cat([x[:, 1:], x[:, -1:]], 1)
+        return x
+    m00, m10, m01, m11 = mu, sh(mu, 1, 0), sh(mu, 0, 1), sh(mu, 1, 1)
+    ok = (m00 > 0) & (m10 > 0) & (m01 > 0) & (m11 > 0)
+    one = torch.ones_like(mu)
+    inv = (1.0 / torch.where(ok, m00, one) + 1.0 / torch.where(ok, m10, one) + 1.0 / torch.where(ok, m01, one)
+           + 1.0 / torch.where(ok, m11, one))
+    mu_yz = torch.where(ok, 4.0 / inv, torch.zeros_like(mu))
+    by = 2.0 / (rho_pad + sh(rho_pad, 0, 1))
+    bz = 2.0 / (rho_pad + sh(rho_pad, 1, 0))
+    return l2m, lam, mu_yz, by, bz
+
+
+class _ElasticFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, vp, vs, rho, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, pml_freq, loc_mode):
+        for name, t in (("vp", vp), ("vs", vs), ("rho", rho)):
+            if t.dim() != 2 or t.shape != vp.shape:
+                raise RuntimeError(f"model['{name}'] must be 2-D with the shape of model['vp']")
+            if not t.is_cuda:
+                raise RuntimeError(f"model['{name}'] must be a CUDA tensor: this propagator has no CPU path")
+            if t.dtype != torch.float32:
+                raise RuntimeError(f"model['{name}'] must be float32, got {t.dtype}")
+        if order not in (2, 4, 6, 8):
+            raise RuntimeError(f"accuracy must be 2, 4, 6 or 8, got {order}")
+        if source_amplitudes.dim() != 3:
+            raise RuntimeError("source_amplitudes must be [nt, n_shots, n_sources_per_shot]")
+        nt, S, Ns = source_amplitudes.shape
+        if x_s.dim() != 3 or tuple(x_s.shape) != (S, Ns, 2):
+            raise RuntimeError(f"source_locations must be [{S}, {Ns}, 2], got {tuple(x_s.shape)}")
+        if x_r.dim() != 3 or x_r.shape[0] != S or x_r.shape[2] != 2:
+            raise RuntimeError(f"receiver_locations must be [{S}, n_receivers, 2], got {tuple(x_r.shape)}")
+        R = int(x_r.shape[1])
+        dev = vp.device
+        dz, dy = H.spacing(dx)
+        nz, ny = int(vp.shape[0]), int(vp.shape[1])
+        h, pw = order // 2, int(pml_width)
+        P = pw + h
+        nzp, nyp = nz + 2 * P, ny + 2 * P
+        vmax = float(vpmax) if vpmax is not None else float(vp.detach().abs().max())
+        ratio, dti = H.inner_step(float(dt), dz, dy, vmax)
+        nti = nt * ratio
+
+        def pad(x):
+            return F.pad(x.detach()[None, None], (P,) * 4, mode="replicate")[0, 0]
+        params = [t.contiguous() for t in effective_parameters(pad(vp), pad(vs), pad(rho))]
+        prof_z = cpml_profiles(nzp, h, pw, dz, dti, vmax, pml_freq).to(dev).contiguous()
+        prof_y = cpml_profiles(nyp, h, pw, dy, dti, vmax, pml_freq).to(dev).contiguous()
+
+        def cells(x):
+            c = H.to_cells(x.to(dev), dz, dy, loc_mode)
+            bad = ((c[..., 0] < 0) | (c[..., 0] >= nz) | (c[..., 1] < 0) | (c[..., 1] >= ny)).any()
+            return ((c[..., 0] + P) * nyp + (c[..., 1] + P)).to(torch.int32).contiguous(), bad
+        s_cell, bad_s = cells(x_s)
+        r_cell, bad_r = cells(x_r)
+        if bool((bad_s | bad_r).item()):
+            raise RuntimeError("source/receiver location outside the model")
+        amp = H.resample_up(source_amplitudes.detach().to(dev, torch.float32), ratio).contiguous()
+
+        need_model = any(ctx.needs_input_grad[:3])
+        need_any = need_model or ctx.needs_input_grad[3]
+        desc = _lib.ElasticDesc(nzp, nyp, order, pw, S, nti, Ns, R, dz, dy, dti)
+        L = _lib.lib()
+        n_wave = int(L.fwi_elastic_wave_floats(C.byref(desc)))
+        wave = torch.zeros(n_wave, dtype=torch.float32, device=dev)
+        rec = torch.empty(2, nti, S, R, dtype=torch.float32, device=dev)
+        snap = torch.empty(nti * 5 * S * nzp * nyp, dtype=torch.float32, device=dev) if need_any else None
+        b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
+                                _ptr(amp), _ptr(r_cell), _ptr(rec), _ptr(snap), None, None, None, None)
+        cur = torch.cuda.current_stream(dev)
+        with torch.cuda.device(dev):
+            ev = _lib.time_loop_begin(cur)
+            _lib.check(L.fwi_elastic_forward(C.byref(desc), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_forward")
+            _lib.time_loop_end(cur, ev, "elastic_fwd", nti)
+        out = rec[:, ::ratio].contiguous() if ratio > 1 else rec
+        ctx.saved = (vp.detach(), vs.detach(), rho.detach(), params, prof_z, prof_y, s_cell, r_cell, snap, desc)
+        ctx.meta = (nt, S, Ns, R, nti, ratio, P, dev)
+        ctx.src_like = source_amplitudes.detach()
+        return out
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, grad_rec):
+        vp, vs, rho, params, prof_z, prof_y, s_cell, r_cell, snap, desc = ctx.saved
+        nt, S, Ns, R, nti, ratio, P, dev = ctx.meta
+        need_model = any(ctx.needs_input_grad[:3])
+        g = grad_rec.to(dev, torch.float32)
+        if ratio > 1:
+            g_in = torch.zeros(2, nti, S, R, dtype=torch.float32, device=dev)
+            g_in[:, ::ratio] = g
+        else:
+            g_in = g.contiguous()
+        L = _lib.lib()
+        cells = desc.nzp * desc.nyp
+        wave = torch.zeros(int(L.fwi_elastic_wave_floats(C.byref(desc))), dtype=torch.float32, device=dev)
+        scratch = torch.zeros(4 * S * cells, dtype=torch.float32, device=dev)
+        grad = torch.zeros(5, S, desc.nzp, desc.nyp, dtype=torch.float32, device=dev)
+        gsrc = torch.zeros(nti, S, Ns, dtype=torch.float32, device=dev)
+        b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
+                                None, _ptr(r_cell), None, _ptr(snap), _ptr(scratch), _ptr(grad), _ptr(g_in), _ptr(gsrc))
+        cur = torch.cuda.current_stream(dev)
+        with torch.cuda.device(dev):
+            ev = _lib.time_loop_begin(cur)
+            _lib.check(L.fwi_elastic_backward(C.byref(desc), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_backward")
+            _lib.time_loop_end(cur, ev, "elastic_adj", nti)
+        gvp = gvs = grho = gs = None
+        if need_model:
+            gpar = grad.sum(1)                       # fixed-order sum over shots
+            with torch.enable_grad():
+                leaves = [t.clone().requires_grad_(True) for t in (vp, vs, rho)]
+                padded = [F.pad(t[None, None], (P,) * 4, mode="replicate")[0, 0] for t in leaves]
+                eff = effective_parameters(*padded)
+                gvp, gvs, grho = torch.autograd.grad(eff, leaves, [gpar[k] for k in range(5)], allow_unused=True)
+        if ctx.needs_input_grad[3]:
+            gs = H.resample_up_adjoint(gsrc, ratio, ctx.src_like.to(dev, torch.float32))
+            gs = gs.to(ctx.src_like.device, ctx.src_like.dtype)
+        ctx.saved = None
+        return (gvp if ctx.needs_input_grad[0] else None, gvs if ctx.needs_input_grad[1] else None,
+                grho if ctx.needs_input_grad[2] else None, gs, None, None, None, None, None, None, None, None, None)
+
+
+class Propagator(torch.nn.Module):
+    """``Propagator({'vp': vp, 'vs': vs, 'rho': rho}, dx)(source_amplitudes, x_s, x_r, dt)``.
+
+    Returns receiver particle velocities ``[2, nt, n_shots, n_receivers]`` (component 0 horizontal
+    v_y, 1 vertical v_z: the ``seis_x`` / ``seis_y`` pair the reference consumes,
+    models/networks.py:9054-9061).  Sources are explosive (equal sxx / szz moment rate).
+    ``pml_width`` (default 10), ``accuracy`` 2/4/6/8 (default 4), ``pml_freq`` (Hz, the frequency the
+    C-PML is tuned to, default 25), ``vpmax``, ``loc_mode`` as in the scalar propagator.
+    """
+
+    def __init__(self, model: dict, dx, pml_width=None, survey_pad=None, vpmax=None, *, accuracy: int = 4,
+                 pml_freq: float = 25.0, loc_mode: str = "trunc"):
+        super().__init__()
+        if not isinstance(model, dict) or not {"vp", "vs", "rho"} <= set(model):
+            raise RuntimeError("model must be a dict with keys 'vp', 'vs' and 'rho'")
+        extra = set(model) - {"vp", "vs", "rho"}
+        if extra:
+            raise RuntimeError(f"unknown model keys {sorted(extra)}")
+        if survey_pad is not None:
+            raise RuntimeError("survey_pad is not supported by the elastic propagator")
+        self.model = model
+        self.dx = dx
+        self.pml_width = 10 if pml_width is None else int(pml_width)
+        if self.pml_width < 0:
+            raise RuntimeError("pml_width must be >= 0")
+        self.vpmax = vpmax
+        self.accuracy = accuracy
+        self.pml_freq = float(pml_freq)
+        self.loc_mode = loc_mode
+
+    def forward(self, source_amplitudes, source_locations, receiver_locations, dt):
+        m = self.model
+        return _ElasticFunction.apply(m["vp"], m["vs"], m["rho"], source_amplitudes, source_locations,
+                                      receiver_locations, float(dt), self.dx, self.accuracy, self.pml_width,
+                                      self.vpmax, self.pml_freq, self.loc_mode)

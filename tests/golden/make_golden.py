@@ -55,5 +55,45 @@ def main():
         print(name, "rec", tuple(rec.shape), float(rec.abs().max()), "grad_v", float(gv.abs().max()))
 
 
+ELASTIC = {
+    # the elastic call shape (vp, vs, rho; explosive source; two-component receivers), incl. a water layer
+    "el_o4_pml6": dict(nz=20, ny=28, dx=10.0, order=4, pml=6, S=2, R=5, nt=50, dt=1e-3, f=20.0),
+    "el_o8_pml5_sub": dict(nz=18, ny=24, dx=10.0, order=8, pml=5, S=1, R=4, nt=30, dt=2.5e-3, f=15.0),
+}
+
+
+def elastic_inputs(c):
+    vp = K.layered_model(c["nz"], c["ny"], seed=4).double()
+    vs = vp / 1.732
+    vs[:3] = 0.0
+    rho = 310.0 * vp ** 0.25
+    g = torch.Generator().manual_seed(11)
+    x_s = torch.zeros(c["S"], 1, 2)
+    x_s[..., 0] = torch.randint(1, c["nz"] - 1, (c["S"], 1), generator=g).float() * c["dx"]
+    x_s[..., 1] = torch.randint(1, c["ny"] - 1, (c["S"], 1), generator=g).float() * c["dx"]
+    x_r = torch.zeros(c["S"], c["R"], 2)
+    x_r[..., 0] = torch.randint(0, c["nz"], (c["S"], c["R"]), generator=g).float() * c["dx"]
+    x_r[..., 1] = torch.randint(0, c["ny"], (c["S"], c["R"]), generator=g).float() * c["dx"]
+    src = (K.ricker(c["f"], c["nt"], c["dt"], 1.0 / c["f"]).reshape(-1, 1, 1).repeat(1, c["S"], 1) * 1e6).double()
+    grad_rec = torch.randn(2, c["nt"], c["S"], c["R"], generator=g).double()
+    return vp, vs, rho, x_s, x_r, src, grad_rec
+
+
+def main_elastic():
+    from oracle import elastic_ref as E
+    here = os.path.dirname(os.path.abspath(__file__))
+    for name, c in ELASTIC.items():
+        vp, vs, rho, x_s, x_r, src, grad_rec = elastic_inputs(c)
+        rec, gvp, gvs, grho, gs = E.elastic_gradient(vp, vs, rho, c["dx"], src, x_s, x_r, c["dt"], grad_rec,
+                                                     order=c["order"], pml_width=c["pml"])
+        np.savez_compressed(
+            os.path.join(here, name + ".npz"), vp=vp.float().numpy(), vs=vs.float().numpy(), rho=rho.float().numpy(),
+            x_s=x_s.numpy(), x_r=x_r.numpy(), src=src.float().numpy(), grad_rec=grad_rec.float().numpy(),
+            dx=np.asarray(c["dx"], dtype=np.float64), dt=c["dt"], order=c["order"], pml=c["pml"], rec=rec.numpy(),
+            grad_vp=gvp.numpy(), grad_vs=gvs.numpy(), grad_rho=grho.numpy(), grad_src=gs.numpy())
+        print(name, "rec", tuple(rec.shape), float(rec.abs().max()), "grad_vp", float(gvp.abs().max()))
+
+
 if __name__ == "__main__":
     main()
+    main_elastic()

@@ -26,6 +26,7 @@ def so():
 def test_header_declares_entry_points():
     syms = _declared_symbols()
     for must in ("fwi_acoustic_get_layout", "fwi_acoustic_forward", "fwi_acoustic_backward",
+                 "fwi_elastic_forward", "fwi_elastic_backward", "fwi_elastic_wave_floats", "fwi_acoustic_plan_stats",
                  "fwi_last_error", "fwi_version", "fwi_kernel_launches", "fwi_device_ok"):
         assert must in syms
 
@@ -62,7 +63,8 @@ def test_layout_is_pure_host_code_and_checks_arguments():
 def test_ctypes_structs_match_header_field_order():
     src = open(os.path.join(ROOT, "include", "fwi_b200.h")).read()
     for struct, cls in (("fwi_acoustic_desc", _lib.AcousticDesc), ("fwi_acoustic_layout", _lib.AcousticLayout),
-                        ("fwi_acoustic_buffers", _lib.AcousticBuffers)):
+                        ("fwi_acoustic_buffers", _lib.AcousticBuffers), ("fwi_elastic_desc", _lib.ElasticDesc),
+                        ("fwi_elastic_buffers", _lib.ElasticBuffers)):
         body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (struct, struct), src, flags=re.S).group(1)
         body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
         names = []

@@ -21,7 +21,7 @@ from oracle import cpu_ref as O
 from oracle import torch_ref as T
 from tests import _cases as K
 
-GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "o*.npz")))
 
 
 def _load(path):
