@@ -133,8 +133,11 @@ typedef struct fwi_elastic_buffers {
     float *wave;              /* [13][n_shots][nzp][nyp], zero on entry: vy vz sxx szz syz psi0..7
                                  (backward: their adjoint variables) */
     const int32_t *src_cell;  /* [n_shots][n_src] cell = z*nyp + y */
+    const int32_t *src_link;  /* [n_shots][n_src] chains of points sharing a cell: bits 0..29 = index of the
+                                 next point of the chain + 1 (0 = last), bit 30 set = not the first of its chain */
     const float *src_amp;     /* [nsteps][n_shots][n_src] (forward) */
     const int32_t *rec_cell;  /* [n_shots][n_rec] */
+    const int32_t *rec_link;  /* [n_shots][n_rec] as src_link (used by the adjoint injection) */
     float *rec_out;           /* [2][nsteps][n_shots][n_rec]: vy, vz recorded before each step (forward) */
     float *snap;              /* [nsteps][5][n_shots][nzp][nyp] fy fz e1 e2 e3: written by forward when not
                                  NULL, read by backward */

@@ -128,3 +128,28 @@ def injection_lists(cells_dev: torch.Tensor, nzp: int, pitch: int):
     cell = cells_dev.reshape(-1)[order].to(torch.int32).contiguous()
     col = (order % n).to(torch.int32).contiguous()
     return start.contiguous(), cell, col
+
+
+def duplicate_links(cells: torch.Tensor) -> torch.Tensor:
+    """Chains the points of each shot that share a cell, for deterministic parallel injection.
+
+    cells [S, n] -> link [S, n] int32: bits 0..29 = index (within the shot) of the next point in the
+    same cell + 1, 0 if none; bit 30 set if the point is not the first of its chain.  Chains follow
+    the original list order (stable sort)."""
+    S, n = cells.shape
+    dev = cells.device
+    if n == 0:
+        return torch.zeros(S, 0, dtype=torch.int32, device=dev)
+    c = cells.long()
+    order = torch.argsort(c, dim=1, stable=True)
+    cs = torch.gather(c, 1, order)
+    same_next = torch.zeros(S, n, dtype=torch.bool, device=dev)
+    same_next[:, :-1] = cs[:, 1:] == cs[:, :-1]
+    same_prev = torch.zeros(S, n, dtype=torch.bool, device=dev)
+    same_prev[:, 1:] = same_next[:, :-1]
+    nxt = torch.zeros(S, n, dtype=torch.long, device=dev)
+    nxt[:, :-1] = order[:, 1:] + 1
+    link_sorted = torch.where(same_next, nxt, torch.zeros_like(nxt)) + same_prev.long() * 0x40000000
+    link = torch.zeros(S, n, dtype=torch.long, device=dev)
+    link.scatter_(1, order, link_sorted)
+    return link.to(torch.int32).contiguous()

@@ -47,8 +47,8 @@ class ElasticDesc(C.Structure):
 
 
 class ElasticBuffers(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in ("l2m", "lam", "mu", "by", "bz", "prof_z", "prof_y", "wave", "src_cell",
-                                          "src_amp", "rec_cell", "rec_out", "snap", "scratch", "grad", "grad_rec",
+    _fields_ = [(n, C.c_void_p) for n in ("l2m", "lam", "mu", "by", "bz", "prof_z", "prof_y", "wave", "src_cell", "src_link",
+                                          "src_amp", "rec_cell", "rec_link", "rec_out", "snap", "scratch", "grad", "grad_rec",
                                           "grad_src")]
 
 

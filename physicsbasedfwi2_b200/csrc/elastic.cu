@@ -213,16 +213,26 @@ __global__ void elastic_sample_sum(const float *a, const float *b, long long cel
     const long long c = (long long)s * cells + __ldg(cell + t);
     out[t] = scale * (a[c] + b[c]);
 }
-// a[cell] += scale * amp_a, b[cell] += scale * amp_b
-__global__ void elastic_inject2(float *a, float *b, long long cells, int S, int n, const int *cell,
+// a[cell] += scale * amp_a, b[cell] += scale * amp_b.  One thread per point; points that share a
+// cell are chained by `link` (bits 0..29: index of the next point in the same cell + 1, 0 = none;
+// bit 30 set: not the first of its chain) and added by the first one in list order: deterministic.
+__global__ void elastic_inject2(float *a, float *b, long long cells, int S, int n, const int *cell, const int *link,
                                 const float *amp_a, const float *amp_b, float scale) {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= S) return;
-    for (int r = 0; r < n; ++r) {
-        const long long c = (long long)s * cells + __ldg(cell + s * n + r);
-        a[c] = a[c] + scale * __ldg(amp_a + s * n + r);
-        b[c] = b[c] + scale * __ldg(amp_b + s * n + r);
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S * n) return;
+    int l = __ldg(link + t);
+    if (l & 0x40000000) return;
+    const int s = t / n;
+    const long long c = (long long)s * cells + __ldg(cell + t);
+    float va = a[c] + scale * __ldg(amp_a + t), vb = b[c] + scale * __ldg(amp_b + t);
+    while ((l & 0x3fffffff) != 0) {
+        const int k = s * n + (l & 0x3fffffff) - 1;
+        va = va + scale * __ldg(amp_a + k);
+        vb = vb + scale * __ldg(amp_b + k);
+        l = __ldg(link + k);
     }
+    a[c] = va;
+    b[c] = vb;
 }
 
 int check(const fwi_elastic_desc *d) {
@@ -279,7 +289,7 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
     if (rc != FWI_OK) return rc;
     FWI_CHECK_ARG(b && b->l2m && b->lam && b->mu && b->by && b->bz && b->prof_z && b->prof_y && b->wave,
                   "parameter grids, profiles and wave workspace must not be NULL");
-    FWI_CHECK_ARG(d->n_src == 0 || (b->src_cell && b->src_amp), "src_cell/src_amp required when n_src > 0");
+    FWI_CHECK_ARG(d->n_src == 0 || (b->src_cell && b->src_link && b->src_amp), "src_cell/src_link/src_amp required when n_src > 0");
     FWI_CHECK_ARG(d->n_rec == 0 || (b->rec_cell && b->rec_out), "rec_cell/rec_out required when n_rec > 0");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     EParams p;
@@ -305,9 +315,9 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
         }
         fwi::count_launch(2);
         if (d->n_src) {
-            elastic_inject2<<<(d->n_shots + 63) / 64, 64, 0, st>>>(p.f[SXX], p.f[SZZ], p.cells, d->n_shots, d->n_src,
-                                                                  b->src_cell, b->src_amp + n * nsrc,
-                                                                  b->src_amp + n * nsrc, p.dt);
+            elastic_inject2<<<(unsigned)((nsrc + 127) / 128), 128, 0, st>>>(
+                p.f[SXX], p.f[SZZ], p.cells, d->n_shots, d->n_src, b->src_cell, b->src_link, b->src_amp + n * nsrc,
+                b->src_amp + n * nsrc, p.dt);
             fwi::count_launch();
         }
         FWI_CHECK_CUDA(cudaGetLastError());
@@ -321,7 +331,7 @@ extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic
     FWI_CHECK_ARG(b && b->l2m && b->lam && b->mu && b->by && b->bz && b->prof_z && b->prof_y && b->wave,
                   "parameter grids, profiles and wave workspace must not be NULL");
     FWI_CHECK_ARG(b->snap && b->scratch && b->grad, "snap, scratch and grad are required by the adjoint pass");
-    FWI_CHECK_ARG(d->n_rec == 0 || (b->rec_cell && b->grad_rec), "rec_cell/grad_rec required when n_rec > 0");
+    FWI_CHECK_ARG(d->n_rec == 0 || (b->rec_cell && b->rec_link && b->grad_rec), "rec_cell/rec_link/grad_rec required when n_rec > 0");
     FWI_CHECK_ARG(d->n_src == 0 || (b->src_cell && b->grad_src), "src_cell/grad_src required when n_src > 0");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     EParams p;
@@ -343,8 +353,8 @@ extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic
         ELASTIC_LAUNCH_H(elastic_b1b);
         fwi::count_launch(4);
         if (d->n_rec) {
-            elastic_inject2<<<(d->n_shots + 63) / 64, 64, 0, st>>>(
-                p.f[VY], p.f[VZ], p.cells, d->n_shots, d->n_rec, b->rec_cell, b->grad_rec + n * nrec,
+            elastic_inject2<<<(unsigned)((nrec + 127) / 128), 128, 0, st>>>(
+                p.f[VY], p.f[VZ], p.cells, d->n_shots, d->n_rec, b->rec_cell, b->rec_link, b->grad_rec + n * nrec,
                 b->grad_rec + ((long long)d->nsteps + n) * nrec, 1.0f);
             fwi::count_launch();
         }

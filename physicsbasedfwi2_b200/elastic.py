@@ -116,6 +116,7 @@ class _ElasticFunction(torch.autograd.Function):
             return ((c[..., 0] + P) * nyp + (c[..., 1] + P)).to(torch.int32).contiguous(), bad
         s_cell, bad_s = cells(x_s)
         r_cell, bad_r = cells(x_r)
+        s_link, r_link = H.duplicate_links(s_cell), H.duplicate_links(r_cell)
         if bool((bad_s | bad_r).item()):
             raise RuntimeError("source/receiver location outside the model")
         amp = H.resample_up(source_amplitudes.detach().to(dev, torch.float32), ratio).contiguous()
@@ -129,14 +130,15 @@ class _ElasticFunction(torch.autograd.Function):
         rec = torch.empty(2, nti, S, R, dtype=torch.float32, device=dev)
         snap = torch.empty(nti * 5 * S * nzp * nyp, dtype=torch.float32, device=dev) if need_any else None
         b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
-                                _ptr(amp), _ptr(r_cell), _ptr(rec), _ptr(snap), None, None, None, None)
+                                _ptr(s_link), _ptr(amp), _ptr(r_cell), _ptr(r_link), _ptr(rec), _ptr(snap), None, None,
+                                None, None)
         cur = torch.cuda.current_stream(dev)
         with torch.cuda.device(dev):
             ev = _lib.time_loop_begin(cur)
             _lib.check(L.fwi_elastic_forward(C.byref(desc), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_forward")
             _lib.time_loop_end(cur, ev, "elastic_fwd", nti)
         out = rec[:, ::ratio].contiguous() if ratio > 1 else rec
-        ctx.saved = (vp.detach(), vs.detach(), rho.detach(), params, prof_z, prof_y, s_cell, r_cell, snap, desc)
+        ctx.saved = (vp.detach(), vs.detach(), rho.detach(), params, prof_z, prof_y, s_cell, r_cell, s_link, r_link, snap, desc)
         ctx.meta = (nt, S, Ns, R, nti, ratio, P, dev)
         ctx.src_like = source_amplitudes.detach()
         return out
@@ -144,7 +146,7 @@ class _ElasticFunction(torch.autograd.Function):
     @staticmethod
     @torch.autograd.function.once_differentiable
     def backward(ctx, grad_rec):
-        vp, vs, rho, params, prof_z, prof_y, s_cell, r_cell, snap, desc = ctx.saved
+        vp, vs, rho, params, prof_z, prof_y, s_cell, r_cell, s_link, r_link, snap, desc = ctx.saved
         nt, S, Ns, R, nti, ratio, P, dev = ctx.meta
         need_model = any(ctx.needs_input_grad[:3])
         g = grad_rec.to(dev, torch.float32)
@@ -160,7 +162,8 @@ class _ElasticFunction(torch.autograd.Function):
         grad = torch.zeros(5, S, desc.nzp, desc.nyp, dtype=torch.float32, device=dev)
         gsrc = torch.zeros(nti, S, Ns, dtype=torch.float32, device=dev)
         b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
-                                None, _ptr(r_cell), None, _ptr(snap), _ptr(scratch), _ptr(grad), _ptr(g_in), _ptr(gsrc))
+                                _ptr(s_link), None, _ptr(r_cell), _ptr(r_link), None, _ptr(snap), _ptr(scratch), _ptr(grad),
+                                _ptr(g_in), _ptr(gsrc))
         cur = torch.cuda.current_stream(dev)
         with torch.cuda.device(dev):
             ev = _lib.time_loop_begin(cur)
