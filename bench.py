@@ -43,6 +43,10 @@ WORKLOADS = {
     # two-component receivers; vs = vp / sqrt(3) with a 24-row water layer, rho = 310 vp^0.25 (Gardner)
     "c3": dict(nz=376, ny=1151, dx=10.0, order=4, pml=10, nt=3000, dt=1e-3, freq=8.0, n_rec=370, rec_stride=3,
                z_acq=4, survey_shots=128, vmin=1500.0, vmax=4200.0, elastic=True),
+    # BASELINE.json configs[3]: SEAM-sized 2-D acoustic slice with wavefield checkpointing (state kept every
+    # 64 steps, snapshots recomputed per segment in the backward pass: one extra forward per gradient)
+    "c4": dict(nz=1501, ny=3501, dx=10.0, order=8, pml=20, nt=4000, dt=1e-3, freq=8.0, n_rec=876, rec_stride=4,
+               z_acq=2, survey_shots=64, vmin=1500.0, vmax=4500.0, ckpt=64),
     "c1": dict(nz=100, ny=300, dx=10.0, order=4, pml=10, nt=1000, dt=1e-3, freq=15.0, n_rec=101,
                rec_stride=3, z_acq=0, survey_shots=10, vmin=1500.0, vmax=3500.0),
 }
@@ -215,7 +219,8 @@ def run_reference(args, w):
 def bench_config(w, batch, world, name):
     return {"workload": f"{name}: 2-D {'elastic P-SV' if w.get('elastic') else 'acoustic'} {w['nz']}x{w['ny']} dx={w['dx']}m order {w['order']} "
                         f"pml {w['pml']} nt {w['nt']} dt {w['dt']} {w['freq']}Hz Ricker, "
-                        f"{w['n_rec']} receivers/shot, fwd+adjoint gradient (MSE), snapshot every step",
+                        f"{w['n_rec']} receivers/shot, fwd+adjoint gradient (MSE), "
+                        + (f"wavefield checkpoint every {w['ckpt']} steps + recompute" if w.get("ckpt") else "snapshot every step"),
             "shots_per_gpu_per_step": batch, "shots_per_step": batch * world,
             "survey_shots": w["survey_shots"], "parallelism": f"shot-parallel x{world}",
             "l2": "working set per launch exceeds L2 (no flush needed)"}
@@ -271,8 +276,10 @@ def main():
     # shots per step: one q snapshot per inner step per shot must fit HBM next to the wavefields
     P = w["pml"] + w["order"] // 2
     per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nt + 8) * (5 if w.get("elastic") else 1)
+    if w.get("ckpt"):
+        per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (6 * (nt // w["ckpt"] + 2) + w["ckpt"] + 24)
     free, _ = torch.cuda.mem_get_info(dev)
-    batch = args.shots or max(1, min(6, int(0.88 * free // per_shot)))
+    batch = args.shots or max(1, min(16 if w.get("ckpt") else 6, int(0.88 * free // per_shot)))
 
     v_host = synth_model(w).pin_memory()
     x_s_h, x_r_h = synth_survey(w, batch, first_shot=rank * batch)
@@ -294,7 +301,8 @@ def main():
             prop = pkg.Propagator({"vp": v_d, "vs": vs_d, "rho": rho_d}, w["dx"], pml_width=w["pml"],
                                   accuracy=w["order"], vpmax=w["vmax"])
         else:
-            prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"])
+            prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"],
+                              checkpoint_every=w.get("ckpt", 0))
         rec = prop(src_d, xs_d, xr_d, w["dt"])
         loss = 0.5 * ((rec - obs_d) ** 2).sum()
         loss.backward()

@@ -84,12 +84,27 @@ class _Plan:
     def lists(self, cell):
         return H.injection_lists(cell, self.nzp, self.pitch)
 
+    def new_wave(self) -> torch.Tensor:
+        return torch.zeros(int(self.lay.wave_fields) * self.S * self.stride, dtype=torch.float32, device=self.dev)
+
+    def settle(self, wave: torch.Tensor, nsteps: int) -> torch.Tensor:
+        """The library starts every call with (u, u-) = fields (0, 1) and rotates the pairs each
+        step: after an odd number of steps put the fields back in that order so that the state
+        can be carried into another call."""
+        if nsteps % 2 == 0:
+            return wave
+        nf = int(self.lay.wave_fields)
+        perm = [1, 0, 3, 2, 5, 4][:nf]
+        return wave.view(nf, -1)[perm].contiguous().view(-1)
+
     def run(self, *, nsteps, adjoint, inj, inj_amp, smp_cell, n_smp, q_write=None, q_read=None,
-            image=None) -> torch.Tensor:
-        """One time loop.  inj = (start, cell, col) lists; returns smp_out [nsteps, S, n_smp]."""
+            image=None, wave=None) -> torch.Tensor:
+        """One time loop.  inj = (start, cell, col) lists; returns smp_out [nsteps, S, n_smp].
+        `wave` carries the state of a previous call (see settle()); None starts from rest."""
         n_inj = 0 if inj_amp is None else int(inj_amp.shape[2])
         d = self.desc(nsteps, adjoint, n_inj, n_smp)
-        wave = torch.zeros(int(self.lay.wave_fields) * self.S * self.stride, dtype=torch.float32, device=self.dev)
+        if wave is None:
+            wave = self.new_wave()
         smp_out = torch.empty(nsteps, self.S, n_smp, dtype=torch.float32, device=self.dev)
         start, icell, icol = inj
         table = torch.empty(int(self.lay.unit_table_bytes), dtype=torch.uint8, device=self.dev)
@@ -109,7 +124,7 @@ class _Plan:
 class _ScalarFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, v, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, loc_mode,
-                chunk_rows):
+                chunk_rows, checkpoint_every=0):
         if source_amplitudes.dim() != 3:
             raise RuntimeError("source_amplitudes must be [nt, n_shots, n_sources_per_shot]")
         nt, S, Ns = source_amplitudes.shape
@@ -129,15 +144,32 @@ class _ScalarFunction(torch.autograd.Function):
         need_v = ctx.needs_input_grad[0]
         need_s = ctx.needs_input_grad[1]
         q = None
-        if need_v:
-            q = torch.empty(nti * S * plan.stride, dtype=torch.float32, device=dev)
         r32 = r_cell.to(torch.int32).contiguous()
-        rec = plan.run(nsteps=nti, adjoint=0, inj=plan.lists(s_cell), inj_amp=amp,
-                       smp_cell=r32, n_smp=R, q_write=q)
+        K = int(checkpoint_every)
+        ctx.ckpt = None
+        if need_v and K > 0 and K < nti:
+            # wavefield checkpointing: keep the state every K steps instead of a snapshot per step;
+            # backward() recomputes the snapshots of one segment at a time
+            wave, ckpts, parts = plan.new_wave(), [], []
+            lists = plan.lists(s_cell)
+            for t0 in range(0, nti, K):
+                n = min(K, nti - t0)
+                ckpts.append(wave.clone())
+                parts.append(plan.run(nsteps=n, adjoint=0, inj=lists, inj_amp=amp[t0:t0 + n], smp_cell=r32,
+                                      n_smp=R, wave=wave))
+                wave = plan.settle(wave, n)
+            rec = torch.cat(parts, 0)
+            ctx.ckpt = (K, ckpts)
+        else:
+            if need_v:
+                q = torch.empty(nti * S * plan.stride, dtype=torch.float32, device=dev)
+            rec = plan.run(nsteps=nti, adjoint=0, inj=plan.lists(s_cell), inj_amp=amp,
+                           smp_cell=r32, n_smp=R, q_write=q)
         out = rec[::plan.ratio].contiguous() if plan.ratio > 1 else rec
         ctx.plan = plan
         ctx.q = q
         ctx.amp = amp if need_v else None
+        ctx.r32 = r32
         ctx.geom = (s_cell, r_cell, r_z, r_y, nt, S, Ns, R, nti)
         ctx.need = (need_v, need_s)
         ctx.src_like = source_amplitudes.detach()
@@ -159,9 +191,25 @@ class _ScalarFunction(torch.autograd.Function):
         image = None
         if need_v:
             image = torch.zeros(int(plan.lay.n_images) * plan.stride, dtype=torch.float32, device=dev)
-        gs = plan.run(nsteps=nti, adjoint=1, inj=plan.lists(r_cell), inj_amp=g_in,
-                      smp_cell=s_cell.to(torch.int32).contiguous(), n_smp=Ns,
-                      q_read=ctx.q if need_v else None, image=image)
+        s32 = s_cell.to(torch.int32).contiguous()
+        if ctx.ckpt is not None:
+            K, ckpts = ctx.ckpt
+            qseg = torch.empty(K * S * plan.stride, dtype=torch.float32, device=dev)
+            awave, parts = plan.new_wave(), []
+            src_lists, rec_lists = plan.lists(s_cell), plan.lists(r_cell)
+            starts = list(range(0, nti, K))
+            for t0 in reversed(starts):
+                n = min(K, nti - t0)
+                plan.run(nsteps=n, adjoint=0, inj=src_lists, inj_amp=ctx.amp[t0:t0 + n], smp_cell=ctx.r32,
+                         n_smp=0, q_write=qseg, wave=ckpts.pop())
+                parts.append(plan.run(nsteps=n, adjoint=1, inj=rec_lists, inj_amp=g_in[t0:t0 + n].contiguous(),
+                                      smp_cell=s32, n_smp=Ns, q_read=qseg, image=image, wave=awave))
+                awave = plan.settle(awave, n)
+            gs = torch.cat(parts[::-1], 0)
+            ctx.ckpt = None
+        else:
+            gs = plan.run(nsteps=nti, adjoint=1, inj=plan.lists(r_cell), inj_amp=g_in, smp_cell=s32, n_smp=Ns,
+                          q_read=ctx.q if need_v else None, image=image)
         grad_v = grad_s = None
         if need_v:
             G = image.view(int(plan.lay.n_images), plan.nzp, plan.pitch).sum(0)
@@ -176,7 +224,7 @@ class _ScalarFunction(torch.autograd.Function):
             grad_s = H.resample_up_adjoint(gs, plan.ratio, ctx.src_like.to(dev, torch.float32))
             grad_s = grad_s.to(ctx.src_like.device, ctx.src_like.dtype)
         ctx.q = None
-        return grad_v, grad_s, None, None, None, None, None, None, None, None, None
+        return grad_v, grad_s, None, None, None, None, None, None, None, None, None, None
 
 
 class Propagator(torch.nn.Module):
@@ -186,11 +234,14 @@ class Propagator(torch.nn.Module):
     key ``'vp'`` holding a float32 CUDA tensor [nz, ny]; ``dx`` a float or (dz, dy).
     ``pml_width`` (int, default 10), ``survey_pad`` (None or cells) and ``vpmax`` as in deepwave.
     Extensions: ``accuracy`` (2/4/6/8, default 4), ``loc_mode`` ('trunc' | 'round'),
-    ``chunk_rows`` (rows per interior work unit, kernel tuning, 0 = auto).
+    ``chunk_rows`` (cap on the rows of one work segment, kernel tuning / tests, 0 = none),
+    ``checkpoint_every`` (K > 0: wavefield checkpointing - the forward pass keeps the state every K
+    inner steps instead of one snapshot per step, and the backward pass recomputes the snapshots
+    of one K-step segment at a time: memory O(nt/K + K) fields instead of O(nt), one extra forward).
     """
 
     def __init__(self, model: dict, dx, pml_width=None, survey_pad=None, vpmax=None, *,
-                 accuracy: int = 4, loc_mode: str = "trunc", chunk_rows: int = 0):
+                 accuracy: int = 4, loc_mode: str = "trunc", chunk_rows: int = 0, checkpoint_every: int = 0):
         super().__init__()
         if not isinstance(model, dict) or "vp" not in model:
             raise RuntimeError("model must be a dict with key 'vp'")
@@ -217,6 +268,9 @@ class Propagator(torch.nn.Module):
         self.accuracy = accuracy
         self.loc_mode = loc_mode
         self.chunk_rows = chunk_rows
+        if checkpoint_every < 0:
+            raise RuntimeError("checkpoint_every must be >= 0")
+        self.checkpoint_every = int(checkpoint_every)
 
     def forward(self, source_amplitudes: torch.Tensor, source_locations: torch.Tensor,
                 receiver_locations: torch.Tensor, dt: float) -> torch.Tensor:
@@ -225,7 +279,7 @@ class Propagator(torch.nn.Module):
         if self.survey_pad is not None:
             v, x_s, x_r = _crop_to_survey(v, self.dx, x_s, x_r, self.survey_pad)
         return _ScalarFunction.apply(v, source_amplitudes, x_s, x_r, float(dt), self.dx, self.accuracy,
-                                     self.pml_width, self.vpmax, self.loc_mode, self.chunk_rows)
+                                     self.pml_width, self.vpmax, self.loc_mode, self.chunk_rows, self.checkpoint_every)
 
 
 def _crop_to_survey(v, dx, x_s, x_r, survey_pad):

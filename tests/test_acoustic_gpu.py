@@ -114,3 +114,27 @@ def test_cuda_matches_committed_golden_vectors(cuda_lib, path):
     assert K.rel_l2(rec, torch.from_numpy(z["rec"])) <= TRACE_TOL
     assert K.rel_l2(vg.grad, torch.from_numpy(z["grad_v"])) <= GRAD_TOL
     assert K.rel_l2(sg.grad, torch.from_numpy(z["grad_src"])) <= GRAD_TOL
+
+
+@pytest.mark.parametrize("K", [14, 7, 33])
+def test_wavefield_checkpointing_reproduces_the_stored_snapshot_gradient(cuda_lib, K):
+    """checkpoint_every=K recomputes the snapshots segment by segment (BASELINE config 4): same
+    kernels, same arithmetic, so traces and gradients must be identical to the k=1 snapshot mode."""
+    from physicsbasedfwi2_b200.scalar import Propagator
+    c = CASES[1]       # 8th order, sub-stepped (ratio 2), two sources per shot
+    from tests import _cases as KK
+    v = KK.layered_model(c["nz"], c["ny"], seed=1)
+    x_s, x_r = KK.survey(c["nz"], c["ny"], c["dx"], c["S"], c["R"], c["Ns"], seed=2, scattered=True)
+    src = KK.ricker(c["f"], c["nt"], c["dt"], 1.0 / c["f"]).reshape(-1, 1, 1).repeat(1, c["S"], c["Ns"]).contiguous()
+    grad_rec = torch.randn(c["nt"], c["S"], c["R"], generator=torch.Generator().manual_seed(3))
+    dev = torch.device("cuda:0")
+    outs = []
+    for ck in (0, K):
+        vg = v.to(dev).requires_grad_(True)
+        sg = src.to(dev).requires_grad_(True)
+        prop = Propagator({"vp": vg}, c["dx"], pml_width=c["pml"], accuracy=c["order"], checkpoint_every=ck)
+        rec = prop(sg, x_s.to(dev), x_r.to(dev), c["dt"])
+        (rec * grad_rec.to(dev)).sum().backward()
+        outs.append((rec.detach(), vg.grad, sg.grad))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
