@@ -279,7 +279,7 @@ def main():
     if w.get("ckpt"):
         per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (6 * (nt // w["ckpt"] + 2) + w["ckpt"] + 24)
     free, _ = torch.cuda.mem_get_info(dev)
-    batch = args.shots or max(1, min(16 if w.get("ckpt") else 6, int(0.88 * free // per_shot)))
+    batch = args.shots or max(1, min(16 if w.get("ckpt") else 6, int((0.6 if w.get("ckpt") else 0.88) * free // per_shot)))
 
     v_host = synth_model(w).pin_memory()
     x_s_h, x_r_h = synth_survey(w, batch, first_shot=rank * batch)
