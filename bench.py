@@ -47,6 +47,10 @@ WORKLOADS = {
     # 64 steps, snapshots recomputed per segment in the backward pass: one extra forward per gradient)
     "c4": dict(nz=1501, ny=3501, dx=10.0, order=8, pml=20, nt=4000, dt=1e-3, freq=8.0, n_rec=876, rec_stride=4,
                z_acq=2, survey_shots=64, vmin=1500.0, vmax=4500.0, ckpt=64),
+    # BASELINE.json configs[3], x-slab variant: every shot is cut into one column slab per GPU, ghost columns
+    # exchanged over NVLink every 8 steps (slab.py); snapshot every step; all ranks work on the SAME shots
+    "c4dd": dict(nz=1501, ny=3501, dx=10.0, order=8, pml=20, nt=4000, dt=1e-3, freq=8.0, n_rec=876, rec_stride=4,
+                 z_acq=2, survey_shots=64, vmin=1500.0, vmax=4500.0, slabs=8),
     "c1": dict(nz=100, ny=300, dx=10.0, order=4, pml=10, nt=1000, dt=1e-3, freq=15.0, n_rec=101,
                rec_stride=3, z_acq=0, survey_shots=10, vmin=1500.0, vmax=3500.0),
 }
@@ -221,8 +225,10 @@ def bench_config(w, batch, world, name):
                         f"pml {w['pml']} nt {w['nt']} dt {w['dt']} {w['freq']}Hz Ricker, "
                         f"{w['n_rec']} receivers/shot, fwd+adjoint gradient (MSE), "
                         + (f"wavefield checkpoint every {w['ckpt']} steps + recompute" if w.get("ckpt") else "snapshot every step"),
-            "shots_per_gpu_per_step": batch, "shots_per_step": batch * world,
-            "survey_shots": w["survey_shots"], "parallelism": f"shot-parallel x{world}",
+            "shots_per_gpu_per_step": batch, "shots_per_step": batch * (1 if w.get("slabs") else world),
+            "survey_shots": w["survey_shots"],
+            "parallelism": (f"x-slab domain decomposition x{world}, ghost exchange every {w['slabs']} steps"
+                            if w.get("slabs") else f"shot-parallel x{world}"),
             "l2": "working set per launch exceeds L2 (no flush needed)"}
 
 
@@ -278,13 +284,16 @@ def main():
     per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nt + 8) * (5 if w.get("elastic") else 1)
     if w.get("ckpt"):
         per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (6 * (nt // w["ckpt"] + 2) + w["ckpt"] + 24)
+    if w.get("slabs"):
+        cols = (ny + 2 * P) // world + 2 * w["slabs"] * (w["order"] // 2) + 64
+        per_shot = (nz + 2 * P) * cols * 4 * (nt + 16)
     free, _ = torch.cuda.mem_get_info(dev)
     batch = args.shots or max(1, min(16 if w.get("ckpt") else 6, int((0.6 if w.get("ckpt") else 0.88) * free // per_shot)))
 
     v_host = synth_model(w).pin_memory()
-    x_s_h, x_r_h = synth_survey(w, batch, first_shot=rank * batch)
+    x_s_h, x_r_h = synth_survey(w, batch, first_shot=0 if w.get("slabs") else rank * batch)
     src_h = ricker(w["freq"], nt, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1).repeat(1, batch, 1).contiguous().pin_memory()
-    gen = torch.Generator().manual_seed(2 + rank)
+    gen = torch.Generator().manual_seed(2 + (0 if w.get("slabs") else rank))
     obs_shape = (2, nt, batch, w["n_rec"]) if w.get("elastic") else (nt, batch, w["n_rec"])
     obs_h = torch.randn(*obs_shape, generator=gen).mul_(1e-3).pin_memory()   # "observed" data
     x_s_h, x_r_h = x_s_h.pin_memory(), x_r_h.pin_memory()
@@ -302,10 +311,13 @@ def main():
                                   accuracy=w["order"], vpmax=w["vmax"])
         else:
             prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"],
-                              checkpoint_every=w.get("ckpt", 0))
+                              checkpoint_every=w.get("ckpt", 0), slabs=bool(w.get("slabs")) and world > 1,
+                              halo_steps=w.get("slabs") or 8)
         rec = prop(src_d, xs_d, xr_d, w["dt"])
         loss = 0.5 * ((rec - obs_d) ** 2).sum()
         loss.backward()
+        if w.get("slabs"):
+            return v_d.grad, loss           # slab mode: traces and gradient are already whole on every rank
         g, l = allreduce_gradient(v_d.grad, loss)
         return g, l
 
@@ -361,7 +373,7 @@ def main():
     ms_fwd, ms_adj = sum(t_fwd) / len(t_fwd), sum(t_adj) / len(t_adj)      # ms per launch
 
     cells = nz * ny
-    work = cells * nt * batch * world * 2            # cell-updates per step, whole job
+    work = cells * nt * batch * (1 if w.get("slabs") else world) * 2   # cell-updates per step, whole job
     value = work * args.steps / (ms * 1e-3) / 1e9
 
     e2e = None
@@ -376,7 +388,7 @@ def main():
 
     if rank == 0:
         peak, peak_src = hbm_peak()
-        unit_launch = cells * batch                   # cell-updates one launch performs
+        unit_launch = cells * batch // (world if w.get("slabs") else 1)   # cell-updates one launch performs
         bf, ba = (B_FWD_EL, B_ADJ_EL) if w.get("elastic") else (B_FWD, B_ADJ)
         ach_f = unit_launch * bf / (ms_fwd * 1e-3) / 1e9
         ach_a = unit_launch * ba / (ms_adj * 1e-3) / 1e9
@@ -398,7 +410,8 @@ def main():
                 pass
         line = {"metric": "FWI gradient Gcell-updates/s (fwd+adjoint)", "value": round(value, 3),
                 "unit": "Gcell-updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak",
+                "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
+                "scaling": "strong" if w.get("slabs") else "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": bench_config(w, batch, world, args.workload), "roofline": roof,
                 "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}

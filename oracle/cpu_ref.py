@@ -47,14 +47,16 @@ def _ptr(a: Optional[np.ndarray]):
 
 def run(np_dtype, nzp, nyp, order, pml_width, S, dz, dy, dt, w, sigz, sigy, nsteps, adjoint,
         inj_cell, inj_amp, inj_scale_a, smp_cell, smp_div_a, q_write=None, q_read=None, G=None,
-        u_final=None):
-    """Thin call of fwi_oracle_acoustic_run_{f32,f64}; returns smp_out [nsteps, S, n_smp]."""
-    f = getattr(lib(), "fwi_oracle_acoustic_run_" + ("f32" if np_dtype == np.float32 else "f64"))
+        u_final=None, state=None):
+    """Thin call of fwi_oracle_acoustic_run[_state]_{f32,f64}; returns smp_out [nsteps, S, n_smp].
+    `state` [6, S, nzp*nyp] (u, u-, pz, -, py, -) is read and left updated when given."""
+    f = getattr(lib(), "fwi_oracle_acoustic_run_" + ("state_" if state is not None else "")
+                + ("f32" if np_dtype == np.float32 else "f64"))
     f.restype = ctypes.c_int
     n_inj = 0 if inj_cell is None else inj_cell.shape[1]
     n_smp = 0 if smp_cell is None else smp_cell.shape[1]
     smp_out = np.zeros((nsteps, S, n_smp), dtype=np_dtype) if n_smp else None
-    for a in (w, sigz, sigy, inj_amp, q_write, q_read, G, u_final):
+    for a in (w, sigz, sigy, inj_amp, q_write, q_read, G, u_final, state):
         assert a is None or (a.dtype == np_dtype and a.flags.c_contiguous)
     for a in (inj_cell, smp_cell):
         assert a is None or (a.dtype == np.int32 and a.flags.c_contiguous)
@@ -63,7 +65,7 @@ def run(np_dtype, nzp, nyp, order, pml_width, S, dz, dy, dt, w, sigz, sigy, nste
            _ptr(w), _ptr(sigz), _ptr(sigy), ctypes.c_int(nsteps), ctypes.c_int(adjoint),
            ctypes.c_int(n_inj), _ptr(inj_cell), _ptr(inj_amp), ctypes.c_int(inj_scale_a),
            ctypes.c_int(n_smp), _ptr(smp_cell), _ptr(smp_out), ctypes.c_int(smp_div_a),
-           _ptr(q_write), _ptr(q_read), _ptr(G), _ptr(u_final))
+           _ptr(q_write), _ptr(q_read), _ptr(G), _ptr(state if state is not None else u_final))
     if rc != 0:
         raise RuntimeError(f"fwi_oracle_acoustic_run failed rc={rc}")
     return smp_out

@@ -78,12 +78,13 @@ static void NAME(row_int)(const NAME(ctx_t) * c, int z, int y0, int y1, const RE
  *  per step n:  smp_out[n] = field[smp_cell] (/a if smp_div_a);   [G += field * q_read[n]];
  *               step (writing q_write[n] if given);   field+[inj_cell] += coef * inj_amp[n].
  *  All arrays use the padded pitch-free layout [.., nzp*nyp].  Returns 0, or 1 on bad args. */
-int NAME(fwi_oracle_acoustic_run)(int nzp, int nyp, int order, int pml_width, int S, double dz,
+static int NAME(acoustic_run_core)(int nzp, int nyp, int order, int pml_width, int S, double dz,
                                   double dy, double dt, const REAL *w, const REAL *sigz,
                                   const REAL *sigy, int nsteps, int adjoint, int n_inj,
                                   const int *inj_cell, const REAL *inj_amp, int inj_scale_a,
                                   int n_smp, const int *smp_cell, REAL *smp_out, int smp_div_a,
-                                  REAL *q_write, const REAL *q_read, REAL *G, REAL *u_final) {
+                                  REAL *q_write, const REAL *q_read, REAL *G, REAL *u_final,
+                                  REAL *state) {
     if (order != 2 && order != 4 && order != 6 && order != 8) return 1;
     const int h = order / 2;
     if (nzp <= 2 * h || nyp <= 2 * h || S < 1 || nsteps < 0) return 1;
@@ -106,6 +107,12 @@ int NAME(fwi_oracle_acoustic_run)(int nzp, int nyp, int order, int pml_width, in
     REAL *pya = (REAL *)calloc(S * cells, sizeof(REAL));
     REAL *pyb = (REAL *)calloc(S * cells, sizeof(REAL));
     if (!ua || !ub || !pza || !pzb || !pya || !pyb) return 2;
+    if (state) { /* carried state, fields in the order u, u-, pz, (scratch), py, (scratch) */
+        memcpy(ua, state + 0 * S * cells, S * cells * sizeof(REAL));
+        memcpy(ub, state + 1 * S * cells, S * cells * sizeof(REAL));
+        memcpy(pza, state + 2 * S * cells, S * cells * sizeof(REAL));
+        memcpy(pya, state + 4 * S * cells, S * cells * sizeof(REAL));
+    }
     /* rows / columns that can see PML memory variables: frame widened by h */
     const int zlo = h + pml_width + h, zhi = nzp - h - pml_width - h;
     const int ylo = h + pml_width + h, yhi = nyp - h - pml_width - h;
@@ -169,6 +176,37 @@ int NAME(fwi_oracle_acoustic_run)(int nzp, int nyp, int order, int pml_width, in
         { REAL *t = py; py = pyn; pyn = t; }
     }
     if (u_final) memcpy(u_final, u, S * cells * sizeof(REAL));
+    if (state) {
+        memcpy(state + 0 * S * cells, u, S * cells * sizeof(REAL));
+        memcpy(state + 1 * S * cells, um, S * cells * sizeof(REAL));
+        memcpy(state + 2 * S * cells, pz, S * cells * sizeof(REAL));
+        memcpy(state + 4 * S * cells, py, S * cells * sizeof(REAL));
+    }
     free(ua); free(ub); free(pza); free(pzb); free(pya); free(pyb);
     return 0;
+}
+
+int NAME(fwi_oracle_acoustic_run)(int nzp, int nyp, int order, int pml_width, int S, double dz,
+                                  double dy, double dt, const REAL *w, const REAL *sigz,
+                                  const REAL *sigy, int nsteps, int adjoint, int n_inj,
+                                  const int *inj_cell, const REAL *inj_amp, int inj_scale_a,
+                                  int n_smp, const int *smp_cell, REAL *smp_out, int smp_div_a,
+                                  REAL *q_write, const REAL *q_read, REAL *G, REAL *u_final) {
+    return NAME(acoustic_run_core)(nzp, nyp, order, pml_width, S, dz, dy, dt, w, sigz, sigy, nsteps,
+                                   adjoint, n_inj, inj_cell, inj_amp, inj_scale_a, n_smp, smp_cell,
+                                   smp_out, smp_div_a, q_write, q_read, G, u_final, NULL);
+}
+
+/* Same, continuing from (and leaving) the state [6][S][nzp*nyp] = u, u-, pz, -, py, - : lets a
+ * caller cut the time loop into segments (tests of the checkpointed and x-slab drivers). */
+int NAME(fwi_oracle_acoustic_run_state)(int nzp, int nyp, int order, int pml_width, int S, double dz,
+                                  double dy, double dt, const REAL *w, const REAL *sigz,
+                                  const REAL *sigy, int nsteps, int adjoint, int n_inj,
+                                  const int *inj_cell, const REAL *inj_amp, int inj_scale_a,
+                                  int n_smp, const int *smp_cell, REAL *smp_out, int smp_div_a,
+                                  REAL *q_write, const REAL *q_read, REAL *G, REAL *state) {
+    if (!state) return 1;
+    return NAME(acoustic_run_core)(nzp, nyp, order, pml_width, S, dz, dy, dt, w, sigz, sigy, nsteps,
+                                   adjoint, n_inj, inj_cell, inj_amp, inj_scale_a, n_smp, smp_cell,
+                                   smp_out, smp_div_a, q_write, q_read, G, NULL, state);
 }

@@ -30,7 +30,9 @@ class _Plan:
     """Everything about one call that does not depend on the direction of time."""
 
     def __init__(self, v: torch.Tensor, dx, dt: float, order: int, pml_width: int,
-                 vpmax: Optional[float], n_shots: int, chunk_rows: int = 0):
+                 vpmax: Optional[float], n_shots: int, chunk_rows: int = 0, window=None):
+        """`window` = (c0, c1): restrict the plan to the padded columns [c0, c1) of the global grid
+        (an x-slab, slab.py); model, PML profiles and point coordinates stay global."""
         if v.dim() != 2:
             raise RuntimeError(f"model['vp'] must be 2-D [nz, ny], got shape {tuple(v.shape)}")
         if not v.is_cuda:
@@ -44,7 +46,11 @@ class _Plan:
         self.nz, self.ny = int(v.shape[0]), int(v.shape[1])
         self.order, self.h, self.pw = order, order // 2, int(pml_width)
         self.P = self.pw + self.h
-        self.nzp, self.nyp = self.nz + 2 * self.P, self.ny + 2 * self.P
+        self.nzp, self.nyp_global = self.nz + 2 * self.P, self.ny + 2 * self.P
+        self.c0, self.c1 = (0, self.nyp_global) if window is None else (int(window[0]), int(window[1]))
+        if not (0 <= self.c0 < self.c1 <= self.nyp_global) or self.c1 - self.c0 <= 2 * self.P:
+            raise RuntimeError(f"bad column window {window} for a padded width of {self.nyp_global}")
+        self.nyp = self.c1 - self.c0
         self.vmax = float(vpmax) if vpmax is not None else float(v.detach().abs().max())
         self.ratio, self.dti = H.inner_step(float(dt), self.dz, self.dy, self.vmax)
         self.S = n_shots
@@ -58,14 +64,18 @@ class _Plan:
         self.stride = int(lay.shot_stride)
 
         vp = F.pad(v.detach()[None, None], (self.P,) * 4, mode="replicate")[0, 0]
+        self.v_pad_global = vp
+        vp = vp[:, self.c0:self.c1]
         self.v_pad = vp
         dti = torch.tensor(self.dti, dtype=torch.float32, device=self.dev)
         self.w = torch.zeros(self.nzp, self.pitch, dtype=torch.float32, device=self.dev)
         self.w[:, self.col0:self.col0 + self.nyp] = (vp * vp) * (dti * dti)
         sz = H.sigma_profile(self.nzp, self.h, self.pw, self.dz, self.vmax).float()
         sy = torch.zeros(self.pitch, dtype=torch.float32)
-        sy[self.col0:self.col0 + self.nyp] = H.sigma_profile(self.nyp, self.h, self.pw, self.dy, self.vmax).float()
+        sy[self.col0:self.col0 + self.nyp] = H.sigma_profile(self.nyp_global, self.h, self.pw, self.dy,
+                                                             self.vmax).float()[self.c0:self.c1]
         self.sigz, self.sigy = sz.to(self.dev), sy.to(self.dev)
+        self.n_fields, self.n_images = int(lay.wave_fields), int(lay.n_images)
 
     def desc(self, nsteps, adjoint, n_inj, n_smp) -> _lib.AcousticDesc:
         return _lib.AcousticDesc(self.nzp, self.nyp, self.order, self.pw, self.S, self.chunk_rows, nsteps,
@@ -77,9 +87,13 @@ class _Plan:
         c = H.to_cells(x.to(self.dev), self.dz, self.dy, loc_mode)
         bad = ((c[..., 0] < 0) | (c[..., 0] >= self.nz) | (c[..., 1] < 0) | (c[..., 1] >= self.ny)).any()
         z = c[..., 0].clamp(0, self.nz - 1) + self.P
-        ycol = c[..., 1].clamp(0, self.ny - 1) + self.P + self.col0
+        ycol = (c[..., 1].clamp(0, self.ny - 1) + self.P - self.c0).clamp(self.h, self.nyp - self.h - 1) + self.col0
         cell = z * self.pitch + ycol
         return cell, z, ycol, bad
+
+    def padded_columns(self, x: torch.Tensor, loc_mode: str) -> torch.Tensor:
+        """[S, n, 2] metres -> global padded column [S, n] of each point."""
+        return H.to_cells(x.to(self.dev), self.dz, self.dy, loc_mode)[..., 1] + self.P
 
     def lists(self, cell):
         return H.injection_lists(cell, self.nzp, self.pitch)
@@ -237,11 +251,15 @@ class Propagator(torch.nn.Module):
     ``chunk_rows`` (cap on the rows of one work segment, kernel tuning / tests, 0 = none),
     ``checkpoint_every`` (K > 0: wavefield checkpointing - the forward pass keeps the state every K
     inner steps instead of one snapshot per step, and the backward pass recomputes the snapshots
-    of one K-step segment at a time: memory O(nt/K + K) fields instead of O(nt), one extra forward).
+    of one K-step segment at a time: memory O(nt/K + K) fields instead of O(nt), one extra forward),
+    ``slabs`` (True or a process group: x-slab domain decomposition of every shot over the ranks of
+    the group with ghost-zone exchange every ``halo_steps`` inner steps, see slab.py; every rank
+    passes identical arguments and receives the full traces and the full gradient).
     """
 
     def __init__(self, model: dict, dx, pml_width=None, survey_pad=None, vpmax=None, *,
-                 accuracy: int = 4, loc_mode: str = "trunc", chunk_rows: int = 0, checkpoint_every: int = 0):
+                 accuracy: int = 4, loc_mode: str = "trunc", chunk_rows: int = 0, checkpoint_every: int = 0,
+                 slabs=False, halo_steps: int = 8):
         super().__init__()
         if not isinstance(model, dict) or "vp" not in model:
             raise RuntimeError("model must be a dict with key 'vp'")
@@ -271,6 +289,10 @@ class Propagator(torch.nn.Module):
         if checkpoint_every < 0:
             raise RuntimeError("checkpoint_every must be >= 0")
         self.checkpoint_every = int(checkpoint_every)
+        if slabs is not False and slabs is not None and checkpoint_every:
+            raise RuntimeError("slabs and checkpoint_every cannot be combined")
+        self.slabs = None if slabs is False else slabs
+        self.halo_steps = int(halo_steps)
 
     def forward(self, source_amplitudes: torch.Tensor, source_locations: torch.Tensor,
                 receiver_locations: torch.Tensor, dt: float) -> torch.Tensor:
@@ -278,6 +300,11 @@ class Propagator(torch.nn.Module):
         x_s, x_r = source_locations, receiver_locations
         if self.survey_pad is not None:
             v, x_s, x_r = _crop_to_survey(v, self.dx, x_s, x_r, self.survey_pad)
+        if self.slabs is not None:
+            from .slab import _SlabFunction
+            return _SlabFunction.apply(v, source_amplitudes, x_s, x_r, float(dt), self.dx, self.accuracy,
+                                       self.pml_width, self.vpmax, self.loc_mode, self.halo_steps,
+                                       None if self.slabs is True else self.slabs, _Plan)
         return _ScalarFunction.apply(v, source_amplitudes, x_s, x_r, float(dt), self.dx, self.accuracy,
                                      self.pml_width, self.vpmax, self.loc_mode, self.chunk_rows, self.checkpoint_every)
 

@@ -1,0 +1,240 @@
+"""x-slab domain decomposition of the scalar propagator: one shot spread over the GPUs of a box.
+
+Second multi-GPU mode of the path (BASELINE config 4 variant) for grids whose
+single-shot working set (one snapshot per step) does not fit one GPU.  The reference has no such
+mode: it runs every shot whole on one hard-coded GPU (models/networks.py:5316, :5464), so this
+is an extension behind the same call -
+
+    prop = Propagator({'vp': v}, dx, slabs=True)          # every rank, identical arguments
+    rec = prop(source_amplitudes, x_s, x_r, dt)           # full [nt, S, R] on every rank
+    loss(rec).backward()                                  # full v.grad on every rank
+
+Decomposition.  The padded grid [nzp, nyp] is cut along y (the fast axis is kept whole per row
+pitch; slabs are column ranges) into `world` slabs of near-equal width.  Rank r owns the padded
+columns [lo_r, hi_r) and works on the window [lo_r - G, hi_r + G) (clipped at the two ends of
+the grid), G = halo_steps * order/2 ghost columns.  A window is advanced `halo_steps` steps at a
+time with the ordinary step kernel (csrc/acoustic.cu, through the C ABI): the outermost order/2
+columns of a window are never updated, so after k steps the k*order/2 outer columns of an inner
+edge are stale, and after halo_steps steps exactly the ghost zone is.  Then every rank refreshes
+its ghost zones from the neighbours' owned columns - u, u-, pz, py, G columns each - with one
+batched send/recv pair per neighbour (NCCL P2P over NVLink on GPUs; gloo in the CPU tests).
+Owned columns therefore always hold the values the undecomposed grid would, and the arithmetic
+per cell is that of the single-GPU kernel.  The adjoint is the same recurrence, so it is
+decomposed the same way; snapshots and the image stay local to a window and only the owned
+columns of the image are kept.
+
+Points.  Sources are injected by every rank whose window contains them (ghost zones included -
+the ghost field must evolve like the neighbour's); receivers are sampled by the owning rank only
+and the traces are summed over ranks (exact: the other ranks contribute zeros).  The adjoint swaps
+the roles.  The model gradient is assembled from the owned image columns with one all_reduce of
+the padded image (every element has exactly one non-zero contributor).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from . import _host as H
+from .distributed import shard_bounds
+
+
+class SlabGeometry:
+    """Column bookkeeping of one rank's slab (pure integers; tested on CPU)."""
+
+    def __init__(self, nyp: int, order: int, pml_width: int, world: int, rank: int, halo_steps: int):
+        if halo_steps < 1:
+            raise RuntimeError("halo_steps must be >= 1")
+        self.h = order // 2
+        self.P = pml_width + self.h
+        self.G = halo_steps * self.h
+        self.world, self.rank, self.T = world, rank, halo_steps
+        self.lo, self.hi = shard_bounds(nyp, rank, world)
+        widths = [shard_bounds(nyp, r, world) for r in range(world)]
+        need = max(self.G, 2 * self.P + 1)
+        if world > 1 and min(b - a for a, b in widths) < need:
+            raise RuntimeError(f"slabs of {min(b - a for a, b in widths)} columns are narrower than the "
+                               f"{need} columns {halo_steps} halo steps need: use fewer ranks or halo steps")
+        self.has_left, self.has_right = rank > 0, rank < world - 1
+        self.c0 = self.lo - (self.G if self.has_left else 0)
+        self.c1 = self.hi + (self.G if self.has_right else 0)
+        self.nyp = nyp
+
+    # window-local column ranges
+    @property
+    def own(self) -> Tuple[int, int]:
+        return self.lo - self.c0, self.hi - self.c0
+
+    def send_left(self) -> Tuple[int, int]:      # my first G owned columns -> left neighbour's right ghost
+        a = self.lo - self.c0
+        return a, a + self.G
+
+    def send_right(self) -> Tuple[int, int]:     # my last G owned columns -> right neighbour's left ghost
+        b = self.hi - self.c0
+        return b - self.G, b
+
+    def ghost_left(self) -> Tuple[int, int]:
+        return 0, self.G
+
+    def ghost_right(self) -> Tuple[int, int]:
+        b = self.hi - self.c0
+        return b, b + self.G
+
+
+def exchange_ghosts(wave: torch.Tensor, geo: SlabGeometry, n_fields: int, n_shots: int, nzp: int,
+                    pitch: int, col0: int, group=None) -> None:
+    """Refreshes the ghost columns of the live fields (u, u-, pz, py) in place.
+
+    `wave` is the flat workspace [n_fields][S][nzp][pitch] in settled order.  One packed message per
+    neighbour and direction; the four P2P operations are batched (a single NCCL group)."""
+    if geo.world == 1:
+        return
+    live = [0, 1, 2, 4] if n_fields >= 6 else [0, 1]
+    W = wave.view(n_fields, n_shots, nzp, pitch)
+    ops, recvs = [], []
+
+    def ranks(r):
+        return r if group is None else dist.get_global_rank(group, r)
+
+    def plan(has, peer, send_cols, ghost_cols):
+        if not has:
+            return
+        a, b = send_cols
+        out = W[live, :, :, col0 + a:col0 + b].contiguous()
+        buf = torch.empty_like(out)
+        ops.append(dist.P2POp(dist.isend, out, ranks(peer), group))
+        ops.append(dist.P2POp(dist.irecv, buf, ranks(peer), group))
+        recvs.append((buf, ghost_cols))
+
+    plan(geo.has_left, geo.rank - 1, geo.send_left(), geo.ghost_left())
+    plan(geo.has_right, geo.rank + 1, geo.send_right(), geo.ghost_right())
+    for req in dist.batch_isend_irecv(ops):
+        req.wait()
+    for buf, (a, b) in recvs:
+        W[live, :, :, col0 + a:col0 + b] = buf
+
+
+class _SlabFunction(torch.autograd.Function):
+    """Propagator call on an x-slab decomposition; see the module docstring.  `plan_cls` is the
+    per-window time-loop runner: scalar._Plan (the CUDA kernels) in the product."""
+
+    @staticmethod
+    def forward(ctx, v, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, loc_mode,
+                halo_steps, group, plan_cls):
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError("slab decomposition needs an initialised torch.distributed process group")
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        if source_amplitudes.dim() != 3:
+            raise RuntimeError("source_amplitudes must be [nt, n_shots, n_sources_per_shot]")
+        nt, S, Ns = source_amplitudes.shape
+        if x_s.dim() != 3 or tuple(x_s.shape) != (S, Ns, 2):
+            raise RuntimeError(f"source_locations must be [{S}, {Ns}, 2], got {tuple(x_s.shape)}")
+        if x_r.dim() != 3 or x_r.shape[0] != S or x_r.shape[2] != 2:
+            raise RuntimeError(f"receiver_locations must be [{S}, n_receivers, 2], got {tuple(x_r.shape)}")
+        R = int(x_r.shape[1])
+        h = order // 2
+        nyp = int(v.shape[1]) + 2 * (pml_width + h)
+        geo = SlabGeometry(nyp, order, pml_width, world, rank, halo_steps)
+        if vpmax is None:
+            vpmax = float(v.detach().abs().max())        # the model is replicated: same on every rank
+        plan = plan_cls(v, dx, dt, order, pml_width, vpmax, S, window=(geo.c0, geo.c1))
+        dev = plan.dev
+        s_cell, _, _, bad_s = plan.points(x_s, "source", loc_mode)
+        r_cell, _, _, bad_r = plan.points(x_r, "receiver", loc_mode)
+        if bool((bad_s | bad_r).item()):
+            raise RuntimeError("source/receiver location outside the model")
+        s_col, r_col = plan.padded_columns(x_s, loc_mode), plan.padded_columns(x_r, loc_mode)
+
+        def masks(col):
+            inside = (col >= geo.c0 + h) & (col < geo.c1 - h)       # the window can inject there
+            owned = (col >= geo.lo) & (col < geo.hi)                 # this rank reports it
+            return inside.to(torch.float32), owned.to(torch.float32)
+
+        s_in, s_own = masks(s_col)
+        r_in, r_own = masks(r_col)
+        amp = H.resample_up(source_amplitudes.detach().to(dev, torch.float32), plan.ratio).contiguous()
+        nti = nt * plan.ratio
+        need_v, need_s = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        q = torch.empty(nti * S * plan.stride, dtype=torch.float32, device=dev) if need_v else None
+        r32 = r_cell.to(torch.int32).contiguous()
+        lists = plan.lists(s_cell)
+        amp_in = (amp * s_in[None]).contiguous()
+        wave, parts = plan.new_wave(), []
+        T = geo.T
+        for t0 in range(0, nti, T):
+            n = min(T, nti - t0)
+            qv = None if q is None else q[t0 * S * plan.stride:(t0 + n) * S * plan.stride]
+            parts.append(plan.run(nsteps=n, adjoint=0, inj=lists, inj_amp=amp_in[t0:t0 + n], smp_cell=r32,
+                                  n_smp=R, q_write=qv, wave=wave))
+            wave = plan.settle(wave, n)
+            if t0 + n < nti:
+                exchange_ghosts(wave, geo, plan.n_fields, S, plan.nzp, plan.pitch, plan.col0, group)
+        rec = torch.cat(parts, 0) * r_own[None]
+        if world > 1:
+            dist.all_reduce(rec, op=dist.ReduceOp.SUM, group=group)
+        out = rec[::plan.ratio].contiguous() if plan.ratio > 1 else rec
+        ctx.plan, ctx.geo, ctx.group, ctx.q = plan, geo, group, q
+        ctx.amp = amp
+        ctx.cells = (s_cell, r_cell, s_col)
+        ctx.masks = (s_own, r_in)
+        ctx.dims = (nt, S, Ns, R, nti)
+        ctx.need = (need_v, need_s)
+        ctx.src_like = source_amplitudes.detach()
+        return out
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, grad_rec):
+        plan, geo, group = ctx.plan, ctx.geo, ctx.group
+        s_cell, r_cell, s_col = ctx.cells
+        s_own, r_in = ctx.masks
+        nt, S, Ns, R, nti = ctx.dims
+        need_v, need_s = ctx.need
+        dev = plan.dev
+        g = grad_rec.to(dev, torch.float32)
+        if plan.ratio > 1:
+            g_in = torch.zeros(nti, S, R, dtype=torch.float32, device=dev)
+            g_in[::plan.ratio] = g
+        else:
+            g_in = g
+        g_in = (g_in * r_in[None]).contiguous()
+        image = torch.zeros(plan.n_images * plan.stride, dtype=torch.float32, device=dev) if need_v else None
+        s32 = s_cell.to(torch.int32).contiguous()
+        rec_lists = plan.lists(r_cell)
+        awave, parts = plan.new_wave(), []
+        T = geo.T
+        starts = list(range(0, nti, T))
+        for t0 in reversed(starts):
+            n = min(T, nti - t0)
+            qv = None if not need_v else ctx.q[t0 * S * plan.stride:(t0 + n) * S * plan.stride]
+            parts.append(plan.run(nsteps=n, adjoint=1, inj=rec_lists, inj_amp=g_in[t0:t0 + n], smp_cell=s32,
+                                  n_smp=Ns, q_read=qv, image=image, wave=awave))
+            awave = plan.settle(awave, n)
+            if t0 > 0:
+                exchange_ghosts(awave, geo, plan.n_fields, S, plan.nzp, plan.pitch, plan.col0, group)
+        gs = torch.cat(parts[::-1], 0) * s_own[None]                   # [nti, S, Ns], owner's samples only
+        if geo.world > 1:
+            dist.all_reduce(gs, op=dist.ReduceOp.SUM, group=group)
+        grad_v = grad_s = None
+        if need_v:
+            a, b = geo.own
+            Gw = image.view(plan.n_images, plan.nzp, plan.pitch).sum(0)[:, plan.col0 + a:plan.col0 + b]
+            Gp = torch.zeros(plan.nzp, geo.nyp, dtype=torch.float32, device=dev)
+            Gp[:, geo.lo:geo.hi] = Gw
+            if geo.world > 1:
+                dist.all_reduce(Gp, op=dist.ReduceOp.SUM, group=group)
+            # source term of dJ/dw at the source cells (global padded coordinates, every rank alike)
+            z = torch.div(s_cell, plan.pitch, rounding_mode="floor")
+            Gp.view(-1).index_add_(0, (z * geo.nyp + s_col).reshape(-1), (gs * ctx.amp).sum(0).reshape(-1))
+            grad_v = H.replicate_pad_adjoint((2.0 / plan.v_pad_global) * Gp, plan.P)
+        if need_s:
+            grad_s = H.resample_up_adjoint(gs, plan.ratio, ctx.src_like.to(dev, torch.float32))
+            grad_s = grad_s.to(ctx.src_like.device, ctx.src_like.dtype)
+        ctx.q = None
+        return (grad_v, grad_s) + (None,) * 11
+
+
+def slab_columns(nyp: int, world: int) -> List[Tuple[int, int]]:
+    """Owned padded-column range of every rank."""
+    return [shard_bounds(nyp, r, world) for r in range(world)]

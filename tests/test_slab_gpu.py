@@ -1,0 +1,93 @@
+"""x-slab domain decomposition on the CUDA kernels.
+
+* one GPU: a world-size-1 group - the call is cut into halo_steps-long launches of the windowed
+  plan (window = whole grid) and must reproduce the ordinary call bit for bit;
+* two GPUs (skipped on a one-GPU box; run with `gpurun --gpus 2`): one process per GPU over NCCL,
+  ghost columns exchanged every halo_steps steps; traces and gradients must match the CPU oracle
+  to the north-star tolerances and the undecomposed CUDA result to round-off."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from tests import _cases as K
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _problem(order):
+    nz, ny, S, R, nt, pw = 36, 300, 3, 25, 130, 8
+    v = K.layered_model(nz, ny, seed=3)
+    x_s, x_r = K.survey(nz, ny, 10.0, S, R, 1, seed=4)
+    x_s[1, 0, 0] = 9 * 10.0
+    x_r[:, ::3, 0] = 7 * 10.0
+    src = K.ricker(18.0, nt, 1e-3, 1 / 18.0).reshape(-1, 1, 1).repeat(1, S, 1).contiguous()
+    g = torch.randn(nt, S, R, generator=torch.Generator().manual_seed(5))
+    return dict(v=v, x_s=x_s, x_r=x_r, src=src, g=g, dx=10.0, dt=1e-3, pw=pw, order=order)
+
+
+def _gradient(p, dev, **kw):
+    from physicsbasedfwi2_b200.scalar import Propagator
+    vg = p["v"].to(dev).requires_grad_(True)
+    sg = p["src"].to(dev).requires_grad_(True)
+    prop = Propagator({"vp": vg}, p["dx"], pml_width=p["pw"], accuracy=p["order"], **kw)
+    rec = prop(sg, p["x_s"].to(dev), p["x_r"].to(dev), p["dt"])
+    (rec * p["g"].to(dev)).sum().backward()
+    return rec.detach().cpu(), vg.grad.cpu(), sg.grad.cpu()
+
+
+def _worker(rank, world, port, T, order, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl" if world > 1 else "gloo", rank=rank, world_size=world,
+                            **({"device_id": dev} if world > 1 else {}))
+    try:
+        from oracle import cpu_ref as O
+        p = _problem(order)
+        rec, gv, gs = _gradient(p, dev, slabs=True, halo_steps=T)
+        r1, gv1, gs1 = _gradient(p, dev)                              # undecomposed, same GPU
+        r0, gv0, gs0 = O.acoustic_gradient(p["v"], p["dx"], p["src"], p["x_s"], p["x_r"], p["dt"], grad_rec=p["g"],
+                                           order=order, pml_width=p["pw"], dtype=torch.float32)
+        out[rank] = dict(oracle=(K.rel_l2(rec, r0), K.rel_l2(gv, gv0), K.rel_l2(gs, gs0)),
+                         single=(K.rel_l2(rec, r1), K.rel_l2(gv, gv1), K.rel_l2(gs, gs1)),
+                         exact=bool(torch.equal(rec, r1) and torch.equal(gv, gv1)))
+    finally:
+        dist.destroy_process_group()
+
+
+def _check(out, world):
+    assert len(out) == world
+    for r in range(world):
+        et, ev, es = out[r]["oracle"]
+        assert et <= 1e-5 and ev <= 1e-4 and es <= 1e-4, (r, out[r])
+        et, ev, es = out[r]["single"]
+        assert et <= 2e-6 and ev <= 2e-5 and es <= 2e-5, (r, out[r])
+
+
+@pytest.mark.parametrize("T,order", [(8, 4), (5, 8)])
+def test_segmented_window_plan_on_one_gpu(cuda_lib, T, order):
+    out = mp.Manager().dict()
+    mp.spawn(_worker, args=(1, _free_port(), T, order, out), nprocs=1, join=True)
+    _check(out, 1)
+    assert out[0]["exact"], out[0]
+
+
+@pytest.mark.parametrize("T,order", [(8, 4), (4, 8), (1, 2)])
+def test_two_gpu_slabs_match_oracle_and_single_gpu(cuda_lib, T, order):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    out = mp.Manager().dict()
+    mp.spawn(_worker, args=(2, _free_port(), T, order, out), nprocs=2, join=True)
+    _check(out, 2)
