@@ -281,12 +281,14 @@ def main():
     nz, ny, nt = w["nz"], w["ny"], w["nt"]
     # shots per step: one q snapshot per inner step per shot must fit HBM next to the wavefields
     P = w["pml"] + w["order"] // 2
-    per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nt + 8) * (5 if w.get("elastic") else 1)
+    from physicsbasedfwi2_b200 import _host
+    nti = nt * (1 if w.get("elastic") else _host.inner_step(w["dt"], w["dx"], w["dx"], w["vmax"])[0])
+    per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nti + 8) * (5 if w.get("elastic") else 1)
     if w.get("ckpt"):
-        per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (6 * (nt // w["ckpt"] + 2) + w["ckpt"] + 24)
+        per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (6 * (nti // w["ckpt"] + 2) + w["ckpt"] + 24)
     if w.get("slabs"):
         cols = (ny + 2 * P) // world + 2 * w["slabs"] * (w["order"] // 2) + 64
-        per_shot = (nz + 2 * P) * cols * 4 * (nt + 16)
+        per_shot = (nz + 2 * P) * cols * 4 * (nti + 16)
     free, _ = torch.cuda.mem_get_info(dev)
     batch = args.shots or max(1, min(16 if w.get("ckpt") else 6, int((0.6 if w.get("ckpt") else 0.88) * free // per_shot)))
 
@@ -373,7 +375,7 @@ def main():
     ms_fwd, ms_adj = sum(t_fwd) / len(t_fwd), sum(t_adj) / len(t_adj)      # ms per launch
 
     cells = nz * ny
-    work = cells * nt * batch * (1 if w.get("slabs") else world) * 2   # cell-updates per step, whole job
+    work = cells * nti * batch * (1 if w.get("slabs") else world) * 2   # cell-updates (inner steps) per step, whole job
     value = work * args.steps / (ms * 1e-3) / 1e9
 
     e2e = None
@@ -401,7 +403,7 @@ def main():
                 "algorithmic_bytes_per_cell_update": {"forward": bf, "adjoint": ba},
                 "forward": {"ms_per_launch": round(ms_fwd, 5), "achieved": round(ach_f, 1), "frac": round(ach_f / peak, 4)},
                 "adjoint": {"ms_per_launch": round(ms_adj, 5), "achieved": round(ach_a, 1), "frac": round(ach_a / peak, 4)},
-                "kernel_share_of_step": round((ms_fwd + ms_adj) * nt * args.steps / ms, 4)}
+                "kernel_share_of_step": round((ms_fwd + ms_adj) * nti * args.steps / ms, 4)}
         prof = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(prof):
             try:
