@@ -105,6 +105,52 @@ int fwi_acoustic_plan_stats(const fwi_acoustic_desc *desc, int n_units, int64_t 
  * adjoint=1 with q_read/image replaces its backward (models/networks.py:5491). */
 int fwi_acoustic_run(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);
 
+/* ---- x-slab domain decomposition: ghost-zone exchange by peer stores over NVLink ---------- */
+/* One shot spread over the GPUs of a box (BASELINE config 4 variant; no reference
+ * counterpart - the reference runs every shot whole on one GPU, models/networks.py:5316).  Each
+ * rank advances a column window of the grid with ghost_cols = halo_steps * order/2 extra columns
+ * per inner edge.  Every halo_steps steps the native time loop (a) packs its outermost owned
+ * columns of the live fields (u, u-, pz, py) and stores them straight into the neighbour's staging
+ * buffer through a peer mapping, then raises the neighbour's flag (release, system scope), and
+ * (b) waits for its own flags and unpacks its staging buffer into its ghost columns.  Staging is
+ * double-buffered by exchange parity, so a rank can run at most one exchange ahead of a neighbour
+ * without overwriting data still in use.  No host synchronisation inside the loop.
+ *
+ * Exchange memory of one rank ("comm block", allocated with fwi_peer_alloc, mapped by the two
+ * neighbours with fwi_peer_open): 256 header bytes = uint32 flags_in[2] (side 0: raised by the left
+ * neighbour, side 1: by the right), uint32 counter[2], uint32 status; then
+ * float stage[2 parity][2 side][slot_floats], slot_floats = live * n_shots * nzp * ghost_cols. */
+typedef struct fwi_slab_link {
+    int32_t halo_steps;       /* steps between exchanges (>= 1) */
+    int32_t ghost_cols;       /* halo_steps * order/2 */
+    int32_t has_left, has_right;
+    int32_t send_left_col, send_right_col;   /* first DEVICE column of the owned columns sent to each side */
+    int32_t ghost_left_col, ghost_right_col; /* first DEVICE column of each ghost zone */
+    void *comm;               /* this rank's comm block */
+    void *peer_left, *peer_right; /* the neighbours' comm blocks (peer mappings), NULL where none */
+    uint32_t epoch;           /* exchanges completed before this call; the call's k-th exchange is epoch + k */
+    uint32_t timeout_ms;      /* a flag wait longer than this sets status = 1 and stops waiting (0 = 20000) */
+} fwi_slab_link;
+
+#define FWI_SLAB_HEADER_BYTES 256
+
+/* Peer-visible device memory for comm blocks (cudaMalloc + CUDA IPC; zero-filled).  `handle` is
+ * 64 opaque bytes another process of the same box passes to fwi_peer_open. */
+int fwi_peer_alloc(int64_t bytes, void **ptr, unsigned char handle[64]);
+int fwi_peer_open(const unsigned char handle[64], void **ptr);
+int fwi_peer_close(void *ptr);
+int fwi_peer_free(void *ptr);
+/* Reads the status word of a comm block (synchronises `stream`): 0 ok, 1 a flag wait timed out. */
+int fwi_slab_status(const void *comm, void *stream, uint32_t *status);
+/* Number of exchanges fwi_acoustic_run_slab performs for `nsteps` steps (host arithmetic). */
+int32_t fwi_slab_exchanges(int32_t nsteps, int32_t halo_steps);
+
+/* fwi_acoustic_run on a window of the grid with in-loop ghost exchange.  Forward: exchange after
+ * step n when (n + 1) % halo_steps == 0 and n + 1 < nsteps.  Adjoint: after step n when
+ * (nsteps - n) % halo_steps == 0 and n > 0.  All ranks must call with the same nsteps. */
+int fwi_acoustic_run_slab(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf,
+                          const fwi_slab_link *link, void *stream);
+
 /* Named wrappers with the direction fixed (argument checks differ). */
 int fwi_acoustic_forward(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);
 int fwi_acoustic_backward(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);

@@ -40,6 +40,17 @@ class AcousticBuffers(C.Structure):
                 ("image", C.c_void_p), ("unit_table", C.c_void_p)]
 
 
+class SlabLink(C.Structure):
+    _fields_ = [("halo_steps", C.c_int32), ("ghost_cols", C.c_int32), ("has_left", C.c_int32),
+                ("has_right", C.c_int32), ("send_left_col", C.c_int32), ("send_right_col", C.c_int32),
+                ("ghost_left_col", C.c_int32), ("ghost_right_col", C.c_int32), ("comm", C.c_void_p),
+                ("peer_left", C.c_void_p), ("peer_right", C.c_void_p), ("epoch", C.c_uint32),
+                ("timeout_ms", C.c_uint32)]
+
+
+SLAB_HEADER_BYTES = 256
+
+
 class ElasticDesc(C.Structure):
     _fields_ = [("nzp", C.c_int32), ("nyp", C.c_int32), ("order", C.c_int32), ("pml_width", C.c_int32),
                 ("n_shots", C.c_int32), ("nsteps", C.c_int32), ("n_src", C.c_int32), ("n_rec", C.c_int32),
@@ -103,6 +114,16 @@ def lib() -> C.CDLL:
     for name in ("fwi_acoustic_run", "fwi_acoustic_forward", "fwi_acoustic_backward"):
         getattr(L, name).argtypes = [C.POINTER(AcousticDesc), C.POINTER(AcousticBuffers), C.c_void_p]
         getattr(L, name).restype = C.c_int
+    L.fwi_acoustic_run_slab.argtypes = [C.POINTER(AcousticDesc), C.POINTER(AcousticBuffers), C.POINTER(SlabLink),
+                                        C.c_void_p]
+    L.fwi_acoustic_run_slab.restype = C.c_int
+    L.fwi_peer_alloc.argtypes = [C.c_int64, C.POINTER(C.c_void_p), C.c_char_p]
+    L.fwi_peer_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    L.fwi_peer_close.argtypes = [C.c_void_p]
+    L.fwi_peer_free.argtypes = [C.c_void_p]
+    L.fwi_slab_status.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]
+    L.fwi_slab_exchanges.argtypes = [C.c_int32, C.c_int32]
+    L.fwi_slab_exchanges.restype = C.c_int32
     L.fwi_elastic_wave_floats.argtypes = [C.POINTER(ElasticDesc)]
     L.fwi_elastic_wave_floats.restype = C.c_int64
     for name in ("fwi_elastic_forward", "fwi_elastic_backward"):

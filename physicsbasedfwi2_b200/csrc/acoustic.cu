@@ -26,6 +26,7 @@
 //
 // Arithmetic order per cell follows oracle/cpu_ref_impl.h (explicit fma, no contraction).
 #include <cuda.h>
+#include <string.h>
 
 #include <algorithm>
 #include <type_traits>
@@ -940,6 +941,92 @@ cudaError_t launch_h(int h, const StepParams &p, int blocks, cudaStream_t st) {
     }
 }
 
+// ---- x-slab ghost exchange (include/fwi_b200.h, fwi_slab_link) ----------------------------------
+struct SlabXfer {
+    const float *src[4];      // push: the live fields of this rank (u, u-, pz, py)
+    float *dst[4];            // unpack: the same fields
+    int n_live, S, nzp, pitch, G;
+    long long stride;         // floats per shot per field
+    int col[2];               // push: first sent column per side; unpack: first ghost column per side
+    int has[2];
+    float *stage[2];          // push: the neighbour's staging slot per side; unpack: this rank's slot per side
+    unsigned *flag[2];        // push: the neighbour's flag to raise per side; unpack: this rank's flag per side
+    unsigned *counter;        // push: this rank's block counters [2]
+    unsigned *status;
+    unsigned epoch;
+    unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// blockIdx.y = side.  Packs [live][S][nzp][G] from the owned edge columns into the neighbour's
+// staging slot with peer stores; the last block to finish raises the neighbour's flag.
+__global__ void __launch_bounds__(256) slab_push_kernel(const SlabXfer x) {
+    const int side = blockIdx.y;
+    if (!x.has[side]) return;
+    const long long per_field = (long long)x.S * x.nzp * x.G;
+    const long long total = per_field * x.n_live;
+    float *out = x.stage[side];
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+        const int f = (int)(e / per_field);
+        long long r = e - f * per_field;
+        const int c = (int)(r % x.G);
+        r /= x.G;
+        const int z = (int)(r % x.nzp), s = (int)(r / x.nzp);
+        out[e] = x.src[f][s * x.stride + (long long)z * x.pitch + x.col[side] + c];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned done = atomicAdd(&x.counter[side], 1u);
+        if (done == gridDim.x - 1) {
+            x.counter[side] = 0;
+            __threadfence_system();
+            st_release_sys(x.flag[side], x.epoch);
+        }
+    }
+}
+
+// blockIdx.y = side.  Waits until the neighbour has delivered exchange `epoch`, then copies the
+// staging slot into the ghost columns.  A wait that exceeds the timeout sets status and gives up
+// (the data is then wrong, and the host reports it) instead of hanging the device.
+__global__ void __launch_bounds__(256) slab_unpack_kernel(const SlabXfer x) {
+    const int side = blockIdx.y;
+    if (!x.has[side]) return;
+    if (threadIdx.x == 0) {
+        const unsigned long long t0 = global_ns();
+        while ((int)(ld_acquire_sys(x.flag[side]) - x.epoch) < 0) {
+            if (*(volatile unsigned *)x.status != 0) break;
+            if (global_ns() - t0 > x.timeout_ns) { atomicExch(x.status, 1u); break; }
+            __nanosleep(200);
+        }
+    }
+    __syncthreads();
+    const long long per_field = (long long)x.S * x.nzp * x.G;
+    const long long total = per_field * x.n_live;
+    const float *in = x.stage[side];
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+        const int f = (int)(e / per_field);
+        long long r = e - f * per_field;
+        const int c = (int)(r % x.G);
+        r /= x.G;
+        const int z = (int)(r % x.nzp), s = (int)(r / x.nzp);
+        x.dst[f][s * x.stride + (long long)z * x.pitch + x.col[side] + c] = __ldcv(in + e);
+    }
+}
+
 }  // namespace
 
 extern "C" int fwi_acoustic_get_layout(const fwi_acoustic_desc *desc, fwi_acoustic_layout *out) {
@@ -997,7 +1084,7 @@ extern "C" int fwi_acoustic_plan_stats(const fwi_acoustic_desc *desc, int n_unit
     return FWI_OK;
 }
 
-extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, void *stream) {
+static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, const fwi_slab_link *link, void *stream) {
     int rc = check_desc(d);
     if (rc != FWI_OK) return rc;
     FWI_CHECK_ARG(b != nullptr, "buffers struct is NULL");
@@ -1107,6 +1194,26 @@ extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_b
         p.trace = d_trace;
     }
     int blocks = ceil_div(n_units, kNW);
+    SlabXfer push = {}, unpack = {};
+    unsigned exchanges = 0;
+    if (link) {
+        char *me = static_cast<char *>(link->comm);
+        char *peer[2] = {static_cast<char *>(link->peer_left), static_cast<char *>(link->peer_right)};
+        push.n_live = unpack.n_live = d->pml_width > 0 ? 4 : 2;
+        push.S = unpack.S = d->n_shots; push.nzp = unpack.nzp = d->nzp; push.pitch = unpack.pitch = g.pitch;
+        push.G = unpack.G = link->ghost_cols; push.stride = unpack.stride = p.stride;
+        push.has[0] = unpack.has[0] = link->has_left; push.has[1] = unpack.has[1] = link->has_right;
+        push.col[0] = link->send_left_col; push.col[1] = link->send_right_col;
+        unpack.col[0] = link->ghost_left_col; unpack.col[1] = link->ghost_right_col;
+        unsigned *hdr = reinterpret_cast<unsigned *>(me);
+        push.counter = hdr + 2;
+        push.status = unpack.status = hdr + 4;
+        unpack.flag[0] = hdr + 0; unpack.flag[1] = hdr + 1;
+        // what I send to my left neighbour arrives "from its right" (its side 1), and vice versa
+        push.flag[0] = peer[0] ? reinterpret_cast<unsigned *>(peer[0]) + 1 : nullptr;
+        push.flag[1] = peer[1] ? reinterpret_cast<unsigned *>(peer[1]) + 0 : nullptr;
+        push.timeout_ns = unpack.timeout_ns = (unsigned long long)(link->timeout_ms ? link->timeout_ms : 20000u) * 1000000ull;
+    }
     for (int it = 0; it < d->nsteps; ++it) {
         const int n = d->adjoint ? d->nsteps - 1 - it : it;
         p.u = u; p.um = um; p.pz = pz; p.pzn = pzn; p.py = py; p.pyn = pyn;
@@ -1132,6 +1239,33 @@ extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_b
         float *t = u; u = um; um = t;
         t = pz; pz = pzn; pzn = t;
         t = py; py = pyn; pyn = t;
+        if (link && it + 1 < d->nsteps && (it + 1) % link->halo_steps == 0) {
+            // ghost exchange number epoch + k of the live fields, which are now u, um, pz, py
+            const unsigned epoch = link->epoch + ++exchanges;
+            const size_t slot = (size_t)push.n_live * d->n_shots * d->nzp * link->ghost_cols;
+            char *me = static_cast<char *>(link->comm);
+            char *peer[2] = {static_cast<char *>(link->peer_left), static_cast<char *>(link->peer_right)};
+            const float *live[4] = {u, um, pz, py};
+            for (int f = 0; f < 4; ++f) { push.src[f] = live[f]; unpack.dst[f] = const_cast<float *>(live[f]); }
+            push.epoch = unpack.epoch = epoch;
+            for (int side = 0; side < 2; ++side) {
+                // stage[parity][side]: I write the neighbour's slot of the OPPOSITE side, and read my own
+                float *mine = reinterpret_cast<float *>(me + FWI_SLAB_HEADER_BYTES) + ((size_t)(epoch & 1) * 2 + side) * slot;
+                unpack.stage[side] = mine;
+                push.stage[side] = peer[side] ? reinterpret_cast<float *>(peer[side] + FWI_SLAB_HEADER_BYTES)
+                                                     + ((size_t)(epoch & 1) * 2 + (1 - side)) * slot
+                                              : nullptr;
+            }
+            const int xb = (int)std::min<size_t>(64, (slot + 255) / 256);
+            slab_push_kernel<<<dim3(xb, 2), 256, 0, st>>>(push);
+            slab_unpack_kernel<<<dim3(xb, 2), 256, 0, st>>>(unpack);
+            cudaError_t e2 = cudaGetLastError();
+            if (e2 != cudaSuccess) {
+                fwi::set_error("slab exchange launch failed at step %d: %s", n, cudaGetErrorString(e2));
+                return FWI_ERR_CUDA;
+            }
+            fwi::count_launch(2);
+        }
     }
     if (p.trace) {
         std::vector<unsigned long long> tr(2 * (size_t)n_units);
@@ -1155,6 +1289,63 @@ extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_b
             fclose(f);
         }
     }
+    return FWI_OK;
+}
+
+extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, void *stream) {
+    return run_impl(d, b, nullptr, stream);
+}
+
+extern "C" int32_t fwi_slab_exchanges(int32_t nsteps, int32_t halo_steps) {
+    if (nsteps <= 0 || halo_steps <= 0) return 0;
+    return (nsteps - 1) / halo_steps;
+}
+
+extern "C" int fwi_acoustic_run_slab(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b,
+                                     const fwi_slab_link *link, void *stream) {
+    FWI_CHECK_ARG(d && b && link, "NULL argument");
+    FWI_CHECK_ARG(link->halo_steps >= 1 && link->ghost_cols == link->halo_steps * (d->order / 2),
+                  "ghost_cols must equal halo_steps * order/2");
+    FWI_CHECK_ARG(link->comm != nullptr, "comm block is NULL");
+    FWI_CHECK_ARG(!link->has_left || link->peer_left, "peer_left is NULL");
+    FWI_CHECK_ARG(!link->has_right || link->peer_right, "peer_right is NULL");
+    return run_impl(d, b, link, stream);
+}
+
+extern "C" int fwi_slab_status(const void *comm, void *stream, uint32_t *status) {
+    FWI_CHECK_ARG(comm && status, "NULL argument");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    FWI_CHECK_CUDA(cudaMemcpyAsync(status, static_cast<const char *>(comm) + 16, 4, cudaMemcpyDeviceToHost, st));
+    FWI_CHECK_CUDA(cudaStreamSynchronize(st));
+    return FWI_OK;
+}
+
+extern "C" int fwi_peer_alloc(int64_t bytes, void **ptr, unsigned char handle[64]) {
+    FWI_CHECK_ARG(bytes > 0 && ptr && handle, "bad arguments");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    FWI_CHECK_CUDA(cudaMalloc(ptr, (size_t)bytes));
+    FWI_CHECK_CUDA(cudaMemset(*ptr, 0, (size_t)bytes));
+    cudaIpcMemHandle_t h;
+    FWI_CHECK_CUDA(cudaIpcGetMemHandle(&h, *ptr));
+    memcpy(handle, &h, 64);
+    return FWI_OK;
+}
+
+extern "C" int fwi_peer_open(const unsigned char handle[64], void **ptr) {
+    FWI_CHECK_ARG(handle && ptr, "bad arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    FWI_CHECK_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return FWI_OK;
+}
+
+extern "C" int fwi_peer_close(void *ptr) {
+    FWI_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+    return FWI_OK;
+}
+
+extern "C" int fwi_peer_free(void *ptr) {
+    FWI_CHECK_CUDA(cudaFree(ptr));
     return FWI_OK;
 }
 

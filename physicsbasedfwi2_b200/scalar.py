@@ -112,9 +112,10 @@ class _Plan:
         return wave.view(nf, -1)[perm].contiguous().view(-1)
 
     def run(self, *, nsteps, adjoint, inj, inj_amp, smp_cell, n_smp, q_write=None, q_read=None,
-            image=None, wave=None) -> torch.Tensor:
+            image=None, wave=None, link=None) -> torch.Tensor:
         """One time loop.  inj = (start, cell, col) lists; returns smp_out [nsteps, S, n_smp].
-        `wave` carries the state of a previous call (see settle()); None starts from rest."""
+        `wave` carries the state of a previous call (see settle()); None starts from rest.
+        `link` (a _lib.SlabLink): the loop exchanges ghost columns with the neighbouring slabs."""
         n_inj = 0 if inj_amp is None else int(inj_amp.shape[2])
         d = self.desc(nsteps, adjoint, n_inj, n_smp)
         if wave is None:
@@ -129,8 +130,12 @@ class _Plan:
         with torch.cuda.device(self.dev):
             fn = _lib.lib().fwi_acoustic_backward if adjoint else _lib.lib().fwi_acoustic_forward
             ev = _lib.time_loop_begin(cur)
-            _lib.check(fn(C.byref(d), C.byref(b), C.c_void_p(cur.cuda_stream)),
-                       "fwi_acoustic_backward" if adjoint else "fwi_acoustic_forward")
+            if link is not None:
+                _lib.check(_lib.lib().fwi_acoustic_run_slab(C.byref(d), C.byref(b), C.byref(link),
+                                                            C.c_void_p(cur.cuda_stream)), "fwi_acoustic_run_slab")
+            else:
+                _lib.check(fn(C.byref(d), C.byref(b), C.c_void_p(cur.cuda_stream)),
+                           "fwi_acoustic_backward" if adjoint else "fwi_acoustic_forward")
             _lib.time_loop_end(cur, ev, "acoustic_adj" if adjoint else "acoustic_fwd", nsteps)
         return smp_out
 
@@ -254,12 +259,14 @@ class Propagator(torch.nn.Module):
     of one K-step segment at a time: memory O(nt/K + K) fields instead of O(nt), one extra forward),
     ``slabs`` (True or a process group: x-slab domain decomposition of every shot over the ranks of
     the group with ghost-zone exchange every ``halo_steps`` inner steps, see slab.py; every rank
-    passes identical arguments and receives the full traces and the full gradient).
+    passes identical arguments and receives the full traces and the full gradient; ``exchange`` =
+    'peer': ghost columns move by peer stores + flags inside the native time loop, 'p2p': by
+    batched NCCL send/recv between halo_steps-long launches).
     """
 
     def __init__(self, model: dict, dx, pml_width=None, survey_pad=None, vpmax=None, *,
                  accuracy: int = 4, loc_mode: str = "trunc", chunk_rows: int = 0, checkpoint_every: int = 0,
-                 slabs=False, halo_steps: int = 8):
+                 slabs=False, halo_steps: int = 8, exchange: str = "peer"):
         super().__init__()
         if not isinstance(model, dict) or "vp" not in model:
             raise RuntimeError("model must be a dict with key 'vp'")
@@ -293,6 +300,9 @@ class Propagator(torch.nn.Module):
             raise RuntimeError("slabs and checkpoint_every cannot be combined")
         self.slabs = None if slabs is False else slabs
         self.halo_steps = int(halo_steps)
+        if exchange not in ("peer", "p2p"):
+            raise RuntimeError("exchange must be 'peer' (in-loop peer stores over NVLink) or 'p2p' (NCCL send/recv)")
+        self.exchange = exchange
 
     def forward(self, source_amplitudes: torch.Tensor, source_locations: torch.Tensor,
                 receiver_locations: torch.Tensor, dt: float) -> torch.Tensor:
@@ -304,7 +314,7 @@ class Propagator(torch.nn.Module):
             from .slab import _SlabFunction
             return _SlabFunction.apply(v, source_amplitudes, x_s, x_r, float(dt), self.dx, self.accuracy,
                                        self.pml_width, self.vpmax, self.loc_mode, self.halo_steps,
-                                       None if self.slabs is True else self.slabs, _Plan)
+                                       None if self.slabs is True else self.slabs, _Plan, self.exchange)
         return _ScalarFunction.apply(v, source_amplitudes, x_s, x_r, float(dt), self.dx, self.accuracy,
                                      self.pml_width, self.vpmax, self.loc_mode, self.chunk_rows, self.checkpoint_every)
 

@@ -17,7 +17,11 @@ time with the ordinary step kernel (csrc/acoustic.cu, through the C ABI): the ou
 columns of a window are never updated, so after k steps the k*order/2 outer columns of an inner
 edge are stale, and after halo_steps steps exactly the ghost zone is.  Then every rank refreshes
 its ghost zones from the neighbours' owned columns - u, u-, pz, py, G columns each - with one
-batched send/recv pair per neighbour (NCCL P2P over NVLink on GPUs; gloo in the CPU tests).
+batched send/recv pair per neighbour (exchange='p2p': NCCL P2P over NVLink on GPUs; gloo in the CPU
+tests) - or, the default on GPUs (exchange='peer'), inside ONE native time loop: a pack kernel
+stores the columns straight into the neighbour's staging buffer through a CUDA-IPC peer mapping
+and raises a flag, an unpack kernel waits for its own flags and fills the ghost columns (csrc/
+acoustic.cu, fwi_acoustic_run_slab); no host synchronisation, no collective.
 Owned columns therefore always hold the values the undecomposed grid would, and the arithmetic
 per cell is that of the single-GPU kernel.  The adjoint is the same recurrence, so it is
 decomposed the same way; snapshots and the image stay local to a window and only the owned
@@ -115,13 +119,70 @@ def exchange_ghosts(wave: torch.Tensor, geo: SlabGeometry, n_fields: int, n_shot
         W[live, :, :, col0 + a:col0 + b] = buf
 
 
+class PeerComm:
+    """Exchange memory of one rank for the in-loop ghost exchange (include/fwi_b200.h, fwi_slab_link):
+    a peer-visible comm block per rank, the two neighbours' blocks mapped through CUDA IPC, and the
+    running exchange count.  Creation is collective over the group."""
+
+    _cache = {}
+
+    def __init__(self, group, slot_floats: int, dev: torch.device):
+        import ctypes as C
+        from . import _lib
+        self.group, self.dev = group, dev
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.bytes = _lib.SLAB_HEADER_BYTES + 4 * slot_floats * 4
+        L = _lib.lib()
+        with torch.cuda.device(dev):
+            ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+            _lib.check(L.fwi_peer_alloc(self.bytes, C.byref(ptr), handle), "fwi_peer_alloc")
+            self.ptr = ptr.value
+            handles = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle.raw), group=group)
+            self.peer = [None, None]
+            for side, r in ((0, self.rank - 1), (1, self.rank + 1)):
+                if 0 <= r < self.world:
+                    q = C.c_void_p()
+                    _lib.check(L.fwi_peer_open(handles[r], C.byref(q)), "fwi_peer_open")
+                    self.peer[side] = q.value
+        self.epoch = 0
+
+    @classmethod
+    def get(cls, group, slot_floats: int, dev: torch.device) -> "PeerComm":
+        key = (id(group) if group is not None else 0, slot_floats, dev.index)
+        if key not in cls._cache:
+            cls._cache[key] = cls(group, slot_floats, dev)
+        return cls._cache[key]
+
+    def link(self, geo: "SlabGeometry", col0: int, nsteps: int):
+        """fwi_slab_link for one native time loop of `nsteps` steps; advances the exchange count."""
+        from . import _lib
+        sl, sr, gl, gr = geo.send_left()[0], geo.send_right()[0], geo.ghost_left()[0], geo.ghost_right()[0]
+        ln = _lib.SlabLink(geo.T, geo.G, int(geo.has_left), int(geo.has_right), col0 + sl, col0 + sr, col0 + gl,
+                           col0 + gr, self.ptr, self.peer[0], self.peer[1], self.epoch & 0xFFFFFFFF, 0)
+        self.epoch += int(_lib.lib().fwi_slab_exchanges(nsteps, geo.T))
+        return ln
+
+    def check(self):
+        """Raises if a flag wait timed out on this rank (a neighbour died or the calls diverged)."""
+        import ctypes as C
+        from . import _lib
+        st = C.c_uint32(0)
+        cur = torch.cuda.current_stream(self.dev)
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.lib().fwi_slab_status(self.ptr, C.c_void_p(cur.cuda_stream), C.byref(st)), "fwi_slab_status")
+        if st.value != 0:
+            type(self)._cache = {k: v for k, v in type(self)._cache.items() if v is not self}
+            raise RuntimeError("slab ghost exchange timed out waiting for a neighbouring rank")
+
+
 class _SlabFunction(torch.autograd.Function):
     """Propagator call on an x-slab decomposition; see the module docstring.  `plan_cls` is the
     per-window time-loop runner: scalar._Plan (the CUDA kernels) in the product."""
 
     @staticmethod
     def forward(ctx, v, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, loc_mode,
-                halo_steps, group, plan_cls):
+                halo_steps, group, plan_cls, exchange="p2p"):
         if not (dist.is_available() and dist.is_initialized()):
             raise RuntimeError("slab decomposition needs an initialised torch.distributed process group")
         world, rank = dist.get_world_size(group), dist.get_rank(group)
@@ -160,21 +221,34 @@ class _SlabFunction(torch.autograd.Function):
         r32 = r_cell.to(torch.int32).contiguous()
         lists = plan.lists(s_cell)
         amp_in = (amp * s_in[None]).contiguous()
-        wave, parts = plan.new_wave(), []
+        comm = None
+        if exchange == "peer" and world > 1:
+            live = 4 if plan.n_fields >= 6 else 2
+            comm = PeerComm.get(group, live * S * plan.nzp * geo.G, dev)
         T = geo.T
-        for t0 in range(0, nti, T):
-            n = min(T, nti - t0)
-            qv = None if q is None else q[t0 * S * plan.stride:(t0 + n) * S * plan.stride]
-            parts.append(plan.run(nsteps=n, adjoint=0, inj=lists, inj_amp=amp_in[t0:t0 + n], smp_cell=r32,
-                                  n_smp=R, q_write=qv, wave=wave))
-            wave = plan.settle(wave, n)
-            if t0 + n < nti:
-                exchange_ghosts(wave, geo, plan.n_fields, S, plan.nzp, plan.pitch, plan.col0, group)
-        rec = torch.cat(parts, 0) * r_own[None]
+        if comm is not None or world == 1:
+            # one native time loop; ghost columns move by peer stores + flags inside it
+            rec = plan.run(nsteps=nti, adjoint=0, inj=lists, inj_amp=amp_in, smp_cell=r32, n_smp=R, q_write=q,
+                           **({"link": comm.link(geo, plan.col0, nti)} if comm is not None else {}))
+            if comm is not None:
+                comm.check()
+        else:
+            wave, parts = plan.new_wave(), []
+            for t0 in range(0, nti, T):
+                n = min(T, nti - t0)
+                qv = None if q is None else q[t0 * S * plan.stride:(t0 + n) * S * plan.stride]
+                parts.append(plan.run(nsteps=n, adjoint=0, inj=lists, inj_amp=amp_in[t0:t0 + n], smp_cell=r32,
+                                      n_smp=R, q_write=qv, wave=wave))
+                wave = plan.settle(wave, n)
+                if t0 + n < nti:
+                    exchange_ghosts(wave, geo, plan.n_fields, S, plan.nzp, plan.pitch, plan.col0, group)
+            rec = torch.cat(parts, 0)
+        rec = rec * r_own[None]
         if world > 1:
             dist.all_reduce(rec, op=dist.ReduceOp.SUM, group=group)
         out = rec[::plan.ratio].contiguous() if plan.ratio > 1 else rec
         ctx.plan, ctx.geo, ctx.group, ctx.q = plan, geo, group, q
+        ctx.comm = comm
         ctx.amp = amp
         ctx.cells = (s_cell, r_cell, s_col)
         ctx.masks = (s_own, r_in)
@@ -202,18 +276,29 @@ class _SlabFunction(torch.autograd.Function):
         image = torch.zeros(plan.n_images * plan.stride, dtype=torch.float32, device=dev) if need_v else None
         s32 = s_cell.to(torch.int32).contiguous()
         rec_lists = plan.lists(r_cell)
-        awave, parts = plan.new_wave(), []
         T = geo.T
-        starts = list(range(0, nti, T))
-        for t0 in reversed(starts):
-            n = min(T, nti - t0)
-            qv = None if not need_v else ctx.q[t0 * S * plan.stride:(t0 + n) * S * plan.stride]
-            parts.append(plan.run(nsteps=n, adjoint=1, inj=rec_lists, inj_amp=g_in[t0:t0 + n], smp_cell=s32,
-                                  n_smp=Ns, q_read=qv, image=image, wave=awave))
-            awave = plan.settle(awave, n)
-            if t0 > 0:
-                exchange_ghosts(awave, geo, plan.n_fields, S, plan.nzp, plan.pitch, plan.col0, group)
-        gs = torch.cat(parts[::-1], 0) * s_own[None]                   # [nti, S, Ns], owner's samples only
+        comm = ctx.comm
+        if comm is not None or geo.world == 1:
+            gs = plan.run(nsteps=nti, adjoint=1, inj=rec_lists, inj_amp=g_in, smp_cell=s32, n_smp=Ns,
+                          q_read=ctx.q if need_v else None, image=image,
+                          **({"link": comm.link(geo, plan.col0, nti)} if comm is not None else {}))
+            if comm is not None:
+                comm.check()
+        else:
+            awave, parts = plan.new_wave(), []
+            # segments aligned to the END of the record, like the native loop's adjoint schedule
+            ends = list(range(nti, 0, -T))
+            for t1 in ends:
+                t0 = max(0, t1 - T)
+                n = t1 - t0
+                qv = None if not need_v else ctx.q[t0 * S * plan.stride:(t0 + n) * S * plan.stride]
+                parts.append(plan.run(nsteps=n, adjoint=1, inj=rec_lists, inj_amp=g_in[t0:t0 + n], smp_cell=s32,
+                                      n_smp=Ns, q_read=qv, image=image, wave=awave))
+                awave = plan.settle(awave, n)
+                if t0 > 0:
+                    exchange_ghosts(awave, geo, plan.n_fields, S, plan.nzp, plan.pitch, plan.col0, group)
+            gs = torch.cat(parts[::-1], 0)
+        gs = gs * s_own[None]                                          # [nti, S, Ns], owner's samples only
         if geo.world > 1:
             dist.all_reduce(gs, op=dist.ReduceOp.SUM, group=group)
         grad_v = grad_s = None
@@ -232,7 +317,7 @@ class _SlabFunction(torch.autograd.Function):
             grad_s = H.resample_up_adjoint(gs, plan.ratio, ctx.src_like.to(dev, torch.float32))
             grad_s = grad_s.to(ctx.src_like.device, ctx.src_like.dtype)
         ctx.q = None
-        return (grad_v, grad_s) + (None,) * 11
+        return (grad_v, grad_s) + (None,) * 12
 
 
 def slab_columns(nyp: int, world: int) -> List[Tuple[int, int]]:

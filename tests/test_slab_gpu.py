@@ -47,7 +47,7 @@ def _gradient(p, dev, **kw):
     return rec.detach().cpu(), vg.grad.cpu(), sg.grad.cpu()
 
 
-def _worker(rank, world, port, T, order, out):
+def _worker(rank, world, port, T, order, out, exchange="peer"):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
@@ -56,7 +56,8 @@ def _worker(rank, world, port, T, order, out):
     try:
         from oracle import cpu_ref as O
         p = _problem(order)
-        rec, gv, gs = _gradient(p, dev, slabs=True, halo_steps=T)
+        rec, gv, gs = _gradient(p, dev, slabs=True, halo_steps=T, exchange=exchange)
+        rec, gv, gs = _gradient(p, dev, slabs=True, halo_steps=T, exchange=exchange)   # twice: the epoch carries over
         r1, gv1, gs1 = _gradient(p, dev)                              # undecomposed, same GPU
         r0, gv0, gs0 = O.acoustic_gradient(p["v"], p["dx"], p["src"], p["x_s"], p["x_r"], p["dt"], grad_rec=p["g"],
                                            order=order, pml_width=p["pw"], dtype=torch.float32)
@@ -84,10 +85,11 @@ def test_segmented_window_plan_on_one_gpu(cuda_lib, T, order):
     assert out[0]["exact"], out[0]
 
 
+@pytest.mark.parametrize("exchange", ["peer", "p2p"])
 @pytest.mark.parametrize("T,order", [(8, 4), (4, 8), (1, 2)])
-def test_two_gpu_slabs_match_oracle_and_single_gpu(cuda_lib, T, order):
+def test_two_gpu_slabs_match_oracle_and_single_gpu(cuda_lib, T, order, exchange):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs (gpurun --gpus 2)")
     out = mp.Manager().dict()
-    mp.spawn(_worker, args=(2, _free_port(), T, order, out), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), T, order, out, exchange), nprocs=2, join=True)
     _check(out, 2)
