@@ -106,13 +106,15 @@ def replicate_pad_adjoint(gpad: torch.Tensor, pad: int) -> torch.Tensor:
     return g[:, pad:-pad].contiguous()
 
 
-def injection_lists(cells_dev: torch.Tensor, nzp: int, pitch: int):
+def injection_lists(cells_dev: torch.Tensor, nzp: int, pitch: int, keep=None):
     """Sorts the per-shot point list by device cell so a work unit finds its points by row range.
 
     cells_dev: [S, n] device cell (z*pitch + col).  Returns (row_start [S, nzp+1] int32 absolute
     offsets into the flat lists, cell [S*n] int32 sorted by (shot, cell), col [S*n] int32 = index
     of the entry within its shot before sorting).  The sort is stable, so duplicate points stay
     adjacent and in their original order: the kernel applies them in that fixed order.
+    `keep` [S, n] bool: points to leave out of the lists altogether (they sort behind the last
+    row of the last shot, where no row range reaches them).
     """
     S, n = cells_dev.shape
     dev = cells_dev.device
@@ -121,6 +123,8 @@ def injection_lists(cells_dev: torch.Tensor, nzp: int, pitch: int):
                 torch.zeros(1, dtype=torch.int32, device=dev), torch.zeros(1, dtype=torch.int32, device=dev))
     per_shot = nzp * pitch
     key = (torch.arange(S, device=dev)[:, None] * per_shot + cells_dev).reshape(-1)
+    if keep is not None:
+        key = torch.where(keep.reshape(-1).to(dev), key, torch.full_like(key, S * per_shot))
     skey, order = torch.sort(key, stable=True)
     bounds = (torch.arange(S, device=dev)[:, None] * per_shot
               + torch.arange(nzp + 1, device=dev)[None, :] * pitch).reshape(-1)

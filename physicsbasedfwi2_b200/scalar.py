@@ -95,8 +95,8 @@ class _Plan:
         """[S, n, 2] metres -> global padded column [S, n] of each point."""
         return H.to_cells(x.to(self.dev), self.dz, self.dy, loc_mode)[..., 1] + self.P
 
-    def lists(self, cell):
-        return H.injection_lists(cell, self.nzp, self.pitch)
+    def lists(self, cell, keep=None):
+        return H.injection_lists(cell, self.nzp, self.pitch, keep)
 
     def new_wave(self) -> torch.Tensor:
         return torch.zeros(int(self.lay.wave_fields) * self.S * self.stride, dtype=torch.float32, device=self.dev)

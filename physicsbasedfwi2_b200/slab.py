@@ -219,7 +219,7 @@ class _SlabFunction(torch.autograd.Function):
         need_v, need_s = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         q = torch.empty(nti * S * plan.stride, dtype=torch.float32, device=dev) if need_v else None
         r32 = r_cell.to(torch.int32).contiguous()
-        lists = plan.lists(s_cell)
+        lists = plan.lists(s_cell, s_in > 0)
         amp_in = (amp * s_in[None]).contiguous()
         comm = None
         if exchange == "peer" and world > 1:
@@ -275,7 +275,7 @@ class _SlabFunction(torch.autograd.Function):
         g_in = (g_in * r_in[None]).contiguous()
         image = torch.zeros(plan.n_images * plan.stride, dtype=torch.float32, device=dev) if need_v else None
         s32 = s_cell.to(torch.int32).contiguous()
-        rec_lists = plan.lists(r_cell)
+        rec_lists = plan.lists(r_cell, r_in > 0)
         T = geo.T
         comm = ctx.comm
         if comm is not None or geo.world == 1:

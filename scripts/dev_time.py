@@ -9,6 +9,9 @@ from physicsbasedfwi2_b200.wavelets import ricker
 S = int(sys.argv[1]); nt = int(sys.argv[2]); reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 w = dict(B.WORKLOADS[os.environ.get("WL", "c2")]); w["nt"] = nt
 if "PML" in os.environ: w["pml"] = int(os.environ["PML"])
+if "NY" in os.environ: w["ny"] = int(os.environ["NY"])
+if "NZ" in os.environ: w["nz"] = int(os.environ["NZ"])
+w.pop("slabs", None)
 if "ORDER" in os.environ: w["order"] = int(os.environ["ORDER"])
 dev = torch.device("cuda:0")
 v = B.synth_model(w).to(dev)

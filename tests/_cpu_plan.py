@@ -48,7 +48,7 @@ class CpuPlan:
     def padded_columns(self, x, loc_mode):
         return H.to_cells(x, self.dz, self.dy, loc_mode)[..., 1] + self.P
 
-    def lists(self, cell):
+    def lists(self, cell, keep=None):      # dropped points carry zero amplitude; the oracle takes a dense list
         return (None, cell.to(torch.int32).contiguous(), None)
 
     def new_wave(self):

@@ -108,3 +108,21 @@ def test_injection_lists_sorted_by_cell_with_row_offsets():
     assert [int(col[e]) for e in dup] == [2, 5]
     start0, c0, col0 = H.injection_lists(cell[:, :0], nzp, pitch)
     assert int(start0.abs().sum()) == 0 and start0.numel() == S * (nzp + 1)
+
+
+def test_injection_lists_leave_out_masked_points():
+    """x-slab windows (slab.py) drop the points outside the window: no row range may reach them."""
+    S, n, nzp, pitch = 2, 12, 10, 32
+    g = torch.Generator().manual_seed(1)
+    cell = torch.randint(0, nzp, (S, n), generator=g) * pitch + torch.randint(0, pitch, (S, n), generator=g)
+    keep = torch.rand(S, n, generator=g) < 0.6
+    start, c, col = H.injection_lists(cell, nzp, pitch, keep)
+    start = start.reshape(S, nzp + 1)
+    seen = []
+    for s in range(S):
+        for row in range(nzp):
+            for e in range(int(start[s, row]), int(start[s, row + 1])):
+                assert int(c[e]) // pitch == row and bool(keep[s, int(col[e])])
+                assert int(cell[s, int(col[e])]) == int(c[e])
+                seen.append((s, int(col[e])))
+    assert sorted(seen) == sorted((s, j) for s in range(S) for j in range(n) if bool(keep[s, j]))
