@@ -33,6 +33,28 @@ struct EParams {
     float *grad;                // [5][S][cells]: l2m lam mu by bz images
 };
 
+// Every kernel of the time loop is launched with programmatic stream serialization: its blocks
+// may start (index arithmetic, parameter loads) while the previous kernel drains, and wait here
+// before touching any field the previous kernel writes.
+__device__ __forceinline__ void pdl_wait() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the next kernel may become resident early
+    asm volatile("griddepcontrol.wait;" ::: "memory");                // ... but nobody reads before the previous grid is done
+}
+
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 constexpr int VY = 0, VZ = 1, SXX = 2, SZZ = 3, SYZ = 4, PSI = 5;
 
 template <int H>
@@ -60,7 +82,8 @@ __device__ __forceinline__ float dminus(const float *f, long long i, long long s
     const long long fs = (long long)p.S * p.cells;                                  \
     const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1); \
     const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1); \
-    (void)fs; (void)ypml; (void)zpml;
+    (void)fs; (void)ypml; (void)zpml;                                               \
+    pdl_wait();
 
 // profile accessors: row 0 a, 1 b (integer nodes), 2 a, 3 b (half nodes)
 #define AZ(i) __ldg(p.pz + (i))
@@ -201,6 +224,7 @@ __global__ void elastic_sample2(const float *a, const float *b, long long cells,
     if (t >= S * n) return;
     const int s = t / n;
     const long long c = (long long)s * cells + __ldg(cell + t);
+    pdl_wait();
     out_a[t] = scale * a[c];
     if (out_b) out_b[t] = scale * b[c];
 }
@@ -211,6 +235,7 @@ __global__ void elastic_sample_sum(const float *a, const float *b, long long cel
     if (t >= S * n) return;
     const int s = t / n;
     const long long c = (long long)s * cells + __ldg(cell + t);
+    pdl_wait();
     out[t] = scale * (a[c] + b[c]);
 }
 // a[cell] += scale * amp_a, b[cell] += scale * amp_b.  One thread per point; points that share a
@@ -224,6 +249,7 @@ __global__ void elastic_inject2(float *a, float *b, long long cells, int S, int 
     if (l & 0x40000000) return;
     const int s = t / n;
     const long long c = (long long)s * cells + __ldg(cell + t);
+    pdl_wait();
     float va = a[c] + scale * __ldg(amp_a + t), vb = b[c] + scale * __ldg(amp_b + t);
     while ((l & 0x3fffffff) != 0) {
         const int k = s * n + (l & 0x3fffffff) - 1;
@@ -271,10 +297,10 @@ void fill(EParams &p, const fwi_elastic_desc *d, const fwi_elastic_buffers *b) {
 
 #define ELASTIC_LAUNCH_H(kern, ...)                                      \
     switch (p.h) {                                                       \
-    case 1: kern<1, ##__VA_ARGS__><<<grid, block, 0, st>>>(p); break;    \
-    case 2: kern<2, ##__VA_ARGS__><<<grid, block, 0, st>>>(p); break;    \
-    case 3: kern<3, ##__VA_ARGS__><<<grid, block, 0, st>>>(p); break;    \
-    default: kern<4, ##__VA_ARGS__><<<grid, block, 0, st>>>(p); break;   \
+    case 1: launch_pdl(kern<1, ##__VA_ARGS__>, grid, block, st, p); break;    \
+    case 2: launch_pdl(kern<2, ##__VA_ARGS__>, grid, block, st, p); break;    \
+    case 3: launch_pdl(kern<3, ##__VA_ARGS__>, grid, block, st, p); break;    \
+    default: launch_pdl(kern<4, ##__VA_ARGS__>, grid, block, st, p); break;   \
     }
 
 }  // namespace
@@ -300,7 +326,7 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
     const long long nrec = (long long)d->n_shots * d->n_rec, nsrc = (long long)d->n_shots * d->n_src;
     for (int n = 0; n < d->nsteps; ++n) {
         if (d->n_rec) {
-            elastic_sample2<<<(unsigned)((nrec + 127) / 128), 128, 0, st>>>(
+            launch_pdl(elastic_sample2, dim3((unsigned)((nrec + 127) / 128)), dim3(128), st,
                 p.f[VY], p.f[VZ], p.cells, d->n_shots, d->n_rec, b->rec_cell, b->rec_out + n * nrec,
                 b->rec_out + ((long long)d->nsteps + n) * nrec, 1.0f);
             fwi::count_launch();
@@ -315,7 +341,7 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
         }
         fwi::count_launch(2);
         if (d->n_src) {
-            elastic_inject2<<<(unsigned)((nsrc + 127) / 128), 128, 0, st>>>(
+            launch_pdl(elastic_inject2, dim3((unsigned)((nsrc + 127) / 128)), dim3(128), st,
                 p.f[SXX], p.f[SZZ], p.cells, d->n_shots, d->n_src, b->src_cell, b->src_link, b->src_amp + n * nsrc,
                 b->src_amp + n * nsrc, p.dt);
             fwi::count_launch();
@@ -342,18 +368,18 @@ extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic
     const long long nrec = (long long)d->n_shots * d->n_rec, nsrc = (long long)d->n_shots * d->n_src;
     for (int n = d->nsteps - 1; n >= 0; --n) {
         if (d->n_src) {
-            elastic_sample_sum<<<(unsigned)((nsrc + 127) / 128), 128, 0, st>>>(
+            launch_pdl(elastic_sample_sum, dim3((unsigned)((nsrc + 127) / 128)), dim3(128), st,
                 p.f[SXX], p.f[SZZ], p.cells, d->n_shots, d->n_src, b->src_cell, b->grad_src + n * nsrc, p.dt);
             fwi::count_launch();
         }
         p.snap = const_cast<float *>(b->snap) + (long long)n * 5 * fld;
-        elastic_b2a<<<grid, block, 0, st>>>(p);
+        launch_pdl(elastic_b2a, grid, block, st, p);
         ELASTIC_LAUNCH_H(elastic_b2b);
-        elastic_b1a<<<grid, block, 0, st>>>(p);
+        launch_pdl(elastic_b1a, grid, block, st, p);
         ELASTIC_LAUNCH_H(elastic_b1b);
         fwi::count_launch(4);
         if (d->n_rec) {
-            elastic_inject2<<<(unsigned)((nrec + 127) / 128), 128, 0, st>>>(
+            launch_pdl(elastic_inject2, dim3((unsigned)((nrec + 127) / 128)), dim3(128), st,
                 p.f[VY], p.f[VZ], p.cells, d->n_shots, d->n_rec, b->rec_cell, b->rec_link, b->grad_rec + n * nrec,
                 b->grad_rec + ((long long)d->nsteps + n) * nrec, 1.0f);
             fwi::count_launch();
