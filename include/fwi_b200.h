@@ -197,6 +197,30 @@ int64_t fwi_elastic_wave_floats(const fwi_elastic_desc *desc);   /* floats in `w
 int fwi_elastic_forward(const fwi_elastic_desc *desc, const fwi_elastic_buffers *buf, void *stream);
 int fwi_elastic_backward(const fwi_elastic_desc *desc, const fwi_elastic_buffers *buf, void *stream);
 
+/* ---- trace misfit fused with its backward ------------------------------------------------ */
+/* Replaces the torch glue between the propagator's output and loss.backward() in every `prop`
+ * method of the reference (models/networks.py:5467-5476, backward :5491):
+ *   d = pred - direct;  m = max_t |d| per trace;  n = d / (m + eps);
+ *   loss = mean |n - obs| (kind 0, torch.nn.L1Loss) or mean (n - obs)^2 (kind 1, MSELoss);
+ *   grad_pred = grad_scale * dloss/dpred.
+ * Arrays are [nt][n_traces] (n_traces = shots * receivers, contiguous).  `direct` may be NULL
+ * (no direct-wave subtraction).  fwi_trace_misfit writes the scalar loss and leaves the per-trace
+ * maxima and sums in `workspace`; fwi_trace_misfit_backward (same desc, arrays and workspace) writes
+ * grad_pred = (*grad_loss) * dloss/dpred, grad_loss a device scalar or NULL (= 1).  Deterministic. */
+typedef struct fwi_misfit_desc {
+    int32_t nt, n_traces;
+    int32_t kind;             /* 0 = L1, 1 = MSE */
+    int32_t normalize;        /* 1: divide every trace by its max |.| + eps (models/networks.py:5468-5470) */
+    float eps;                /* 1e-10 in the reference */
+} fwi_misfit_desc;
+
+int64_t fwi_trace_misfit_workspace_bytes(const fwi_misfit_desc *desc);
+int fwi_trace_misfit(const fwi_misfit_desc *desc, const float *pred, const float *direct, const float *obs,
+                     float *loss, void *workspace, void *stream);
+int fwi_trace_misfit_backward(const fwi_misfit_desc *desc, const float *pred, const float *direct,
+                              const float *obs, const float *grad_loss, float *grad_pred, void *workspace,
+                              void *stream);
+
 /* ---- common ---------------------------------------------------------------------------- */
 
 const char *fwi_last_error(void);     /* thread-local, never NULL */

@@ -8,6 +8,8 @@ sm_100a CUDA behind the C ABI in include/fwi_b200.h; there is no CPU fallback.
 from . import wavelets  # noqa: F401
 from . import scalar  # noqa: F401
 from . import elastic  # noqa: F401
+from . import misfit  # noqa: F401
+from . import slab  # noqa: F401
 from ._lib import build, kernel_launches, lib  # noqa: F401
 
 
@@ -19,4 +21,4 @@ def Propagator(model: dict, dx, *args, **kwargs):
     return scalar.Propagator(model, dx, *args, **kwargs)
 
 
-__all__ = ["scalar", "elastic", "wavelets", "Propagator", "build", "lib", "kernel_launches"]
+__all__ = ["scalar", "elastic", "misfit", "slab", "wavelets", "Propagator", "build", "lib", "kernel_launches"]

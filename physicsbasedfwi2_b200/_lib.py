@@ -13,7 +13,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_HERE, "csrc")
 SO_PATH = os.path.join(_HERE, "libfwi_b200.so")
-_SOURCES = ["common.cu", "acoustic.cu", "elastic.cu", "persist.cu"]
+_SOURCES = ["common.cu", "acoustic.cu", "elastic.cu", "misfit.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
 
@@ -49,6 +49,11 @@ class SlabLink(C.Structure):
 
 
 SLAB_HEADER_BYTES = 256
+
+
+class MisfitDesc(C.Structure):
+    _fields_ = [("nt", C.c_int32), ("n_traces", C.c_int32), ("kind", C.c_int32), ("normalize", C.c_int32),
+                ("eps", C.c_float)]
 
 
 class ElasticDesc(C.Structure):
@@ -124,6 +129,12 @@ def lib() -> C.CDLL:
     L.fwi_slab_status.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]
     L.fwi_slab_exchanges.argtypes = [C.c_int32, C.c_int32]
     L.fwi_slab_exchanges.restype = C.c_int32
+    L.fwi_trace_misfit_workspace_bytes.argtypes = [C.POINTER(MisfitDesc)]
+    L.fwi_trace_misfit_workspace_bytes.restype = C.c_int64
+    L.fwi_trace_misfit.argtypes = [C.POINTER(MisfitDesc)] + [C.c_void_p] * 6
+    L.fwi_trace_misfit.restype = C.c_int
+    L.fwi_trace_misfit_backward.argtypes = [C.POINTER(MisfitDesc)] + [C.c_void_p] * 7
+    L.fwi_trace_misfit_backward.restype = C.c_int
     L.fwi_elastic_wave_floats.argtypes = [C.POINTER(ElasticDesc)]
     L.fwi_elastic_wave_floats.restype = C.c_int64
     for name in ("fwi_elastic_forward", "fwi_elastic_backward"):

@@ -120,3 +120,20 @@ def test_work_table_tiles_the_grid_and_is_balanced(shape):
     assert 1 <= nu.value <= 148 * 16 and ns.value >= nu.value
     if chunk == 0:
         assert mx.value <= 1.1 * mean.value + 6.0
+
+
+def test_misfit_and_slab_entry_points_check_arguments_on_the_host():
+    L = pkg.lib()
+    d = _lib.MisfitDesc(3000, 6 * 576, 0, 1, 1e-10)
+    ws = L.fwi_trace_misfit_workspace_bytes(ctypes.byref(d))
+    assert ws > 0 and ws % (16 * 6 * 576) == 0          # 4 partial arrays of [C][M] words
+    assert L.fwi_trace_misfit_workspace_bytes(ctypes.byref(_lib.MisfitDesc(0, 5, 0, 1, 1e-10))) == -1
+    bad = _lib.MisfitDesc(10, 5, 2, 1, 1e-10)
+    assert L.fwi_trace_misfit(ctypes.byref(bad), 1, None, 1, 1, 1, None) == -1
+    assert b"kind" in L.fwi_last_error()
+    assert L.fwi_slab_exchanges(8000, 8) == 999 and L.fwi_slab_exchanges(8, 8) == 0 and L.fwi_slab_exchanges(9, 8) == 1
+    assert L.fwi_slab_exchanges(0, 8) == 0
+    ad = _lib.AcousticDesc(124, 324, 4, 10, 1, 0, 10, 0, 0, 0, 0, 0, 10.0, 10.0, 1e-3)
+    link = _lib.SlabLink(8, 15, 1, 0, 0, 0, 0, 0, None, None, None, 0, 0)      # ghost_cols != 8 * 2
+    assert L.fwi_acoustic_run_slab(ctypes.byref(ad), ctypes.byref(_lib.AcousticBuffers()), ctypes.byref(link), None) == -1
+    assert b"ghost_cols" in L.fwi_last_error()
