@@ -822,11 +822,17 @@ int fill_units(const std::vector<Col> &cols, const Geom &g, const CostModel &cm,
 // more than n_units units (bisection).
 void build_units(const fwi_acoustic_desc *d, const Geom &g, int n_units, std::vector<Col> &cols,
                  std::vector<Seg> &segs, std::vector<int> &unit_start, int mode = 1) {
-    const CostModel cm = cost_model(g, mode);
+    CostModel cm = cost_model(g, mode);
     list_columns(d, g, cols);
     double total = 0;
     for (const Col &c : cols) total += (c.z1 - c.z0) * cm.rate(c.type) + cm.seg;
-    const double min_unit = 24.0;     // small problems: fewer, fuller units
+    // small problems (less than a few rows of work per resident warp, e.g. the reference's own
+    // 100x300 / 151x200 grids): a launch is latency-bound, so cut the work into the shortest
+    // segments the kernel supports and spread them over as many warps as there are segments
+    // (measured on the 100x300 x 10-shot case: 6.5 / 8.4 us per forward / adjoint launch with
+    // units of >= 6 row-costs and 2-row segments, 11.3 / 11.0 us with 24 and 4)
+    static const double min_unit = env_dbl("FWI_B200_MINUNIT", 6.0);
+    if (total / n_units < 24.0 && g.max_rows == 0 && env_int("FWI_B200_MINROWS", 0) == 0) cm.min_rows = 2;
     if (total / n_units < min_unit) n_units = std::max(1, (int)(total / min_unit));
     if (env_int("FWI_B200_PIECES", 0)) {
         // pieces of about one unit's worth of interior rows

@@ -82,9 +82,51 @@ def full(tag, name):
     return num("dram__bytes_read.sum") + num("dram__bytes_write.sum")
 
 
+def full_multi(tag, name, note):
+    """Several kernels in one report (the elastic time step): one block of KEEP metrics per launch."""
+    rep = os.path.join(OUT, name + ".ncu-rep")
+    if not os.path.exists(rep):
+        return None
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    hdr, units = rows[0], rows[1]
+    out = {}
+    with open(os.path.join(PROF, f"{tag}_{name}.txt"), "w") as f:
+        f.write(f"# ncu --set full --clock-control none --import-source on; {note}\n")
+        for vals in rows[2:]:
+            d = {h: (v, u) for h, u, v in zip(hdr, units, vals)}
+            kn = d.get("Kernel Name", ("?", ""))[0]
+            f.write(f"\n## {kn}\n")
+            for k in KEEP:
+                if k in d:
+                    f.write(f"{k:70s} {d[k][0]:>16s} {d[k][1]}\n")
+
+            def num(k):
+                v, u = d[k]
+                return float(v.replace(",", "")) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
+            out[kn.split("(")[0]] = num("dram__bytes_read.sum") + num("dram__bytes_write.sum")
+    return out
+
+
 if __name__ == "__main__":
     tag = sys.argv[1]
     os.makedirs(PROF, exist_ok=True)
+    if len(sys.argv) > 2 and sys.argv[2] == "elastic":
+        src = os.path.join(OUT, "launches_c3.csv")
+        if os.path.exists(src):
+            os.replace(src, os.path.join(OUT, "launches.csv"))
+            launches(tag + "_c3")
+        tf = full_multi(tag, "el_fwd_full", "C3 elastic forward step: sample, f1, f2, inject (bench.py --workload c3 --nt 40)")
+        ta = full_multi(tag, "el_adj_full", "C3 elastic adjoint step: b2a, b2b, b1a, b1b, inject, sample (bench.py --workload c3 --nt 40)")
+        print(tf, ta)
+        tj = os.path.join(PROF, "traffic.json")
+        cur = json.load(open(tj)) if os.path.exists(tj) else {}
+        if tf and ta:
+            cur["c3"] = {"forward_bytes_per_launch": sum(tf.values()), "adjoint_bytes_per_launch": sum(ta.values()),
+                         "pair_bytes_per_launch": sum(tf.values()) + sum(ta.values()),
+                         "per_kernel": {**tf, **ta}, "source": f"profiles/{tag}_el_*_full.txt"}
+            json.dump(cur, open(tj, "w"), indent=1)
+        sys.exit(0)
     launches(tag)
     t = {n: full(tag, n) for n in ("fwd_full", "adj_full")}
     print(t)
