@@ -51,6 +51,12 @@ WORKLOADS = {
     # exchanged over NVLink every 8 steps (slab.py); snapshot every step; all ranks work on the SAME shots
     "c4dd": dict(nz=1501, ny=3501, dx=10.0, order=8, pml=20, nt=4000, dt=1e-3, freq=8.0, n_rec=876, rec_stride=4,
                  z_acq=2, survey_shots=64, vmin=1500.0, vmax=4500.0, slabs=8),
+    # BASELINE.json configs[4]: end-to-end physics-guided inversion iteration in the Auto22 geometry
+    # (models/networks.py:5339-5358: 151x200, dx 10 m, 8 Hz, 4001 steps of 1 ms, 18 shots x 200 receivers at z = 0,
+    # default deepwave order 4 / pml 10): CNN velocity generator -> propagator -> direct-wave subtraction,
+    # trace normalisation, L1 misfit (fused kernel) -> adjoint -> generator backward -> Adam step.
+    "c5": dict(nz=151, ny=200, dx=10.0, order=4, pml=10, nt=4001, dt=1e-3, freq=8.0, n_rec=200, rec_stride=1,
+               z_acq=0, survey_shots=18, vmin=1500.0, vmax=4500.0, e2e_iteration=True),
     "c1": dict(nz=100, ny=300, dx=10.0, order=4, pml=10, nt=1000, dt=1e-3, freq=15.0, n_rec=101,
                rec_stride=3, z_acq=0, survey_shots=10, vmin=1500.0, vmax=3500.0),
 }
@@ -233,6 +239,163 @@ def bench_config(w, batch, world, name):
 
 
 # ------------------------------------------------------------------------------------------------
+# C5: end-to-end physics-guided iteration (generator CNN + propagator gradient + optimiser step)
+# ------------------------------------------------------------------------------------------------
+def make_generator(n_shots, nz, ny, vmin, vmax):
+    """Encoder-decoder velocity generator with the interface of the reference's Auto22 net
+    (models/networks.py:5136-5294: shot gathers [1, shots, nt/4, receivers] -> 8-number latent ->
+    velocity image [1, 1, nz, ny] scaled into [vmin, vmax]).  Ordinary PyTorch, random weights:
+    the CNN is outside the propagator path and only has to have the right shapes and cost."""
+    import torch.nn as nn
+
+    def down(i, o):
+        return nn.Sequential(nn.Conv2d(i, o, 3, padding=1), nn.BatchNorm2d(o), nn.ReLU(inplace=True),
+                             nn.Conv2d(o, o, 3, padding=1), nn.BatchNorm2d(o), nn.ReLU(inplace=True), nn.MaxPool2d(2, ceil_mode=True))
+
+    def up(i, o):
+        return nn.Sequential(nn.Upsample(scale_factor=2, mode="bilinear", align_corners=False),
+                             nn.Conv2d(i, o, 3, padding=1), nn.BatchNorm2d(o), nn.ReLU(inplace=True),
+                             nn.Conv2d(o, o, 3, padding=1), nn.BatchNorm2d(o), nn.ReLU(inplace=True))
+
+    class Generator(nn.Module):
+        def __init__(self):
+            super().__init__()
+            f = [16, 32, 64, 128]
+            self.enc = nn.Sequential(down(n_shots, f[0]), down(f[0], f[1]), down(f[1], f[2]), down(f[2], f[3]))
+            self.h0, self.w0 = (nz + 7) // 8, (ny + 7) // 8
+            self.to_latent = nn.LazyLinear(8)
+            self.from_latent = nn.Linear(8, f[3] * self.h0 * self.w0)
+            self.dec = nn.Sequential(up(f[3], f[2]), up(f[2], f[1]), up(f[1], f[0]))
+            self.head = nn.Conv2d(f[0], 1, 1)
+
+        def forward(self, gathers):
+            z = self.to_latent(torch.flatten(self.enc(gathers[:, :, 1::4, :]), 1))
+            x = self.from_latent(z).view(-1, 128, self.h0, self.w0)
+            x = self.head(self.dec(x)[:, :, :nz, :ny])
+            return vmin + torch.sigmoid(x) * (vmax - vmin)
+
+    return Generator()
+
+
+def run_c5(args, w, dev, rank, world, local):
+    """One step = one training iteration of the Auto22 path (models/Auto22_model.py:357-362 +
+    models/networks.py:5286-5287, 5445-5493) with the shots sharded over the ranks."""
+    import torch.distributed as dist
+    import physicsbasedfwi2_b200 as pkg
+    from physicsbasedfwi2_b200 import _lib
+    from physicsbasedfwi2_b200.distributed import allreduce_gradient, shard_bounds
+    from physicsbasedfwi2_b200.misfit import normalize_traces, trace_misfit
+    from physicsbasedfwi2_b200.scalar import Propagator
+    from physicsbasedfwi2_b200.wavelets import ricker
+    nz, ny, nt, S, R = w["nz"], w["ny"], w["nt"], w["survey_shots"], w["n_rec"]
+    torch.manual_seed(0)
+    gen = make_generator(S, nz, ny, w["vmin"], w["vmax"]).to(dev)
+    opt = torch.optim.Adam(gen.parameters(), lr=5e-3)
+    lo, hi = shard_bounds(S, rank, world)
+    x_s = torch.zeros(S, 1, 2)
+    x_s[:, 0, 1] = torch.linspace(0, (ny - 1) * w["dx"], S)
+    x_r = torch.zeros(S, R, 2)
+    x_r[:, :, 1] = (torch.arange(R).float() * w["dx"])[None]
+    src = ricker(w["freq"], nt, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1).repeat(1, hi - lo, 1).contiguous().to(dev)
+    xs_d, xr_d = x_s[lo:hi].to(dev), x_r[lo:hi].to(dev)
+    kw = dict(pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"])
+    v_true = synth_model(w).to(dev)
+    with torch.no_grad():
+        observed_all = torch.zeros(nt, S, R, device=dev)      # the data set: all shots, on every rank (network input)
+        observed_all[:, lo:hi] = Propagator({"vp": v_true}, w["dx"], **kw)(src, xs_d, xr_d, w["dt"])
+        if world > 1:
+            dist.all_reduce(observed_all)
+        obs_norm = normalize_traces(observed_all[:, lo:hi]).contiguous()
+        # direct wave of the constant 1500 m/s model: constant across iterations, computed once (SURVEY 8a row a5)
+        direct = Propagator({"vp": torch.full_like(v_true, 1500.0)}, w["dx"], **kw)(src, xs_d, xr_d, w["dt"]).contiguous()
+    gathers_h = observed_all[None].permute(0, 2, 1, 3).contiguous().cpu().pin_memory()     # [1, S, nt, R]
+    gathers_d = gathers_h.to(dev)
+    loss_h = torch.empty(1).pin_memory()
+
+    def iteration(gathers):
+        opt.zero_grad(set_to_none=True)
+        f1 = gen(gathers)                                         # [1, 1, nz, ny]
+        v = f1.detach()[0, 0].clamp(w["vmin"], w["vmax"]).requires_grad_(True)
+        pred = Propagator({"vp": v}, w["dx"], **kw)(src, xs_d, xr_d, w["dt"])
+        loss = trace_misfit(pred, obs_norm, direct, kind="l1") * ((hi - lo) / S)   # mean over ALL traces of the survey
+        loss.backward()
+        g, l = allreduce_gradient(v.grad, loss)
+        f1.backward(g[None, None])                                # models/Auto22_model.py:326
+        opt.step()
+        return l
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, sampler=None):
+        barrier()
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), clocks, out
+
+    def step_e2e():
+        l = iteration(gathers_h.to(dev, non_blocking=True))
+        loss_h.copy_(l.reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return l
+
+    for _ in range(args.warmup):
+        l = iteration(gathers_d)
+    torch.cuda.synchronize()
+    if not math.isfinite(float(l)):
+        raise RuntimeError("non-finite misfit in the C5 iteration")
+    _lib.LOOP_TIMES = []
+    n0 = pkg.kernel_launches()
+    ms, clocks, _ = timed(lambda: iteration(gathers_d), args.steps, ClockSampler(local))
+    launches = pkg.kernel_launches() - n0
+    loops, _lib.LOOP_TIMES = _lib.LOOP_TIMES, None
+    t_fwd = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag.endswith("_fwd")]
+    t_adj = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag.endswith("_adj")]
+    ms_fwd, ms_adj = sum(t_fwd) / len(t_fwd), sum(t_adj) / len(t_adj)
+    from physicsbasedfwi2_b200 import _host
+    nti = nt * _host.inner_step(w["dt"], w["dx"], w["dx"], w["vmax"])[0]
+    work = nz * ny * nti * S * 2
+    ms_e, _, _ = timed(step_e2e, args.steps)
+    if rank == 0:
+        peak, peak_src = hbm_peak()
+        unit_launch = nz * ny * (hi - lo)
+        ach = unit_launch * (B_FWD + B_ADJ) / ((ms_fwd + ms_adj) * 1e-3) / 1e9
+        cfg = bench_config(w, hi - lo, world, "c5")
+        cfg["workload"] += "; one step = generator forward + propagator gradient (fused L1 trace misfit, cached direct wave) + generator backward + Adam"
+        cfg["shots_per_step"] = S
+        cfg["l2"] = "wavefields of a launch fit L2 (latency-bound regime of the reference's own grids)"
+        line = {"metric": "FWI gradient Gcell-updates/s (fwd+adjoint)", "value": round(work * args.steps / (ms * 1e-3) / 1e9, 3),
+                "unit": "Gcell-updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+                "roofline": {"bound": "hbm", "kernel": "acoustic_step_kernel (forward MODE 1 + adjoint MODE 2 pair)",
+                             "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                             "traffic": None, "peak_source": peak_src,
+                             "forward": {"ms_per_launch": round(ms_fwd, 5)}, "adjoint": {"ms_per_launch": round(ms_adj, 5)},
+                             "kernel_share_of_step": round((ms_fwd + ms_adj) * nti * args.steps / ms, 4)},
+                "clocks": clocks, "gpu_launches": int(launches),
+                "e2e": {"value": round(work * args.steps / (ms_e * 1e-3) / 1e9, 3), "unit": "Gcell-updates/s",
+                        "h2d_bytes_per_step": gathers_h.numel() * 4, "d2h_bytes_per_step": 4,
+                        "ms_per_step": round(ms_e / args.steps, 3)}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
 def main():
@@ -278,6 +441,9 @@ def main():
     if L.fwi_device_ok(local) != 0:
         raise RuntimeError(L.fwi_last_error().decode())
 
+    if w.get("e2e_iteration"):
+        return run_c5(args, w, dev, rank, world, local)
+
     nz, ny, nt = w["nz"], w["ny"], w["nt"]
     # shots per step: one q snapshot per inner step per shot must fit HBM next to the wavefields
     P = w["pml"] + w["order"] // 2
@@ -290,7 +456,7 @@ def main():
         cols = (ny + 2 * P) // world + 2 * w["slabs"] * (w["order"] // 2) + 64
         per_shot = (nz + 2 * P) * cols * 4 * (nti + 16)
     free, _ = torch.cuda.mem_get_info(dev)
-    batch = args.shots or max(1, min(16 if w.get("ckpt") else 6, int((0.6 if w.get("ckpt") else 0.88) * free // per_shot)))
+    batch = args.shots or max(1, min(16, w["survey_shots"], int((0.6 if w.get("ckpt") else 0.88) * free // per_shot)))
 
     v_host = synth_model(w).pin_memory()
     x_s_h, x_r_h = synth_survey(w, batch, first_shot=0 if w.get("slabs") else rank * batch)
