@@ -1,0 +1,121 @@
+"""Edge cases of the deepwave-style call on the CUDA path: ragged / degenerate inputs, survey
+cropping, size-independent properties at full size (linearity in the source, shot-permutation
+invariance), and the error behaviour the reference's callers rely on (RuntimeError)."""
+import pytest
+import torch
+
+from tests import _cases as K
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _setup(nz=30, ny=80, S=2, R=9, nt=60, seed=1):
+    v = K.layered_model(nz, ny, seed=seed)
+    x_s, x_r = K.survey(nz, ny, 10.0, S, R, 1, seed=seed + 1)
+    src = K.ricker(20.0, nt, 1e-3, 0.05).reshape(-1, 1, 1).repeat(1, S, 1).contiguous()
+    return v, x_s, x_r, src
+
+
+def test_single_time_sample_and_single_receiver(cuda_lib):
+    from oracle import cpu_ref as O
+    from physicsbasedfwi2_b200.scalar import Propagator
+    v, x_s, x_r, src = _setup(S=1, R=1, nt=1)
+    src = src + 1.0
+    rec = Propagator({"vp": v.to(DEV)}, 10.0)(src.to(DEV), x_s.to(DEV), x_r.to(DEV), 1e-3)
+    assert tuple(rec.shape) == (1, 1, 1)
+    r0 = O.acoustic_forward(v, 10.0, src, x_s, x_r, 1e-3, dtype=torch.float32)
+    assert torch.allclose(rec.cpu(), r0, atol=1e-12)
+
+
+def test_no_receivers_gives_empty_traces(cuda_lib):
+    from physicsbasedfwi2_b200.scalar import Propagator
+    v, x_s, x_r, src = _setup()
+    rec = Propagator({"vp": v.to(DEV)}, 10.0)(src.to(DEV), x_s.to(DEV), x_r[:, :0].to(DEV), 1e-3)
+    assert tuple(rec.shape) == (src.shape[0], 2, 0)
+
+
+def test_gradient_wrt_source_only_and_model_only(cuda_lib):
+    """needs_input_grad combinations: the wavelet-only gradient (models/networks.py:13235-13237)
+    must not need snapshots, the model-only gradient must not return a source gradient."""
+    from oracle import cpu_ref as O
+    from physicsbasedfwi2_b200.scalar import Propagator
+    v, x_s, x_r, src = _setup()
+    g = torch.randn(src.shape[0], 2, 9, generator=torch.Generator().manual_seed(3))
+    _, gv0, gs0 = O.acoustic_gradient(v, 10.0, src, x_s, x_r, 1e-3, grad_rec=g, dtype=torch.float32)
+    sg = src.to(DEV).requires_grad_(True)
+    rec = Propagator({"vp": v.to(DEV)}, 10.0)(sg, x_s.to(DEV), x_r.to(DEV), 1e-3)
+    (rec * g.to(DEV)).sum().backward()
+    assert K.rel_l2(sg.grad, gs0) <= 1e-4
+    vg = v.to(DEV).requires_grad_(True)
+    rec = Propagator({"vp": vg}, 10.0)(src.to(DEV), x_s.to(DEV), x_r.to(DEV), 1e-3)
+    (rec * g.to(DEV)).sum().backward()
+    assert K.rel_l2(vg.grad, gv0) <= 1e-4
+
+
+def test_survey_pad_crops_like_a_smaller_model(cuda_lib):
+    from physicsbasedfwi2_b200.scalar import Propagator
+    nz, ny = 40, 200
+    v = K.layered_model(nz, ny, seed=4)
+    x_s = torch.tensor([[[0.0, 900.0]]])
+    x_r = torch.zeros(1, 11, 2)
+    x_r[0, :, 1] = 800.0 + 20.0 * torch.arange(11)
+    src = K.ricker(20.0, 80, 1e-3, 0.05).reshape(-1, 1, 1)
+    pad = 12
+    rec = Propagator({"vp": v.to(DEV)}, 10.0, survey_pad=pad)(src.to(DEV), x_s.to(DEV), x_r.to(DEV), 1e-3)
+    y0, y1 = 80 - pad, 100 + pad + 1
+    off = torch.tensor([0.0, y0 * 10.0])
+    ref = Propagator({"vp": v[:, y0:y1].contiguous().to(DEV)}, 10.0, vpmax=float(v[:, y0:y1].max()))(
+        src.to(DEV), (x_s - off).to(DEV), (x_r - off).to(DEV), 1e-3)
+    assert torch.equal(rec, ref)
+
+
+def test_linearity_in_the_source_and_shot_permutation_at_c1_size(cuda_lib):
+    """Size-independent properties on the reference's own 100x300 case (BASELINE config 1):
+    traces are linear in the source amplitudes, and permuting the shots permutes the traces and
+    leaves the model gradient unchanged up to summation order."""
+    from physicsbasedfwi2_b200.scalar import Propagator
+    nz, ny, S, R, nt = 100, 300, 10, 101, 400
+    v = K.layered_model(nz, ny, seed=0).to(DEV)
+    x_s, x_r = K.survey(nz, ny, 10.0, S, R, 1, seed=0)
+    src = K.ricker(15.0, nt, 1e-3, 1 / 15.0).reshape(-1, 1, 1).repeat(1, S, 1).contiguous()
+    g = torch.randn(nt, S, R, generator=torch.Generator().manual_seed(1)).to(DEV)
+
+    def run(s, perm=None):
+        xs, xr, gg = x_s, x_r, g
+        if perm is not None:
+            xs, xr, s, gg = x_s[perm], x_r[perm], s[:, perm], g[:, perm]
+        vg = v.clone().requires_grad_(True)
+        rec = Propagator({"vp": vg}, 10.0, vpmax=4000.0)(s.to(DEV), xs.to(DEV), xr.to(DEV), 1e-3)
+        (rec * gg).sum().backward()
+        return rec.detach(), vg.grad
+
+    r1, g1 = run(src)
+    r2, _ = run(-2.5 * src)
+    assert K.rel_l2(r2, -2.5 * r1) <= 1e-6
+    perm = torch.randperm(S, generator=torch.Generator().manual_seed(2))
+    r3, g3 = run(src, perm)
+    assert torch.equal(r3, r1[:, perm.to(DEV)])
+    assert K.rel_l2(g3, g1) <= 1e-6
+
+
+def test_error_behaviour_is_runtime_error(cuda_lib):
+    from physicsbasedfwi2_b200.scalar import Propagator
+    v, x_s, x_r, src = _setup()
+    vd, xs, xr, sd = v.to(DEV), x_s.to(DEV), x_r.to(DEV), src.to(DEV)
+    with pytest.raises(RuntimeError):
+        Propagator({"vp": vd.double()}, 10.0)(sd, xs, xr, 1e-3)                  # dtype
+    with pytest.raises(RuntimeError):
+        Propagator({"vp": vd[None]}, 10.0)(sd, xs, xr, 1e-3)                     # 3-D model
+    with pytest.raises(RuntimeError):
+        Propagator({"vp": vd}, 10.0)(sd[:, :1], xs, xr, 1e-3)                    # shot count mismatch
+    with pytest.raises(RuntimeError):
+        bad = xr.clone()
+        bad[0, 0, 1] = 1e6
+        Propagator({"vp": vd}, 10.0)(sd, xs, bad, 1e-3)                          # receiver outside the model
+    with pytest.raises(RuntimeError):
+        Propagator({"vp": vd}, 10.0, accuracy=5)(sd, xs, xr, 1e-3)
+    with pytest.raises(RuntimeError):
+        Propagator({"vs": vd}, 10.0)
+    with pytest.raises(RuntimeError):
+        Propagator({"vp": vd}, 10.0, slabs=True)(sd, xs, xr, 1e-3)               # no process group
