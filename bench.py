@@ -457,7 +457,8 @@ def main():
         per_shot = (nz + 2 * P) * cols * 4 * (nti + 16)
     free, _ = torch.cuda.mem_get_info(dev)
     # 6 shots per launch is where the C2 kernel pair was tuned (7 fit, but run at 67 % instead of 75 % of the roofline)
-    cap = 16 if (w.get("ckpt") or per_shot < (2 << 30)) else 6
+    full_nt = WORKLOADS[args.workload]["nt"]              # the cap must not change with a --nt override (ncu runs)
+    cap = 16 if (w.get("ckpt") or per_shot * (full_nt / nt) < (2 << 30)) else 6
     batch = args.shots or max(1, min(cap, w["survey_shots"], int((0.6 if w.get("ckpt") else 0.88) * free // per_shot)))
 
     v_host = synth_model(w).pin_memory()

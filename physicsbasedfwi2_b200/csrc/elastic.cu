@@ -16,6 +16,8 @@
 // multiplications and of the memory-variable recursions, imaging sums, and the fields Y that the
 // transposed difference operators act on), B2b / B1b gather (D+)^T = -D-, (D-)^T = -D+ of Y.
 // One thread per cell; these kernels are HBM/L2 bound and use no tensor cores.
+#include <stdlib.h>
+
 #include "common.h"
 
 namespace {
@@ -295,6 +297,13 @@ void fill(EParams &p, const fwi_elastic_desc *d, const fwi_elastic_buffers *b) {
     p.scratch = b->scratch; p.grad = b->grad; p.snap = nullptr;
 }
 
+// thread-block shape of the stencil kernels (x along y, the fast axis); tuning knobs for scripts/
+dim3 block_shape() {
+    static const int bx = getenv("FWI_B200_EL_BX") ? atoi(getenv("FWI_B200_EL_BX")) : 32;
+    static const int by = getenv("FWI_B200_EL_BY") ? atoi(getenv("FWI_B200_EL_BY")) : 8;
+    return dim3(bx, by);
+}
+
 #define ELASTIC_LAUNCH_H(kern, ...)                                      \
     switch (p.h) {                                                       \
     case 1: launch_pdl(kern<1, ##__VA_ARGS__>, grid, block, st, p); break;    \
@@ -320,8 +329,8 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     EParams p;
     fill(p, d, b);
-    const dim3 block(32, 8);
-    const dim3 grid((d->nyp - 2 * p.h + 31) / 32, (d->nzp - 2 * p.h + 7) / 8, d->n_shots);
+    const dim3 block = block_shape();
+    const dim3 grid((d->nyp - 2 * p.h + block.x - 1) / block.x, (d->nzp - 2 * p.h + block.y - 1) / block.y, d->n_shots);
     const long long fld = (long long)d->n_shots * p.cells;
     const long long nrec = (long long)d->n_shots * d->n_rec, nsrc = (long long)d->n_shots * d->n_src;
     for (int n = 0; n < d->nsteps; ++n) {
@@ -362,8 +371,8 @@ extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     EParams p;
     fill(p, d, b);
-    const dim3 block(32, 8);
-    const dim3 grid((d->nyp - 2 * p.h + 31) / 32, (d->nzp - 2 * p.h + 7) / 8, d->n_shots);
+    const dim3 block = block_shape();
+    const dim3 grid((d->nyp - 2 * p.h + block.x - 1) / block.x, (d->nzp - 2 * p.h + block.y - 1) / block.y, d->n_shots);
     const long long fld = (long long)d->n_shots * p.cells;
     const long long nrec = (long long)d->n_shots * d->n_rec, nsrc = (long long)d->n_shots * d->n_src;
     for (int n = d->nsteps - 1; n >= 0; --n) {

@@ -136,6 +136,8 @@ if __name__ == "__main__":
             open(os.path.join(PROF, f"{tag}_{n}.txt"), "w").write(open(p).read())
     if t["fwd_full"] and t["adj_full"]:
         # dram bytes per launch of the forward + adjoint pair (what roofline.achieved is quoted over)
-        json.dump({"c2": {"forward_bytes_per_launch": t["fwd_full"], "adjoint_bytes_per_launch": t["adj_full"],
-                          "pair_bytes_per_launch": t["fwd_full"] + t["adj_full"], "source": f"profiles/{tag}_*_full.txt"}},
-                  open(os.path.join(PROF, "traffic.json"), "w"), indent=1)
+        tj = os.path.join(PROF, "traffic.json")
+        cur = json.load(open(tj)) if os.path.exists(tj) else {}
+        cur["c2"] = {"forward_bytes_per_launch": t["fwd_full"], "adjoint_bytes_per_launch": t["adj_full"],
+                     "pair_bytes_per_launch": t["fwd_full"] + t["adj_full"], "source": f"profiles/{tag}_*_full.txt"}
+        json.dump(cur, open(tj, "w"), indent=1)
