@@ -83,3 +83,31 @@ def trace_misfit(pred: torch.Tensor, observed: torch.Tensor, direct: Optional[to
 def normalize_traces(rec: torch.Tensor, eps: float = 1e-10) -> torch.Tensor:
     """The once-per-call normalisation of the observed data (models/networks.py:5418-5419)."""
     return rec / (rec.abs().amax(dim=0, keepdim=True) + eps)
+
+
+class DirectWave:
+    """The direct-wave shot of the reference (``receiver_amplitudes_cte``, models/networks.py:5408-5411):
+    a forward run on a constant 1500 m/s model with the survey's geometry.  The reference recomputes
+    it on every call of ``prop`` although nothing it depends on changes between iterations (a third
+    of its propagator time in Auto22); this object recomputes it only when the
+    geometry, the wavelet or the grid changes."""
+
+    def __init__(self, velocity: float = 1500.0):
+        self.velocity = float(velocity)
+        self._key = None
+        self._val = None
+
+    def __call__(self, model_shape, dx, source_amplitudes, x_s, x_r, dt, device=None, **propagator_kwargs):
+        from .scalar import Propagator
+        dev = torch.device(device) if device is not None else source_amplitudes.device
+        key = (tuple(model_shape), str(dx), float(dt), str(dev), tuple(sorted(propagator_kwargs.items())))
+        same = (self._key is not None and self._key[0] == key
+                and all(a.shape == b.shape and torch.equal(a, b.to(a.device))
+                        for a, b in zip(self._key[1], (source_amplitudes, x_s, x_r))))
+        if not same:
+            const = torch.full(tuple(model_shape), self.velocity, dtype=torch.float32, device=dev)
+            with torch.no_grad():
+                self._val = Propagator({"vp": const}, dx, **propagator_kwargs)(
+                    source_amplitudes.detach().to(dev), x_s.to(dev), x_r.to(dev), dt).contiguous()
+            self._key = (key, tuple(t.detach().clone() for t in (source_amplitudes, x_s, x_r)))
+        return self._val

@@ -63,3 +63,21 @@ def test_rejects_cpu_tensors_and_bad_shapes(cuda_lib):
         trace_misfit(torch.zeros(4, 1, 2, device=dev), torch.zeros(4, 1, 1, device=dev))
     with pytest.raises(RuntimeError):
         trace_misfit(torch.zeros(4, 1, 1, device=dev), torch.zeros(4, 1, 1, device=dev), kind="huber")
+
+
+def test_direct_wave_is_computed_once_per_geometry(cuda_lib):
+    import physicsbasedfwi2_b200 as pkg
+    from physicsbasedfwi2_b200.misfit import DirectWave
+    from physicsbasedfwi2_b200.scalar import Propagator
+    dev = torch.device("cuda:0")
+    x_s, x_r = K.survey(30, 60, 10.0, 2, 7, 1, seed=1)
+    src = K.ricker(20.0, 50, 1e-3, 0.05).reshape(-1, 1, 1).repeat(1, 2, 1).contiguous().to(dev)
+    dw = DirectWave()
+    a = dw((30, 60), 10.0, src, x_s, x_r, 1e-3)
+    n0 = pkg.kernel_launches()
+    b = dw((30, 60), 10.0, src, x_s, x_r, 1e-3)
+    assert pkg.kernel_launches() == n0 and b is a                          # cached: no kernel ran
+    ref = Propagator({"vp": torch.full((30, 60), 1500.0, device=dev)}, 10.0)(src, x_s.to(dev), x_r.to(dev), 1e-3)
+    assert torch.equal(a, ref)
+    c = dw((30, 60), 10.0, src, x_s + 10.0, x_r, 1e-3)                     # moved sources: recomputed
+    assert pkg.kernel_launches() > n0 and not torch.equal(c, a)
