@@ -187,7 +187,7 @@ typedef struct fwi_elastic_buffers {
     float *rec_out;           /* [2][nsteps][n_shots][n_rec]: vy, vz recorded before each step (forward) */
     float *snap;              /* [nsteps][5][n_shots][nzp][nyp] fy fz e1 e2 e3: written by forward when not
                                  NULL, read by backward */
-    float *scratch;           /* [4][n_shots][nzp][nyp] zero on entry (backward) */
+    float *scratch;           /* [8][n_shots][nzp][nyp] zero on entry (backward) */
     float *grad;              /* [5][n_shots][nzp][nyp] zero on entry: images for l2m lam mu by bz (backward) */
     const float *grad_rec;    /* [2][nsteps][n_shots][n_rec] dJ/d(rec_out) (backward) */
     float *grad_src;          /* [nsteps][n_shots][n_src] dJ/d(src_amp) (backward) */

@@ -33,6 +33,7 @@ struct EParams {
     float *snap;                // this step's [5][S][cells]: fy fz e1 e2 e3 (NULL: not stored / read)
     float *scratch;             // [4][S][cells]
     float *grad;                // [5][S][cells]: l2m lam mu by bz images
+    float *psi_in[8], *psi_out[8];  // fused adjoint: memory variables read / written this step (ping-pong)
 };
 
 // Every kernel of the time loop is launched with programmatic stream serialization: its blocks
@@ -218,6 +219,133 @@ __global__ void __launch_bounds__(256) elastic_b1b(const EParams p) {
     p.f[SZZ][o] = p.f[SZZ][o] - dminus<H>(y4, c0, p.nyp, p.cz);
 }
 
+// ---- fused adjoint kernels ------------------------------------------------------------------
+// B2 = B2a + B2b and B1 = B1a + B1b in one kernel each: a CTA evaluates the pointwise stage on its
+// 64 x 32 tile plus a halo of H cells, keeps the four fields Y the transposed differences act on in
+// shared memory, and gathers them for its own cells.  The `scratch` round trip of the two-kernel
+// form (4 fields written and read back per half step) disappears.  Halo cells need the memory
+// variables of the neighbouring tile as they were BEFORE this step, so those are double-buffered
+// (psi_in / psi_out, swapped every step; only PML cells ever touch them).
+constexpr int kTX = 64, kTZ = 32;
+
+template <int H>
+__device__ __forceinline__ float sm_dplus(const float *y, int st, const float *c) {
+    float s = c[0] * (y[st] - y[0]);
+#pragma unroll
+    for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (y[k * st] - y[-(k - 1) * st]);
+    return s;
+}
+template <int H>
+__device__ __forceinline__ float sm_dminus(const float *y, int st, const float *c) {
+    float s = c[0] * (y[0] - y[-st]);
+#pragma unroll
+    for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (y[(k - 1) * st] - y[-k * st]);
+    return s;
+}
+
+template <int H, int NT>
+__global__ void __launch_bounds__(NT) elastic_b2_fused(const EParams p) {
+    constexpr int SX = kTX + 2 * H, SZ = kTZ + 2 * H;
+    __shared__ float Y[4][SZ * SX];
+    const int s = blockIdx.z;
+    const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + p.h;     // first own cell
+    const long long fs = (long long)p.S * p.cells, so = (long long)s * p.cells;
+    pdl_wait();
+    for (int t = threadIdx.x; t < SX * SZ; t += NT) {
+        const int lz = t / SX, lx = t - lz * SX;
+        const int i = i0 - H + lz, j = j0 - H + lx;
+        float y1 = 0.f, y2 = 0.f, y3 = 0.f, y4 = 0.f;
+        if (i >= p.h && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h) {
+            const bool own = lz >= H && lz < H + kTZ && lx >= H && lx < H + kTX;
+            const long long c0 = (long long)i * p.nyp + j, o = so + c0;
+            const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1);
+            const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1);
+            const float asxx = p.f[SXX][o], aszz = p.f[SZZ][o], asyz = p.f[SYZ][o];
+            const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
+            const float ae1 = p.dt * (l2m * asxx + lam * aszz), ae2 = p.dt * (lam * asxx + l2m * aszz), ae3 = (p.dt * mu) * asyz;
+            if (own) {
+                const float e1 = __ldcs(p.snap + 2 * fs + o), e2 = __ldcs(p.snap + 3 * fs + o), e3 = __ldcs(p.snap + 4 * fs + o);
+                p.grad[o] = p.grad[o] + p.dt * (asxx * e1 + aszz * e2);
+                p.grad[fs + o] = p.grad[fs + o] + p.dt * (asxx * e2 + aszz * e1);
+                p.grad[2 * fs + o] = p.grad[2 * fs + o] + p.dt * (asyz * e3);
+            }
+            y1 = ae1; y2 = ae2; y3 = ae3; y4 = ae3;
+            if (ypml) {
+                const float x4 = ae1 + p.psi_in[4][o]; y1 = ae1 + AY(j) * x4;
+                const float x7 = ae3 + p.psi_in[7][o]; y4 = ae3 + AYH(j) * x7;
+                if (own) { p.psi_out[4][o] = BY(j) * x4; p.psi_out[7][o] = BYH(j) * x7; }
+            }
+            if (zpml) {
+                const float x5 = ae2 + p.psi_in[5][o]; y2 = ae2 + AZ(i) * x5;
+                const float x6 = ae3 + p.psi_in[6][o]; y3 = ae3 + AZH(i) * x6;
+                if (own) { p.psi_out[5][o] = BZ(i) * x5; p.psi_out[6][o] = BZH(i) * x6; }
+            }
+        }
+        Y[0][t] = y1; Y[1][t] = y2; Y[2][t] = y3; Y[3][t] = y4;
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < kTX * kTZ; t += NT) {
+        const int tz = t / kTX, tx = t - tz * kTX;
+        const int i = i0 + tz, j = j0 + tx;
+        if (i >= p.nzp - p.h || j >= p.nyp - p.h) continue;
+        const long long o = so + (long long)i * p.nyp + j;
+        const int l = (tz + H) * SX + tx + H;
+        p.f[VY][o] = p.f[VY][o] - (sm_dplus<H>(&Y[0][l], 1, p.cy) + sm_dminus<H>(&Y[2][l], SX, p.cz));
+        p.f[VZ][o] = p.f[VZ][o] - (sm_dplus<H>(&Y[1][l], SX, p.cz) + sm_dminus<H>(&Y[3][l], 1, p.cy));
+    }
+}
+
+template <int H, int NT>
+__global__ void __launch_bounds__(NT) elastic_b1_fused(const EParams p) {
+    constexpr int SX = kTX + 2 * H, SZ = kTZ + 2 * H;
+    __shared__ float Y[4][SZ * SX];
+    const int s = blockIdx.z;
+    const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + p.h;
+    const long long fs = (long long)p.S * p.cells, so = (long long)s * p.cells;
+    pdl_wait();
+    for (int t = threadIdx.x; t < SX * SZ; t += NT) {
+        const int lz = t / SX, lx = t - lz * SX;
+        const int i = i0 - H + lz, j = j0 - H + lx;
+        float y1 = 0.f, y2 = 0.f, y3 = 0.f, y4 = 0.f;
+        if (i >= p.h && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h) {
+            const bool own = lz >= H && lz < H + kTZ && lx >= H && lx < H + kTX;
+            const long long c0 = (long long)i * p.nyp + j, o = so + c0;
+            const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1);
+            const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1);
+            const float avy = p.f[VY][o], avz = p.f[VZ][o];
+            const float agy = (p.dt * __ldg(p.by + c0)) * avy, agz = (p.dt * __ldg(p.bz + c0)) * avz;
+            if (own) {
+                const float fy = __ldcs(p.snap + o), fz = __ldcs(p.snap + fs + o);
+                p.grad[3 * fs + o] = p.grad[3 * fs + o] + p.dt * (avy * fy);
+                p.grad[4 * fs + o] = p.grad[4 * fs + o] + p.dt * (avz * fz);
+            }
+            y1 = agy; y2 = agy; y3 = agz; y4 = agz;
+            if (ypml) {
+                const float x0 = agy + p.psi_in[0][o]; y1 = agy + AYH(j) * x0;
+                const float x2 = agz + p.psi_in[2][o]; y3 = agz + AY(j) * x2;
+                if (own) { p.psi_out[0][o] = BYH(j) * x0; p.psi_out[2][o] = BY(j) * x2; }
+            }
+            if (zpml) {
+                const float x1 = agy + p.psi_in[1][o]; y2 = agy + AZ(i) * x1;
+                const float x3 = agz + p.psi_in[3][o]; y4 = agz + AZH(i) * x3;
+                if (own) { p.psi_out[1][o] = BZ(i) * x1; p.psi_out[3][o] = BZH(i) * x3; }
+            }
+        }
+        Y[0][t] = y1; Y[1][t] = y2; Y[2][t] = y3; Y[3][t] = y4;
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < kTX * kTZ; t += NT) {
+        const int tz = t / kTX, tx = t - tz * kTX;
+        const int i = i0 + tz, j = j0 + tx;
+        if (i >= p.nzp - p.h || j >= p.nyp - p.h) continue;
+        const long long o = so + (long long)i * p.nyp + j;
+        const int l = (tz + H) * SX + tx + H;
+        p.f[SXX][o] = p.f[SXX][o] - sm_dminus<H>(&Y[0][l], 1, p.cy);
+        p.f[SYZ][o] = p.f[SYZ][o] - (sm_dplus<H>(&Y[1][l], SX, p.cz) + sm_dplus<H>(&Y[2][l], 1, p.cy));
+        p.f[SZZ][o] = p.f[SZZ][o] - sm_dminus<H>(&Y[3][l], SX, p.cz);
+    }
+}
+
 // ---- point kernels: one thread per shot walks that shot's list (fixed order: deterministic) ----
 // out[k][s][r] = field_k[s][cell[s][r]] for k = 0 (a) and 1 (b), scaled
 __global__ void elastic_sample2(const float *a, const float *b, long long cells, int S, int n, const int *cell,
@@ -375,6 +503,11 @@ extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic
     const dim3 grid((d->nyp - 2 * p.h + block.x - 1) / block.x, (d->nzp - 2 * p.h + block.y - 1) / block.y, d->n_shots);
     const long long fld = (long long)d->n_shots * p.cells;
     const long long nrec = (long long)d->n_shots * d->n_rec, nsrc = (long long)d->n_shots * d->n_src;
+    // fused adjoint (default): B2a+B2b and B1a+B1b as one kernel each; FWI_B200_EL_FUSED=0 keeps the four-kernel form
+    static const bool fused = !(getenv("FWI_B200_EL_FUSED") && atoi(getenv("FWI_B200_EL_FUSED")) == 0);
+    static const int fnt = getenv("FWI_B200_EL_NT") ? atoi(getenv("FWI_B200_EL_NT")) : 512;
+    const dim3 fblock(fnt == 256 || fnt == 1024 ? fnt : 512);
+    const dim3 fgrid((d->nyp - 2 * p.h + kTX - 1) / kTX, (d->nzp - 2 * p.h + kTZ - 1) / kTZ, d->n_shots);
     for (int n = d->nsteps - 1; n >= 0; --n) {
         if (d->n_src) {
             launch_pdl(elastic_sample_sum, dim3((unsigned)((nsrc + 127) / 128)), dim3(128), st,
@@ -382,11 +515,26 @@ extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic
             fwi::count_launch();
         }
         p.snap = const_cast<float *>(b->snap) + (long long)n * 5 * fld;
-        launch_pdl(elastic_b2a, grid, block, st, p);
-        ELASTIC_LAUNCH_H(elastic_b2b);
-        launch_pdl(elastic_b1a, grid, block, st, p);
-        ELASTIC_LAUNCH_H(elastic_b1b);
-        fwi::count_launch(4);
+        if (fused) {
+            // memory variables ping-pong between the wave workspace and `scratch` (see elastic_b2_fused)
+            const int par = (d->nsteps - 1 - n) & 1;
+            for (int k = 0; k < 8; ++k) {
+                float *a = p.f[PSI + k], *c = b->scratch + k * fld;
+                p.psi_in[k] = par ? c : a;
+                p.psi_out[k] = par ? a : c;
+            }
+            const dim3 block = fblock, grid = fgrid;
+            if (fnt == 256) { ELASTIC_LAUNCH_H(elastic_b2_fused, 256); ELASTIC_LAUNCH_H(elastic_b1_fused, 256); }
+            else if (fnt == 1024) { ELASTIC_LAUNCH_H(elastic_b2_fused, 1024); ELASTIC_LAUNCH_H(elastic_b1_fused, 1024); }
+            else { ELASTIC_LAUNCH_H(elastic_b2_fused, 512); ELASTIC_LAUNCH_H(elastic_b1_fused, 512); }
+            fwi::count_launch(2);
+        } else {
+            launch_pdl(elastic_b2a, grid, block, st, p);
+            ELASTIC_LAUNCH_H(elastic_b2b);
+            launch_pdl(elastic_b1a, grid, block, st, p);
+            ELASTIC_LAUNCH_H(elastic_b1b);
+            fwi::count_launch(4);
+        }
         if (d->n_rec) {
             launch_pdl(elastic_inject2, dim3((unsigned)((nrec + 127) / 128)), dim3(128), st,
                 p.f[VY], p.f[VZ], p.cells, d->n_shots, d->n_rec, b->rec_cell, b->rec_link, b->grad_rec + n * nrec,

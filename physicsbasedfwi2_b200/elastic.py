@@ -158,7 +158,7 @@ class _ElasticFunction(torch.autograd.Function):
         L = _lib.lib()
         cells = desc.nzp * desc.nyp
         wave = torch.zeros(int(L.fwi_elastic_wave_floats(C.byref(desc))), dtype=torch.float32, device=dev)
-        scratch = torch.zeros(4 * S * cells, dtype=torch.float32, device=dev)
+        scratch = torch.zeros(8 * S * cells, dtype=torch.float32, device=dev)
         grad = torch.zeros(5, S, desc.nzp, desc.nyp, dtype=torch.float32, device=dev)
         gsrc = torch.zeros(nti, S, Ns, dtype=torch.float32, device=dev)
         b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
