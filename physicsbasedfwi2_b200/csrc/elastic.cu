@@ -244,105 +244,147 @@ __device__ __forceinline__ float sm_dminus(const float *y, int st, const float *
 }
 
 template <int H, int NT>
-__global__ void __launch_bounds__(NT) elastic_b2_fused(const EParams p) {
+__global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b2_fused(const EParams p) {
     constexpr int SX = kTX + 2 * H, SZ = kTZ + 2 * H;
+    constexpr int N1 = (SX * SZ + NT - 1) / NT, N2 = (kTX * kTZ) / NT;
+    static_assert((kTX * kTZ) % NT == 0, "tile must be a multiple of the CTA size");
     __shared__ float Y[4][SZ * SX];
     const int s = blockIdx.z;
     const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + p.h;     // first own cell
     const long long fs = (long long)p.S * p.cells, so = (long long)s * p.cells;
     pdl_wait();
-    for (int t = threadIdx.x; t < SX * SZ; t += NT) {
+    // stage 1: the fields Y the transposed differences act on, for the tile and its halo (loads only,
+    // apart from the memory variables of own PML cells)
+#pragma unroll
+    for (int q = 0; q < N1; ++q) {
+        const int t = threadIdx.x + q * NT;
+        if (t >= SX * SZ) break;
         const int lz = t / SX, lx = t - lz * SX;
         const int i = i0 - H + lz, j = j0 - H + lx;
         float y1 = 0.f, y2 = 0.f, y3 = 0.f, y4 = 0.f;
         if (i >= p.h && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h) {
-            const bool own = lz >= H && lz < H + kTZ && lx >= H && lx < H + kTX;
             const long long c0 = (long long)i * p.nyp + j, o = so + c0;
             const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1);
             const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1);
-            const float asxx = p.f[SXX][o], aszz = p.f[SZZ][o], asyz = p.f[SYZ][o];
+            const float asxx = __ldg(p.f[SXX] + o), aszz = __ldg(p.f[SZZ] + o), asyz = __ldg(p.f[SYZ] + o);
             const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
             const float ae1 = p.dt * (l2m * asxx + lam * aszz), ae2 = p.dt * (lam * asxx + l2m * aszz), ae3 = (p.dt * mu) * asyz;
-            if (own) {
-                const float e1 = __ldcs(p.snap + 2 * fs + o), e2 = __ldcs(p.snap + 3 * fs + o), e3 = __ldcs(p.snap + 4 * fs + o);
-                p.grad[o] = p.grad[o] + p.dt * (asxx * e1 + aszz * e2);
-                p.grad[fs + o] = p.grad[fs + o] + p.dt * (asxx * e2 + aszz * e1);
-                p.grad[2 * fs + o] = p.grad[2 * fs + o] + p.dt * (asyz * e3);
-            }
             y1 = ae1; y2 = ae2; y3 = ae3; y4 = ae3;
-            if (ypml) {
-                const float x4 = ae1 + p.psi_in[4][o]; y1 = ae1 + AY(j) * x4;
-                const float x7 = ae3 + p.psi_in[7][o]; y4 = ae3 + AYH(j) * x7;
-                if (own) { p.psi_out[4][o] = BY(j) * x4; p.psi_out[7][o] = BYH(j) * x7; }
-            }
-            if (zpml) {
-                const float x5 = ae2 + p.psi_in[5][o]; y2 = ae2 + AZ(i) * x5;
-                const float x6 = ae3 + p.psi_in[6][o]; y3 = ae3 + AZH(i) * x6;
-                if (own) { p.psi_out[5][o] = BZ(i) * x5; p.psi_out[6][o] = BZH(i) * x6; }
+            if (ypml || zpml) {
+                const bool own = lz >= H && lz < H + kTZ && lx >= H && lx < H + kTX;
+                if (ypml) {
+                    const float x4 = ae1 + p.psi_in[4][o]; y1 = ae1 + AY(j) * x4;
+                    const float x7 = ae3 + p.psi_in[7][o]; y4 = ae3 + AYH(j) * x7;
+                    if (own) { p.psi_out[4][o] = BY(j) * x4; p.psi_out[7][o] = BYH(j) * x7; }
+                }
+                if (zpml) {
+                    const float x5 = ae2 + p.psi_in[5][o]; y2 = ae2 + AZ(i) * x5;
+                    const float x6 = ae3 + p.psi_in[6][o]; y3 = ae3 + AZH(i) * x6;
+                    if (own) { p.psi_out[5][o] = BZ(i) * x5; p.psi_out[6][o] = BZH(i) * x6; }
+                }
             }
         }
         Y[0][t] = y1; Y[1][t] = y2; Y[2][t] = y3; Y[3][t] = y4;
     }
-    __syncthreads();
-    for (int t = threadIdx.x; t < kTX * kTZ; t += NT) {
+    // stage 2 operands that do not depend on stage 1: fetched before the barrier so they are in flight
+    float sx[N2], sz[N2], sy[N2], e1[N2], e2[N2], e3[N2], g0[N2], g1[N2], g2[N2], vy[N2], vz[N2];
+    long long oo[N2];
+#pragma unroll
+    for (int q = 0; q < N2; ++q) {
+        const int t = threadIdx.x + q * NT;
         const int tz = t / kTX, tx = t - tz * kTX;
         const int i = i0 + tz, j = j0 + tx;
-        if (i >= p.nzp - p.h || j >= p.nyp - p.h) continue;
-        const long long o = so + (long long)i * p.nyp + j;
+        const bool in = i < p.nzp - p.h && j < p.nyp - p.h;
+        const long long o = so + (long long)(in ? i : p.h) * p.nyp + (in ? j : p.h);
+        oo[q] = in ? o : -1;
+        sx[q] = __ldg(p.f[SXX] + o); sz[q] = __ldg(p.f[SZZ] + o); sy[q] = __ldg(p.f[SYZ] + o);
+        e1[q] = __ldcs(p.snap + 2 * fs + o); e2[q] = __ldcs(p.snap + 3 * fs + o); e3[q] = __ldcs(p.snap + 4 * fs + o);
+        g0[q] = p.grad[o]; g1[q] = p.grad[fs + o]; g2[q] = p.grad[2 * fs + o];
+        vy[q] = p.f[VY][o]; vz[q] = p.f[VZ][o];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < N2; ++q) {
+        if (oo[q] < 0) continue;
+        const long long o = oo[q];
+        const int t = threadIdx.x + q * NT;
+        const int tz = t / kTX, tx = t - tz * kTX;
         const int l = (tz + H) * SX + tx + H;
-        p.f[VY][o] = p.f[VY][o] - (sm_dplus<H>(&Y[0][l], 1, p.cy) + sm_dminus<H>(&Y[2][l], SX, p.cz));
-        p.f[VZ][o] = p.f[VZ][o] - (sm_dplus<H>(&Y[1][l], SX, p.cz) + sm_dminus<H>(&Y[3][l], 1, p.cy));
+        p.grad[o] = g0[q] + p.dt * (sx[q] * e1[q] + sz[q] * e2[q]);
+        p.grad[fs + o] = g1[q] + p.dt * (sx[q] * e2[q] + sz[q] * e1[q]);
+        p.grad[2 * fs + o] = g2[q] + p.dt * (sy[q] * e3[q]);
+        p.f[VY][o] = vy[q] - (sm_dplus<H>(&Y[0][l], 1, p.cy) + sm_dminus<H>(&Y[2][l], SX, p.cz));
+        p.f[VZ][o] = vz[q] - (sm_dplus<H>(&Y[1][l], SX, p.cz) + sm_dminus<H>(&Y[3][l], 1, p.cy));
     }
 }
 
 template <int H, int NT>
-__global__ void __launch_bounds__(NT) elastic_b1_fused(const EParams p) {
+__global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b1_fused(const EParams p) {
     constexpr int SX = kTX + 2 * H, SZ = kTZ + 2 * H;
+    constexpr int N1 = (SX * SZ + NT - 1) / NT, N2 = (kTX * kTZ) / NT;
     __shared__ float Y[4][SZ * SX];
     const int s = blockIdx.z;
     const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + p.h;
     const long long fs = (long long)p.S * p.cells, so = (long long)s * p.cells;
     pdl_wait();
-    for (int t = threadIdx.x; t < SX * SZ; t += NT) {
+#pragma unroll
+    for (int q = 0; q < N1; ++q) {
+        const int t = threadIdx.x + q * NT;
+        if (t >= SX * SZ) break;
         const int lz = t / SX, lx = t - lz * SX;
         const int i = i0 - H + lz, j = j0 - H + lx;
         float y1 = 0.f, y2 = 0.f, y3 = 0.f, y4 = 0.f;
         if (i >= p.h && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h) {
-            const bool own = lz >= H && lz < H + kTZ && lx >= H && lx < H + kTX;
             const long long c0 = (long long)i * p.nyp + j, o = so + c0;
             const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1);
             const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1);
-            const float avy = p.f[VY][o], avz = p.f[VZ][o];
+            const float avy = __ldg(p.f[VY] + o), avz = __ldg(p.f[VZ] + o);
             const float agy = (p.dt * __ldg(p.by + c0)) * avy, agz = (p.dt * __ldg(p.bz + c0)) * avz;
-            if (own) {
-                const float fy = __ldcs(p.snap + o), fz = __ldcs(p.snap + fs + o);
-                p.grad[3 * fs + o] = p.grad[3 * fs + o] + p.dt * (avy * fy);
-                p.grad[4 * fs + o] = p.grad[4 * fs + o] + p.dt * (avz * fz);
-            }
             y1 = agy; y2 = agy; y3 = agz; y4 = agz;
-            if (ypml) {
-                const float x0 = agy + p.psi_in[0][o]; y1 = agy + AYH(j) * x0;
-                const float x2 = agz + p.psi_in[2][o]; y3 = agz + AY(j) * x2;
-                if (own) { p.psi_out[0][o] = BYH(j) * x0; p.psi_out[2][o] = BY(j) * x2; }
-            }
-            if (zpml) {
-                const float x1 = agy + p.psi_in[1][o]; y2 = agy + AZ(i) * x1;
-                const float x3 = agz + p.psi_in[3][o]; y4 = agz + AZH(i) * x3;
-                if (own) { p.psi_out[1][o] = BZ(i) * x1; p.psi_out[3][o] = BZH(i) * x3; }
+            if (ypml || zpml) {
+                const bool own = lz >= H && lz < H + kTZ && lx >= H && lx < H + kTX;
+                if (ypml) {
+                    const float x0 = agy + p.psi_in[0][o]; y1 = agy + AYH(j) * x0;
+                    const float x2 = agz + p.psi_in[2][o]; y3 = agz + AY(j) * x2;
+                    if (own) { p.psi_out[0][o] = BYH(j) * x0; p.psi_out[2][o] = BY(j) * x2; }
+                }
+                if (zpml) {
+                    const float x1 = agy + p.psi_in[1][o]; y2 = agy + AZ(i) * x1;
+                    const float x3 = agz + p.psi_in[3][o]; y4 = agz + AZH(i) * x3;
+                    if (own) { p.psi_out[1][o] = BZ(i) * x1; p.psi_out[3][o] = BZH(i) * x3; }
+                }
             }
         }
         Y[0][t] = y1; Y[1][t] = y2; Y[2][t] = y3; Y[3][t] = y4;
     }
-    __syncthreads();
-    for (int t = threadIdx.x; t < kTX * kTZ; t += NT) {
+    float vy[N2], vz[N2], fy[N2], fz[N2], g3[N2], g4[N2], sx[N2], sy[N2], sz[N2];
+    long long oo[N2];
+#pragma unroll
+    for (int q = 0; q < N2; ++q) {
+        const int t = threadIdx.x + q * NT;
         const int tz = t / kTX, tx = t - tz * kTX;
         const int i = i0 + tz, j = j0 + tx;
-        if (i >= p.nzp - p.h || j >= p.nyp - p.h) continue;
-        const long long o = so + (long long)i * p.nyp + j;
+        const bool in = i < p.nzp - p.h && j < p.nyp - p.h;
+        const long long o = so + (long long)(in ? i : p.h) * p.nyp + (in ? j : p.h);
+        oo[q] = in ? o : -1;
+        vy[q] = __ldg(p.f[VY] + o); vz[q] = __ldg(p.f[VZ] + o);
+        fy[q] = __ldcs(p.snap + o); fz[q] = __ldcs(p.snap + fs + o);
+        g3[q] = p.grad[3 * fs + o]; g4[q] = p.grad[4 * fs + o];
+        sx[q] = p.f[SXX][o]; sy[q] = p.f[SYZ][o]; sz[q] = p.f[SZZ][o];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < N2; ++q) {
+        if (oo[q] < 0) continue;
+        const long long o = oo[q];
+        const int t = threadIdx.x + q * NT;
+        const int tz = t / kTX, tx = t - tz * kTX;
         const int l = (tz + H) * SX + tx + H;
-        p.f[SXX][o] = p.f[SXX][o] - sm_dminus<H>(&Y[0][l], 1, p.cy);
-        p.f[SYZ][o] = p.f[SYZ][o] - (sm_dplus<H>(&Y[1][l], SX, p.cz) + sm_dplus<H>(&Y[2][l], 1, p.cy));
-        p.f[SZZ][o] = p.f[SZZ][o] - sm_dminus<H>(&Y[3][l], SX, p.cz);
+        p.grad[3 * fs + o] = g3[q] + p.dt * (vy[q] * fy[q]);
+        p.grad[4 * fs + o] = g4[q] + p.dt * (vz[q] * fz[q]);
+        p.f[SXX][o] = sx[q] - sm_dminus<H>(&Y[0][l], 1, p.cy);
+        p.f[SYZ][o] = sy[q] - (sm_dplus<H>(&Y[1][l], SX, p.cz) + sm_dplus<H>(&Y[2][l], 1, p.cy));
+        p.f[SZZ][o] = sz[q] - sm_dminus<H>(&Y[3][l], SX, p.cz);
     }
 }
 

@@ -117,7 +117,7 @@ if __name__ == "__main__":
             os.replace(src, os.path.join(OUT, "launches.csv"))
             launches(tag + "_c3")
         tf = full_multi(tag, "el_fwd_full", "C3 elastic forward step: sample, f1, f2, inject (bench.py --workload c3 --nt 40)")
-        ta = full_multi(tag, "el_adj_full", "C3 elastic adjoint step: b2a, b2b, b1a, b1b, inject, sample (bench.py --workload c3 --nt 40)")
+        ta = full_multi(tag, "el_adj_full", "C3 elastic adjoint step: sample, b2_fused, b1_fused, inject (bench.py --workload c3 --nt 40)")
         print(tf, ta)
         tj = os.path.join(PROF, "traffic.json")
         cur = json.load(open(tj)) if os.path.exists(tj) else {}
