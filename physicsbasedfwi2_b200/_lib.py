@@ -13,7 +13,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_HERE, "csrc")
 SO_PATH = os.path.join(_HERE, "libfwi_b200.so")
-_SOURCES = ["common.cu", "acoustic.cu", "elastic.cu", "misfit.cu"]
+_SOURCES = ["common.cu", "acoustic.cu", "acoustic_small.cu", "elastic.cu", "misfit.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
 

@@ -33,6 +33,7 @@
 #include <vector>
 
 #include "common.h"
+#include "acoustic_small.h"
 
 namespace {
 
@@ -1110,6 +1111,35 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     const Geom g = make_geom(d);
     const int h = g.h;
     const int mode = b->q_read ? 2 : (b->q_write ? 1 : 0);
+
+    // ---- small grids: the whole time loop as one cluster-resident kernel (acoustic_small.cu) ----
+    const int small_on = env_int("FWI_B200_SMALL", 1);      // read per call: tests switch paths in-process
+    static const int small_cells = env_int("FWI_B200_SMALL_CELLS", 1500000);
+    if (small_on && !link && !getenv("FWI_B200_TRACE") && d->chunk_rows == 0 &&
+        (int64_t)d->n_shots * d->nzp * d->nyp <= small_cells) {
+        fwi::SmallParams sp = {};
+        sp.nzp = d->nzp; sp.nyp = d->nyp; sp.pitch = g.pitch; sp.col0 = g.col0; sp.h = h; sp.pw = d->pml_width;
+        sp.S = d->n_shots; sp.nsteps = d->nsteps; sp.adjoint = d->adjoint; sp.mode = mode;
+        sp.n_inj = d->n_inj; sp.inj_scale_a = d->inj_scale_a; sp.n_smp = d->n_smp; sp.smp_div_a = d->smp_div_a;
+        sp.wave_pml = d->pml_width > 0;
+        sp.stride = (long long)d->nzp * g.pitch;
+        const double dz = d->dz, dy = d->dy;
+        sp.c0 = (float)(fwi::kD2[h][0] / (dz * dz) + fwi::kD2[h][0] / (dy * dy));
+        for (int k = 1; k <= h; ++k) {
+            sp.cz2[k] = (float)(fwi::kD2[h][k] / (dz * dz));
+            sp.cy2[k] = (float)(fwi::kD2[h][k] / (dy * dy));
+            sp.cz1[k] = (float)(fwi::kD1[h][k - 1] / dz);
+            sp.cy1[k] = (float)(fwi::kD1[h][k - 1] / dy);
+        }
+        sp.dt = (float)d->dt; sp.dt2 = sp.dt * sp.dt; sp.hdt = 0.5f * sp.dt;
+        sp.w = b->w; sp.sigz = b->sigz; sp.sigy = b->sigy; sp.wave = b->wave;
+        sp.inj_row_start = b->inj_row_start; sp.inj_cell = b->inj_cell; sp.inj_col = b->inj_col; sp.inj_amp = b->inj_amp;
+        sp.smp_cell = b->smp_cell; sp.smp_out = b->smp_out;
+        sp.q_write = b->q_write; sp.q_read = b->q_read; sp.image = b->image;
+        bool launched = false;
+        if ((rc = fwi::small_run(sp, stream, &launched)) != FWI_OK) return rc;
+        if (launched) return FWI_OK;
+    }
 
     // ---- work table: one cost-balanced unit per resident warp ----
     int sms = 0;

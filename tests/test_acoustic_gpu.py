@@ -55,8 +55,12 @@ F64_TRACE_TOL = 5e-5
 F64_GRAD_TOL = 2e-4
 
 
+@pytest.mark.parametrize("small", ["1", "0"], ids=["cluster-resident", "step-kernel"])
 @pytest.mark.parametrize("idx", range(len(CASES)))
-def test_traces_and_gradients_match_oracle(cuda_lib, idx):
+def test_traces_and_gradients_match_oracle(cuda_lib, idx, small, monkeypatch):
+    """Both time-loop implementations: the cluster-resident small-grid kernel (acoustic_small.cu, the
+    default at these sizes) and the per-step TMA kernel (acoustic.cu, what the large grids run)."""
+    monkeypatch.setenv("FWI_B200_SMALL", small)
     errs = _run_case(CASES[idx])
     et, ev, es = errs["f32"]                   # same precision as the product: north_star tolerances
     assert et <= TRACE_TOL, f"trace rel-L2 {et:.3e} > {TRACE_TOL}"
@@ -98,11 +102,13 @@ def _golden():
     return sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "o*.npz")))
 
 
+@pytest.mark.parametrize("small", ["1", "0"], ids=["cluster-resident", "step-kernel"])
 @pytest.mark.parametrize("path", _golden(), ids=lambda p: p.split("/")[-1][:-4])
-def test_cuda_matches_committed_golden_vectors(cuda_lib, path):
+def test_cuda_matches_committed_golden_vectors(cuda_lib, path, small, monkeypatch):
     """Golden vectors from tests/golden/make_golden.py (torch-autograd oracle, fp64)."""
     import numpy as np
     from physicsbasedfwi2_b200.scalar import Propagator
+    monkeypatch.setenv("FWI_B200_SMALL", small)
     z = np.load(path)
     dev = torch.device("cuda:0")
     dx = z["dx"].tolist()
@@ -116,11 +122,13 @@ def test_cuda_matches_committed_golden_vectors(cuda_lib, path):
     assert K.rel_l2(sg.grad, torch.from_numpy(z["grad_src"])) <= GRAD_TOL
 
 
+@pytest.mark.parametrize("small", ["1", "0"], ids=["cluster-resident", "step-kernel"])
 @pytest.mark.parametrize("K", [14, 7, 33])
-def test_wavefield_checkpointing_reproduces_the_stored_snapshot_gradient(cuda_lib, K):
+def test_wavefield_checkpointing_reproduces_the_stored_snapshot_gradient(cuda_lib, K, small, monkeypatch):
     """checkpoint_every=K recomputes the snapshots segment by segment (BASELINE config 4): same
     kernels, same arithmetic, so traces and gradients must be identical to the k=1 snapshot mode."""
     from physicsbasedfwi2_b200.scalar import Propagator
+    monkeypatch.setenv("FWI_B200_SMALL", small)
     c = CASES[1]       # 8th order, sub-stepped (ratio 2), two sources per shot
     from tests import _cases as KK
     v = KK.layered_model(c["nz"], c["ny"], seed=1)
