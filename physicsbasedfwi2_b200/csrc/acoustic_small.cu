@@ -30,7 +30,21 @@ namespace {
 
 constexpr int kNT = 512;
 
-template <int H>
+// Cell c of a CTA (row-major over its rows x computational columns) -> local row / padded column.
+struct CellMap {
+    int ncols, H, W, r0, pitch, col0;
+    float inv;
+    __device__ __forceinline__ void at(int c, int &lr, int &x) const {
+        lr = (int)(((float)c + 0.5f) * inv);
+        x = c - lr * ncols + H;
+    }
+    __device__ __forceinline__ int loc(int lr, int x) const { return (lr + H) * W + x; }
+    __device__ __forceinline__ size_t glob(int lr, int x) const { return (size_t)(r0 + lr) * pitch + col0 + x; }
+};
+
+// CPT = cells per thread (compile-time bound: per-cell constants and accumulators live in registers
+// for the whole time loop); ADJ = adjoint pass with imaging (reads the snapshot, accumulates the image).
+template <int H, int CPT, bool ADJ>
 __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParams p) {
     extern __shared__ __align__(16) float sm[];
     cg::cluster_group cluster = cg::this_cluster();
@@ -38,18 +52,21 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
     const int s = blockIdx.x / p.C;
     const int tid = threadIdx.x;
     const int W = p.nyp;                                   // shared-memory row width
-    const int r0 = H + rank * p.rows_per;                  // first / past-last computational row of this CTA
-    const int r1 = min(p.nzp - H, r0 + p.rows_per);
-    const int rows = r1 - r0;                              // may be <= 0 for a trailing CTA of a short grid
+    const int r0 = p.row_start[rank], r1 = p.row_start[rank + 1];   // my computational rows
+    const int rows = r1 - r0;
     const int LR = p.rows_per + 2 * H;                     // local rows (with halos), same for every CTA
     const int fld = LR * W;
     float *U = sm, *UM = sm + fld, *PZ = sm + 2 * fld, *PY = sm + 3 * fld;
-    const int ncols = p.nyp - 2 * H;
-    const int ncell = max(rows, 0) * ncols;
-    const float inv_ncols = 1.0f / (float)ncols;
+    // PML profiles of my rows / of all columns: cluster.sync invalidates L1, so per-step __ldg of them would
+    // pay an L2 round trip on the critical path of every step
+    float *SZ = sm + (p.wave_pml ? 4 : 2) * fld, *SY = SZ + LR;
+    CellMap cm;
+    cm.ncols = p.nyp - 2 * H; cm.H = H; cm.W = W; cm.r0 = r0; cm.pitch = p.pitch; cm.col0 = p.col0;
+    cm.inv = 1.0f / (float)cm.ncols;
+    const int ncell = max(rows, 0) * cm.ncols;
     // PML frame (widened by H: cells that can see a memory variable), as in cpu_ref_impl.h
     const int zlo = H + p.pw + H, zhi = p.nzp - H - p.pw - H;
-    int ylo = H + p.pw + H, yhi = p.nyp - H - p.pw - H;
+    const int ylo = H + p.pw + H, yhi = p.nyp - H - p.pw - H;
     const bool all_pml = p.pw > 0 && yhi <= ylo;
     const size_t gshot = (size_t)s * p.stride;
     const size_t gfld = (size_t)p.S * p.stride;
@@ -67,12 +84,80 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
             PY[t] = in ? p.wave[4 * gfld + g] : 0.f;
         }
     }
+    for (int t = tid; t < LR + W; t += kNT) {
+        if (t < LR) {
+            const int z = r0 - H + t;
+            SZ[t] = (p.wave_pml && z >= 0 && z < p.nzp) ? __ldg(p.sigz + z) : 0.f;
+        } else {
+            SY[t - LR] = p.wave_pml ? __ldg(p.sigy + p.col0 + (t - LR)) : 0.f;
+        }
+    }
+    // ---- per-cell constants and accumulators in registers ----
+    float wreg[CPT], Greg[ADJ ? CPT : 1], qreg[ADJ ? CPT : 1];
+    float *G = ADJ ? p.image + gshot : nullptr;
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+        const int c = tid + k * kNT;
+        wreg[k] = 0.f;
+        if (ADJ) { Greg[k] = 0.f; qreg[k] = 0.f; }
+        if (c < ncell) {
+            int lr, x;
+            cm.at(c, lr, x);
+            wreg[k] = __ldg(p.w + cm.glob(lr, x));
+            if (ADJ) Greg[k] = G[cm.glob(lr, x)];
+        }
+    }
+    // ---- this thread's sampling point and injection entry (constant over the time loop) ----
+    int smp_l = -1;                 // local offset of sampling point r = tid if it lies in my rows
+    float smp_scale = 1.0f;
+    if (tid < p.n_smp) {
+        const int cell = __ldg(p.smp_cell + s * p.n_smp + tid);
+        const int z = cell / p.pitch, y = cell - z * p.pitch;
+        if (z >= r0 && z < r1) {
+            smp_l = (z - r0 + H) * W + (y - p.col0);
+            if (p.smp_div_a) smp_scale = 1.0f + p.hdt * (__ldg(p.sigz + z) + __ldg(p.sigy + y));
+        }
+    }
+    int e0 = 0, e1 = 0;             // list entries of my rows
+    if (p.n_inj > 0 && rows > 0) {
+        const int *rs = p.inj_row_start + (size_t)s * (p.nzp + 1);
+        e0 = __ldg(rs + r0); e1 = __ldg(rs + r1);
+    }
+    int inj_l = -1, inj_col = 0, inj_run = 0;      // entry e0 + tid: first of a run of equal cells?
+    float inj_coef = 0.f;
+    if (e0 + tid < e1) {
+        const int e = e0 + tid;
+        const int cell = __ldg(p.inj_cell + e);
+        if (!(e > e0 && __ldg(p.inj_cell + e - 1) == cell)) {
+            const int z = cell / p.pitch, y = cell - z * p.pitch;
+            inj_coef = __ldg(p.w + cell);
+            if (p.inj_scale_a) inj_coef = (1.0f / (1.0f + p.hdt * (__ldg(p.sigz + z) + __ldg(p.sigy + y)))) * inj_coef;
+            inj_l = (z - r0 + H) * W + (y - p.col0);
+            inj_col = __ldg(p.inj_col + e);
+            inj_run = 1;
+            while (e + inj_run < e1 && __ldg(p.inj_cell + e + inj_run) == cell) ++inj_run;
+        }
+    }
+    const int n_first = p.adjoint ? p.nsteps - 1 : 0;
+    if (ADJ) {
+        const float *qr = p.q_read + (size_t)n_first * gfld + gshot;
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) {
+            const int c = tid + k * kNT;
+            if (c < ncell) { int lr, x; cm.at(c, lr, x); qreg[k] = __ldcs(qr + cm.glob(lr, x)); }
+        }
+    }
     cluster.sync();
 
     for (int it = 0; it < p.nsteps; ++it) {
         const int n = p.adjoint ? p.nsteps - 1 - it : it;
-        // ---- sampling (before the step): the points of this shot that lie in my rows ----
-        for (int r = tid; r < p.n_smp; r += kNT) {
+        // the amplitude this thread injects at the end of the step: in flight during the stencil work
+        float amp0 = 0.f;
+        const float *amp = p.n_inj > 0 ? p.inj_amp + ((size_t)n * p.S + s) * p.n_inj : nullptr;
+        if (inj_run > 0) amp0 = __ldg(amp + inj_col);
+        // ---- sampling (before the step) ----
+        if (smp_l >= 0) p.smp_out[((size_t)n * p.S + s) * p.n_smp + tid] = U[smp_l] * smp_scale;
+        for (int r = tid + kNT; r < p.n_smp; r += kNT) {           // more points than threads: the slow way
             const int cell = __ldg(p.smp_cell + s * p.n_smp + r);
             const int z = cell / p.pitch, y = cell - z * p.pitch;
             if (z >= r0 && z < r1) {
@@ -82,81 +167,92 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
             }
         }
         // ---- phase A: q and the new field (into UM, cell by cell in place) ----
-        const float *qr = p.mode == 2 ? p.q_read + (size_t)n * gfld + gshot : nullptr;
         float *qw = p.mode == 1 ? p.q_write + (size_t)n * gfld + gshot : nullptr;
-        float *G = p.mode == 2 ? p.image + gshot : nullptr;
-        for (int c = tid; c < ncell; c += kNT) {
-            const int lr = (int)(((float)c + 0.5f) * inv_ncols);
-            const int x = c - lr * ncols + H;
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) {
+            const int c = tid + k * kNT;
+            if (c >= ncell) break;
+            int lr, x;
+            cm.at(c, lr, x);
             const int z = r0 + lr;
-            const int l = (lr + H) * W + x;
-            const size_t g = (size_t)z * p.pitch + p.col0 + x;
+            const int l = cm.loc(lr, x);
             const float u = U[l];
             float lap = p.c0 * u;
 #pragma unroll
-            for (int k = 1; k <= H; ++k) lap = fmaf(p.cy2[k], U[l - k] + U[l + k], lap);
+            for (int j = 1; j <= H; ++j) lap = fmaf(p.cy2[j], U[l - j] + U[l + j], lap);
 #pragma unroll
-            for (int k = 1; k <= H; ++k) lap = fmaf(p.cz2[k], U[l - k * W] + U[l + k * W], lap);
+            for (int j = 1; j <= H; ++j) lap = fmaf(p.cz2[j], U[l - j * W] + U[l + j * W], lap);
             const bool pml = p.pw > 0 && (all_pml || z < zlo || z >= zhi || x < ylo || x >= yhi);
-            const float wv = __ldg(p.w + g);
+            if (ADJ) Greg[k] = fmaf(u, qreg[k], Greg[k]);
             if (!pml) {
-                if (qr) G[g] = fmaf(u, __ldcs(qr + g), G[g]);
-                if (qw) __stcs(qw + g, lap);
-                UM[l] = fmaf(wv, lap, fmaf(2.0f, u, -UM[l]));
+                if (qw) __stcs(qw + cm.glob(lr, x), lap);
+                UM[l] = fmaf(wreg[k], lap, fmaf(2.0f, u, -UM[l]));
             } else {
-                const float sz = __ldg(p.sigz + z), sy = __ldg(p.sigy + p.col0 + x);
+                const float sz = SZ[lr + H], sy = SY[x];
                 float dpz = 0.f, dpy = 0.f;
 #pragma unroll
-                for (int k = 1; k <= H; ++k) dpz = fmaf(p.cz1[k], PZ[l + k * W] - PZ[l - k * W], dpz);
+                for (int j = 1; j <= H; ++j) dpz = fmaf(p.cz1[j], PZ[l + j * W] - PZ[l - j * W], dpz);
 #pragma unroll
-                for (int k = 1; k <= H; ++k) dpy = fmaf(p.cy1[k], PY[l + k] - PY[l - k], dpy);
+                for (int j = 1; j <= H; ++j) dpy = fmaf(p.cy1[j], PY[l + j] - PY[l - j], dpy);
                 const float q = (lap + dpz) + dpy;
                 const float hs = p.hdt * (sz + sy);
                 const float a = 1.0f / (1.0f + hs);
                 const float cu = a * fmaf(-p.dt2, sz * sy, 2.0f);
                 const float cum = a * (hs - 1.0f);
-                const float aw = a * wv;
-                if (qr) G[g] = fmaf(u, __ldcs(qr + g), G[g]);
-                if (qw) __stcs(qw + g, q);
+                const float aw = a * wreg[k];
+                if (qw) __stcs(qw + cm.glob(lr, x), q);
                 UM[l] = fmaf(aw, q, fmaf(cu, u, cum * UM[l]));
             }
         }
-        cluster.sync();      // everyone is done reading u / pz halos of this step
+        if (ADJ && it + 1 < p.nsteps) {      // next step's snapshot: in flight across the barriers
+            const float *qr = p.q_read + (size_t)(n - 1) * gfld + gshot;
+#pragma unroll
+            for (int k = 0; k < CPT; ++k) {
+                const int c = tid + k * kNT;
+                if (c < ncell) { int lr, x; cm.at(c, lr, x); qreg[k] = __ldcs(qr + cm.glob(lr, x)); }
+            }
+        }
+        // everyone is done reading u / pz halos of this step.  Only reads have to be over (their values have been
+        // consumed), nothing written so far is needed by a peer: a relaxed arrive does not wait for this
+        // step's snapshot stores to drain to L2 the way cluster.sync()'s release would
+        asm volatile("barrier.cluster.arrive.relaxed.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
         // ---- phase B: memory variables of the frame cells, in place (u is still the old field) ----
         if (p.wave_pml) {
-            for (int c = tid; c < ncell; c += kNT) {
-                const int lr = (int)(((float)c + 0.5f) * inv_ncols);
-                const int x = c - lr * ncols + H;
+#pragma unroll
+            for (int k = 0; k < CPT; ++k) {
+                const int c = tid + k * kNT;
+                if (c >= ncell) break;
+                int lr, x;
+                cm.at(c, lr, x);
                 const int z = r0 + lr;
                 if (!(all_pml || z < zlo || z >= zhi || x < ylo || x >= yhi)) continue;
-                const int l = (lr + H) * W + x;
-                const float sz = __ldg(p.sigz + z), sy = __ldg(p.sigy + p.col0 + x);
+                const int l = cm.loc(lr, x);
+                const float sz = SZ[lr + H], sy = SY[x];
                 float duz = 0.f, duy = 0.f;
 #pragma unroll
-                for (int k = 1; k <= H; ++k) duz = fmaf(p.cz1[k], U[l + k * W] - U[l - k * W], duz);
+                for (int j = 1; j <= H; ++j) duz = fmaf(p.cz1[j], U[l + j * W] - U[l - j * W], duz);
 #pragma unroll
-                for (int k = 1; k <= H; ++k) duy = fmaf(p.cy1[k], U[l + k] - U[l - k], duy);
+                for (int j = 1; j <= H; ++j) duy = fmaf(p.cy1[j], U[l + j] - U[l - j], duy);
                 PZ[l] = fmaf(p.dt * (sy - sz), duz, fmaf(-p.dt, sz, 1.0f) * PZ[l]);
                 PY[l] = fmaf(p.dt * (sz - sy), duy, fmaf(-p.dt, sy, 1.0f) * PY[l]);
             }
         }
-        // ---- injection into the new field: list entries of my rows, runs of equal cells in list order ----
-        if (p.n_inj > 0 && rows > 0) {
-            const int *rs = p.inj_row_start + (size_t)s * (p.nzp + 1);
-            const int e0 = __ldg(rs + r0), e1 = __ldg(rs + r1);
-            const float *amp = p.inj_amp + ((size_t)n * p.S + s) * p.n_inj;
-            for (int e = e0 + tid; e < e1; e += kNT) {
-                const int cell = __ldg(p.inj_cell + e);
-                if (e > e0 && __ldg(p.inj_cell + e - 1) == cell) continue;      // not the first of its run
-                const int z = cell / p.pitch, y = cell - z * p.pitch;
-                float coef = __ldg(p.w + cell);
-                if (p.inj_scale_a) coef = (1.0f / (1.0f + p.hdt * (__ldg(p.sigz + z) + __ldg(p.sigy + y)))) * coef;
-                const int l = (z - r0 + H) * W + (y - p.col0);
-                float v = UM[l];
-                for (int k = e; k < e1 && __ldg(p.inj_cell + k) == cell; ++k)
-                    v = fmaf(coef, __ldg(amp + __ldg(p.inj_col + k)), v);
-                UM[l] = v;
-            }
+        // ---- injection into the new field: runs of equal cells are applied in list order ----
+        if (inj_run > 0) {
+            float v = fmaf(inj_coef, amp0, UM[inj_l]);
+            for (int k = 1; k < inj_run; ++k) v = fmaf(inj_coef, __ldg(amp + __ldg(p.inj_col + e0 + tid + k)), v);
+            UM[inj_l] = v;
+        }
+        for (int e = e0 + tid + kNT; e < e1; e += kNT) {           // more entries than threads: the slow way
+            const int cell = __ldg(p.inj_cell + e);
+            if (__ldg(p.inj_cell + e - 1) == cell) continue;
+            const int z = cell / p.pitch, y = cell - z * p.pitch;
+            float coef = __ldg(p.w + cell);
+            if (p.inj_scale_a) coef = (1.0f / (1.0f + p.hdt * (__ldg(p.sigz + z) + __ldg(p.sigy + y)))) * coef;
+            const int l = (z - r0 + H) * W + (y - p.col0);
+            float v = UM[l];
+            for (int k = e; k < e1 && __ldg(p.inj_cell + k) == cell; ++k) v = fmaf(coef, __ldg(amp + __ldg(p.inj_col + k)), v);
+            UM[l] = v;
         }
         __syncthreads();
         // ---- push my edge rows of the new field and of pz into the neighbours' halo rows (DSMEM) ----
@@ -165,12 +261,12 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
             if (rank > 0) {                      // my first H rows -> the lower halo of the CTA above
                 float *nUM = cluster.map_shared_rank(UM, rank - 1), *nPZ = cluster.map_shared_rank(PZ, rank - 1);
                 for (int t = tid; t < nedge; t += kNT) {
-                    const int src = H * W + t, dst = (H + p.rows_per) * W + t;
+                    const int src = H * W + t, dst = (H + (r0 - p.row_start[rank - 1])) * W + t;
                     nUM[dst] = UM[src];
                     if (p.wave_pml) nPZ[dst] = PZ[src];
                 }
             }
-            if (rank < p.C - 1 && r1 < p.nzp - H) {     // my last H rows -> the upper halo of the CTA below
+            if (rank < p.C - 1) {                // my last H rows -> the upper halo of the CTA below
                 float *nUM = cluster.map_shared_rank(UM, rank + 1), *nPZ = cluster.map_shared_rank(PZ, rank + 1);
                 for (int t = tid; t < nedge; t += kNT) {
                     const int src = rows * W + t, dst = t;
@@ -188,38 +284,64 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
     float *gu = p.wave + (odd ? gfld : 0) + gshot, *gum = p.wave + (odd ? 0 : gfld) + gshot;
     float *gpz = p.wave_pml ? p.wave + (odd ? 3 : 2) * gfld + gshot : nullptr;
     float *gpy = p.wave_pml ? p.wave + (odd ? 5 : 4) * gfld + gshot : nullptr;
-    for (int c = tid; c < ncell; c += kNT) {
-        const int lr = (int)(((float)c + 0.5f) * inv_ncols);
-        const int x = c - lr * ncols + H;
-        const int l = (lr + H) * W + x;
-        const size_t g = (size_t)(r0 + lr) * p.pitch + p.col0 + x;
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+        const int c = tid + k * kNT;
+        if (c >= ncell) break;
+        int lr, x;
+        cm.at(c, lr, x);
+        const int l = cm.loc(lr, x);
+        const size_t g = cm.glob(lr, x);
         gu[g] = U[l];
         gum[g] = UM[l];
         if (p.wave_pml) { gpz[g] = PZ[l]; gpy[g] = PY[l]; }
+        if (ADJ) G[g] = Greg[k];
     }
 }
 
-template <int H>
+template <int H, int CPT, bool ADJ>
 int try_launch(const SmallParams &p0, cudaStream_t st, bool *launched) {
-    *launched = false;
-    auto kern = acoustic_small_kernel<H>;
+    auto kern = acoustic_small_kernel<H, CPT, ADJ>;
     static int max_smem = -1;
     if (max_smem < 0) {
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 0);
     }
     const int nrows = p0.nzp - 2 * H, nf = p0.wave_pml ? 4 : 2;
-    static const int cmax = getenv("FWI_B200_SMALL_CLUSTER") ? atoi(getenv("FWI_B200_SMALL_CLUSTER")) : 8;
-    for (int C = std::min(cmax, 8); C >= 1; C >>= 1) {
+    const int cmax = getenv("FWI_B200_SMALL_CLUSTER") ? atoi(getenv("FWI_B200_SMALL_CLUSTER")) : 8;
+    for (int C = std::min(cmax, 8); C >= 1; --C) {        // the largest cluster whose shots are all co-resident
         SmallParams p = p0;
         p.C = C;
-        p.rows_per = (nrows + C - 1) / C;
-        if (p.rows_per < H) continue;
-        if ((C - 1) * p.rows_per >= nrows && C > 1) continue;          // a CTA would own no row
-        const size_t smem = (size_t)nf * (p.rows_per + 2 * H) * p.nyp * sizeof(float);
+        // cost-balanced split of the computational rows: a row of the PML frame costs about 2.6 interior rows,
+        // an interior row 1 + 1.6 x (share of its columns in the frame)
+        const int zlo = 2 * H + p.pw, zhi = p.nzp - 2 * H - p.pw, ncols = p.nyp - 2 * H;
+        const double mid = 1.0 + (p.pw > 0 ? 1.6 * std::min(1.0, 2.0 * (p.pw + 2 * H) / (double)ncols) : 0.0);
+        auto cost = [&](int z) { return (p.pw > 0 && (z < zlo || z >= zhi)) ? 2.6 : mid; };
+        double total = 0;
+        for (int z = H; z < p.nzp - H; ++z) total += cost(z);
+        p.row_start[0] = H;
+        {
+            double acc = 0;
+            int r = 1;
+            for (int z = H; z < p.nzp - H && r < C; ++z) {
+                acc += cost(z);
+                if (acc >= total * r / C) p.row_start[r++] = z + 1;
+            }
+            for (; r <= C; ++r) p.row_start[r] = p.nzp - H;
+        }
+        p.row_start[C] = p.nzp - H;
+        bool ok = true;
+        p.rows_per = 0;
+        for (int r = 0; r < C; ++r) {
+            const int n = p.row_start[r + 1] - p.row_start[r];
+            if (n < H) ok = false;                                       // pushes come from own rows only
+            p.rows_per = std::max(p.rows_per, n);
+        }
+        if (!ok) continue;
+        if ((long long)p.rows_per * ncols > (long long)CPT * kNT) continue;   // too many cells per thread
+        const size_t smem = ((size_t)nf * (p.rows_per + 2 * H) * p.nyp + (p.rows_per + 2 * H) + p.nyp) * sizeof(float);
         if (smem > (size_t)max_smem) continue;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(p.S * C);
@@ -246,16 +368,31 @@ int try_launch(const SmallParams &p0, cudaStream_t st, bool *launched) {
     return FWI_OK;       // does not fit: the caller uses the general kernel
 }
 
+// smallest register footprint first: 12 cells per thread, then 24
+template <int H>
+int try_h(const SmallParams &p, cudaStream_t st, bool *launched) {
+    *launched = false;
+    int rc;
+    if (p.mode == 2) {
+        rc = try_launch<H, 12, true>(p, st, launched);
+        if (rc != FWI_OK || *launched) return rc;
+        return try_launch<H, 24, true>(p, st, launched);
+    }
+    rc = try_launch<H, 12, false>(p, st, launched);
+    if (rc != FWI_OK || *launched) return rc;
+    return try_launch<H, 24, false>(p, st, launched);
+}
+
 }  // namespace
 
 // Runs the whole time loop in one cluster-resident kernel when the problem fits; *launched says so.
 int small_run(const SmallParams &p, void *stream, bool *launched) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     switch (p.h) {
-    case 1: return try_launch<1>(p, st, launched);
-    case 2: return try_launch<2>(p, st, launched);
-    case 3: return try_launch<3>(p, st, launched);
-    default: return try_launch<4>(p, st, launched);
+    case 1: return try_h<1>(p, st, launched);
+    case 2: return try_h<2>(p, st, launched);
+    case 3: return try_h<3>(p, st, launched);
+    default: return try_h<4>(p, st, launched);
     }
 }
 

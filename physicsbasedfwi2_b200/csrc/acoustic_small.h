@@ -6,7 +6,8 @@ namespace fwi {
 
 struct SmallParams {
     int nzp, nyp, pitch, col0, h, pw, S, C;     // C = CTAs per cluster (= per shot)
-    int rows_per;                               // computational rows per CTA
+    int rows_per;                               // most computational rows any CTA owns (sizes the shared-memory bands)
+    int row_start[9];                           // CTA r owns the rows [row_start[r], row_start[r+1]) (cost-balanced split)
     int nsteps, adjoint, mode;                  // mode 0: plain, 1: write q, 2: read q + image
     int n_inj, inj_scale_a, n_smp, smp_div_a;
     int wave_pml;                               // 1: pz / py exist
