@@ -19,3 +19,11 @@ if [ "${NCU:-1}" = "1" ]; then
     --launch-skip 60 --launch-count 1 -o gpurun_out/adj_full -f python bench.py --nt 40 --steps 1 --warmup 3 --no-cpu --no-e2e \
     > gpurun_out/ncu_adj.log 2>&1; echo "ncu adj rc=$?"
 fi
+# small-grid (cluster-resident) kernel: C1 / C5 bench lines and one full capture of a forward + adjoint pair
+timeout 300 python bench.py --workload c1 > gpurun_out/bench_c1.log 2>&1; echo "c1 rc=$?"; tail -1 gpurun_out/bench_c1.log | cut -c1-160
+timeout 300 python bench.py --workload c5 > gpurun_out/bench_c5.log 2>&1; echo "c5 rc=$?"; tail -1 gpurun_out/bench_c5.log | cut -c1-160
+if [ "${NCU:-1}" = "1" ]; then
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:acoustic_small --launch-skip 6 --launch-count 2 \
+    -o gpurun_out/small_full -f python bench.py --workload c1 --nt 200 --steps 1 --warmup 3 --no-cpu --no-e2e \
+    > gpurun_out/ncu_small.log 2>&1; echo "ncu small rc=$?"
+fi

@@ -111,6 +111,14 @@ def full_multi(tag, name, note):
 if __name__ == "__main__":
     tag = sys.argv[1]
     os.makedirs(PROF, exist_ok=True)
+    if len(sys.argv) > 2 and sys.argv[2] == "small":
+        print(full_multi(tag, "small_full", "C1 cluster-resident time loop: forward (200 steps) and adjoint kernel "
+                         "(bench.py --workload c1 --nt 200)"))
+        for n in ("bench_c1.log", "bench_c5.log"):
+            pth = os.path.join(OUT, n)
+            if os.path.exists(pth):
+                open(os.path.join(PROF, f"{tag}_{n[:-4]}_1gpu.log.txt"), "w").write(open(pth).read())
+        sys.exit(0)
     if len(sys.argv) > 2 and sys.argv[2] == "elastic":
         src = os.path.join(OUT, "launches_c3.csv")
         if os.path.exists(src):
