@@ -192,6 +192,30 @@ def cpu_baseline(w, target_s=12.0):
                       f"oracle/cpu_ref.c with OpenMP ({t:.1f} s)", "seconds": round(t, 2)}
 
 
+def cpu_baseline_elastic(w, n=5):
+    """Elastic workloads: the torch restatement (oracle/elastic_ref.py; autograd adjoint) on the host cores,
+    one shot, `n` time steps.  There is no C port of the elastic scheme; DENISE (the reference's CPU code
+    for this path) is external and absent."""
+    import math as _m
+    from oracle import elastic_ref as E
+    from physicsbasedfwi2_b200.wavelets import ricker
+    v = synth_model(w).double()
+    vs = v / _m.sqrt(3.0)
+    vs[:24] = 0.0
+    rho = 310.0 * v ** 0.25
+    x_s, x_r = synth_survey(w, 1, first_shot=w["survey_shots"] // 2)
+    src = ricker(w["freq"], n, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1).double()
+    g = torch.randn(2, n, 1, w["n_rec"], generator=torch.Generator().manual_seed(2), dtype=torch.float64)
+    kw = dict(order=w["order"], pml_width=w["pml"], vpmax=w["vmax"])
+    t0 = time.perf_counter()
+    E.elastic_gradient(v.float(), vs.float(), rho.float(), w["dx"], src.float(), x_s, x_r, w["dt"], g.float(), **kw)
+    t = time.perf_counter() - t0
+    val = w["nz"] * w["ny"] * n * 2 / t / 1e9
+    return {"value": round(val, 4), "unit": "Gcell-updates/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"1 shot x {n} of {w['nt']} steps, fwd+adjoint (torch autograd), same grid/order/C-PML, fp32, "
+                      f"oracle/elastic_ref.py ({t:.1f} s)", "seconds": round(t, 2)}
+
+
 def run_reference(args, w):
     """--impl reference: the reference's CPU path for this workload.  The reference's propagators
     (deepwave, DENISE) are external and absent, so this is the oracle port (kind 'port')."""
@@ -354,7 +378,7 @@ def run_c5(args, w, dev, rank, world, local):
     for _ in range(args.warmup):
         l = iteration(gathers_d)
     torch.cuda.synchronize()
-    if not math.isfinite(float(l)):
+    if not math.isfinite(float(l.detach())):
         raise RuntimeError("non-finite misfit in the C5 iteration")
     _lib.LOOP_TIMES = []
     n0 = pkg.kernel_launches()
@@ -530,7 +554,7 @@ def main():
     for _ in range(args.warmup):
         g, l = step_resident()
     torch.cuda.synchronize()
-    if not bool(torch.isfinite(g).all()) or not math.isfinite(float(l)):
+    if not bool(torch.isfinite(g).all()) or not math.isfinite(float(l.detach())):
         raise RuntimeError("non-finite gradient / misfit in the benchmark step")
 
     _lib.LOOP_TIMES = []
@@ -586,8 +610,8 @@ def main():
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": bench_config(w, batch, world, args.workload), "roofline": roof,
                 "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}
-        if world == 1 and not args.no_cpu and not w.get("elastic"):
-            line["cpu_baseline"] = cpu_baseline(w)
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline_elastic(w) if w.get("elastic") else cpu_baseline(w)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
