@@ -368,19 +368,20 @@ int try_launch(const SmallParams &p0, cudaStream_t st, bool *launched) {
     return FWI_OK;       // does not fit: the caller uses the general kernel
 }
 
-// smallest register footprint first: 12 cells per thread, then 24
+// smallest register footprint first: 12, 16, then 24 cells per thread
+template <int H, bool ADJ>
+int try_cpt(const SmallParams &p, cudaStream_t st, bool *launched) {
+    int rc = try_launch<H, 12, ADJ>(p, st, launched);
+    if (rc != FWI_OK || *launched) return rc;
+    rc = try_launch<H, 16, ADJ>(p, st, launched);
+    if (rc != FWI_OK || *launched) return rc;
+    return try_launch<H, 24, ADJ>(p, st, launched);
+}
+
 template <int H>
 int try_h(const SmallParams &p, cudaStream_t st, bool *launched) {
     *launched = false;
-    int rc;
-    if (p.mode == 2) {
-        rc = try_launch<H, 12, true>(p, st, launched);
-        if (rc != FWI_OK || *launched) return rc;
-        return try_launch<H, 24, true>(p, st, launched);
-    }
-    rc = try_launch<H, 12, false>(p, st, launched);
-    if (rc != FWI_OK || *launched) return rc;
-    return try_launch<H, 24, false>(p, st, launched);
+    return p.mode == 2 ? try_cpt<H, true>(p, st, launched) : try_cpt<H, false>(p, st, launched);
 }
 
 }  // namespace
