@@ -176,7 +176,8 @@ typedef struct fwi_elastic_buffers {
                                  buoyancy at (i,j+1/2) and (i+1/2,j) */
     const float *prof_z;      /* [4][nzp] C-PML a, b at integer nodes, a, b at half nodes, along z */
     const float *prof_y;      /* [4][nyp] likewise along y */
-    float *wave;              /* [13][n_shots][nzp][nyp], zero on entry: vy vz sxx szz syz psi0..7
+    float *wave;              /* [22][n_shots][nzp][nyp] (fwi_elastic_wave_floats), zero on entry: vy vz sxx szz syz psi0..7
+                                 and a second copy of vy vz sxx szz syz psi0..3 (the fused forward step ping-pongs)
                                  (backward: their adjoint variables) */
     const int32_t *src_cell;  /* [n_shots][n_src] cell = z*nyp + y */
     const int32_t *src_link;  /* [n_shots][n_src] chains of points sharing a cell: bits 0..29 = index of the

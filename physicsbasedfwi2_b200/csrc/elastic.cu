@@ -33,7 +33,8 @@ struct EParams {
     float *snap;                // this step's [5][S][cells]: fy fz e1 e2 e3 (NULL: not stored / read)
     float *scratch;             // [4][S][cells]
     float *grad;                // [5][S][cells]: l2m lam mu by bz images
-    float *psi_in[8], *psi_out[8];  // fused adjoint: memory variables read / written this step (ping-pong)
+    float *psi_in[8], *psi_out[8];  // fused kernels: memory variables read / written this step (ping-pong)
+    float *fo[5];                   // fused forward: vy vz sxx szz syz written this step (p.f[0..4] are read)
 };
 
 // Every kernel of the time loop is launched with programmatic stream serialization: its blocks
@@ -42,6 +43,21 @@ struct EParams {
 __device__ __forceinline__ void pdl_wait() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the next kernel may become resident early
     asm volatile("griddepcontrol.wait;" ::: "memory");                // ... but nobody reads before the previous grid is done
+}
+
+template <typename... KArgs, typename... Args>
+inline void launch_pdl_smem(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
 template <typename... KArgs, typename... Args>
@@ -388,6 +404,134 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b1_fuse
     }
 }
 
+// ---- fused forward kernel -----------------------------------------------------------------------
+// F1 + F2 in one kernel: a CTA loads the three stresses of its 64 x 32 tile plus 2H halo cells into
+// shared memory, computes the new velocities on the tile plus H halo cells into shared memory (own
+// cells also go to HBM, with the force terms of the snapshot), then the new stresses of its own cells
+// from the shared velocities.  Each field crosses HBM once per step (80 B per cell-update instead
+// of ~100 B).  Halo cells recompute what the neighbouring CTA also computes, from the values BEFORE the
+// step, so everything the halo reads is double-buffered: p.f[0..4] / psi_in are read, p.fo / psi_out
+// written, and the host swaps them every step.  psi4..7 belong to own cells only: in place.
+template <int H, int NT, bool SAVE>
+__global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_f_fused(const EParams p) {
+    constexpr int SX0 = kTX + 4 * H, SZ0 = kTZ + 4 * H;      // stress tile
+    constexpr int SX1 = kTX + 2 * H, SZ1 = kTZ + 2 * H;      // velocity tile
+    constexpr int N0 = (SX0 * SZ0 + NT - 1) / NT, N1 = (SX1 * SZ1 + NT - 1) / NT, N2 = (kTX * kTZ) / NT;
+    extern __shared__ __align__(16) float fsm[];
+    float *Sxx = fsm, *Szz = fsm + SX0 * SZ0, *Syz = fsm + 2 * SX0 * SZ0;
+    float *Vy = fsm + 3 * SX0 * SZ0, *Vz = Vy + SX1 * SZ1;
+    const int s = blockIdx.z;
+    const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + p.h;     // first own cell
+    const long long fs = (long long)p.S * p.cells, so = (long long)s * p.cells;
+    pdl_wait();
+    // stage 0: stresses of the tile and 2H halo cells (zero outside the grid)
+#pragma unroll
+    for (int q = 0; q < N0; ++q) {
+        const int t = threadIdx.x + q * NT;
+        if (t >= SX0 * SZ0) break;
+        const int lz = t / SX0, lx = t - lz * SX0;
+        const int i = i0 - 2 * H + lz, j = j0 - 2 * H + lx;
+        float a = 0.f, b = 0.f, c = 0.f;
+        if (i >= 0 && i < p.nzp && j >= 0 && j < p.nyp) {
+            const long long o = so + (long long)i * p.nyp + j;
+            a = __ldg(p.f[SXX] + o); b = __ldg(p.f[SZZ] + o); c = __ldg(p.f[SYZ] + o);
+        }
+        Sxx[t] = a; Szz[t] = b; Syz[t] = c;
+    }
+    // operands of stage 1 that do not depend on stage 0: in flight across the barrier
+    float pvy[N1], pvz[N1], pby[N1], pbz[N1];
+#pragma unroll
+    for (int q = 0; q < N1; ++q) {
+        const int t = threadIdx.x + q * NT;
+        const int lz = t / SX1, lx = t - lz * SX1;
+        const int i = i0 - H + lz, j = j0 - H + lx;
+        const bool in = t < SX1 * SZ1 && i >= p.h && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h;
+        const long long c0 = (long long)(in ? i : p.h) * p.nyp + (in ? j : p.h);
+        pvy[q] = __ldg(p.f[VY] + so + c0); pvz[q] = __ldg(p.f[VZ] + so + c0);
+        pby[q] = __ldg(p.by + c0); pbz[q] = __ldg(p.bz + c0);
+    }
+    __syncthreads();
+    // stage 1: new velocities on the tile and H halo cells
+#pragma unroll
+    for (int q = 0; q < N1; ++q) {
+        const int t = threadIdx.x + q * NT;
+        if (t >= SX1 * SZ1) break;
+        const int lz = t / SX1, lx = t - lz * SX1;
+        const int i = i0 - H + lz, j = j0 - H + lx;
+        float vy = 0.f, vz = 0.f;
+        if (i >= p.h && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h) {
+            const bool own = lz >= H && lz < H + kTZ && lx >= H && lx < H + kTX;
+            const long long c0 = (long long)i * p.nyp + j, o = so + c0;
+            const int l = (lz + H) * SX0 + lx + H;
+            float d1 = sm_dplus<H>(Sxx + l, 1, p.cy), d2 = sm_dminus<H>(Syz + l, SX0, p.cz);
+            float d3 = sm_dminus<H>(Syz + l, 1, p.cy), d4 = sm_dplus<H>(Szz + l, SX0, p.cz);
+            const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1);
+            const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1);
+            if (ypml) {
+                const float q0 = BYH(j) * p.psi_in[0][o] + AYH(j) * d1; d1 = d1 + q0;
+                const float q2 = BY(j) * p.psi_in[2][o] + AY(j) * d3; d3 = d3 + q2;
+                if (own) { p.psi_out[0][o] = q0; p.psi_out[2][o] = q2; }
+            }
+            if (zpml) {
+                const float q1 = BZ(i) * p.psi_in[1][o] + AZ(i) * d2; d2 = d2 + q1;
+                const float q3 = BZH(i) * p.psi_in[3][o] + AZH(i) * d4; d4 = d4 + q3;
+                if (own) { p.psi_out[1][o] = q1; p.psi_out[3][o] = q3; }
+            }
+            const float fy = d1 + d2, fz = d3 + d4;
+            vy = pvy[q] + (p.dt * pby[q]) * fy;
+            vz = pvz[q] + (p.dt * pbz[q]) * fz;
+            if (own) {
+                p.fo[VY][o] = vy; p.fo[VZ][o] = vz;
+                if (SAVE) { __stcs(p.snap + o, fy); __stcs(p.snap + fs + o, fz); }
+            }
+        }
+        Vy[t] = vy; Vz[t] = vz;
+    }
+    float pl2m[N2], plam[N2], pmu[N2];
+#pragma unroll
+    for (int q = 0; q < N2; ++q) {
+        const int t = threadIdx.x + q * NT;
+        const int tz = t / kTX, tx = t - tz * kTX;
+        const int i = min(i0 + tz, p.nzp - p.h - 1), j = min(j0 + tx, p.nyp - p.h - 1);
+        const long long c0 = (long long)i * p.nyp + j;
+        pl2m[q] = __ldg(p.l2m + c0); plam[q] = __ldg(p.lam + c0); pmu[q] = __ldg(p.mu + c0);
+    }
+    __syncthreads();
+    // stage 2: new stresses of the own cells
+#pragma unroll
+    for (int q = 0; q < N2; ++q) {
+        const int t = threadIdx.x + q * NT;
+        const int tz = t / kTX, tx = t - tz * kTX;
+        const int i = i0 + tz, j = j0 + tx;
+        if (i >= p.nzp - p.h || j >= p.nyp - p.h) continue;
+        const long long c0 = (long long)i * p.nyp + j, o = so + c0;
+        const int l = (tz + H) * SX1 + tx + H;
+        float d5 = sm_dminus<H>(Vy + l, 1, p.cy), d6 = sm_dminus<H>(Vz + l, SX1, p.cz);
+        float d7 = sm_dplus<H>(Vy + l, SX1, p.cz), d8 = sm_dplus<H>(Vz + l, 1, p.cy);
+        const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1);
+        const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1);
+        if (ypml) {
+            const float q4 = BY(j) * p.f[PSI + 4][o] + AY(j) * d5; p.f[PSI + 4][o] = q4; d5 = d5 + q4;
+            const float q7 = BYH(j) * p.f[PSI + 7][o] + AYH(j) * d8; p.f[PSI + 7][o] = q7; d8 = d8 + q7;
+        }
+        if (zpml) {
+            const float q5 = BZ(i) * p.f[PSI + 5][o] + AZ(i) * d6; p.f[PSI + 5][o] = q5; d6 = d6 + q5;
+            const float q6 = BZH(i) * p.f[PSI + 6][o] + AZH(i) * d7; p.f[PSI + 6][o] = q6; d7 = d7 + q6;
+        }
+        const float e1 = d5, e2 = d6, e3 = d7 + d8;
+        const float l2m = pl2m[q], lam = plam[q], mu = pmu[q];
+        const int ls = (tz + 2 * H) * SX0 + tx + 2 * H;
+        p.fo[SXX][o] = Sxx[ls] + p.dt * (l2m * e1 + lam * e2);
+        p.fo[SZZ][o] = Szz[ls] + p.dt * (lam * e1 + l2m * e2);
+        p.fo[SYZ][o] = Syz[ls] + (p.dt * mu) * e3;
+        if (SAVE) {
+            __stcs(p.snap + 2 * fs + o, e1);
+            __stcs(p.snap + 3 * fs + o, e2);
+            __stcs(p.snap + 4 * fs + o, e3);
+        }
+    }
+}
+
 // ---- point kernels: one thread per shot walks that shot's list (fixed order: deterministic) ----
 // out[k][s][r] = field_k[s][cell[s][r]] for k = 0 (a) and 1 (b), scaled
 __global__ void elastic_sample2(const float *a, const float *b, long long cells, int S, int n, const int *cell,
@@ -486,8 +630,28 @@ dim3 block_shape() {
 
 extern "C" int64_t fwi_elastic_wave_floats(const fwi_elastic_desc *d) {
     if (check(d) != FWI_OK) return -1;
-    return 13ll * d->n_shots * d->nzp * d->nyp;
+    return 22ll * d->n_shots * d->nzp * d->nyp;      // 13 fields + the second copy of vy vz sxx szz syz psi0..3 (fused forward)
 }
+
+namespace {
+template <int H, bool SAVE>
+void launch_f_fused(const EParams &p, dim3 grid, cudaStream_t st) {
+    constexpr size_t smem = (3 * (kTX + 4 * H) * (kTZ + 4 * H) + 2 * (kTX + 2 * H) * (kTZ + 2 * H)) * sizeof(float);
+    auto kern = elastic_f_fused<H, 512, SAVE>;
+    static bool once = false;
+    if (!once) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); once = true; }
+    launch_pdl_smem(kern, grid, dim3(512), smem, st, p);
+}
+template <bool SAVE>
+void launch_f_fused_h(const EParams &p, dim3 grid, cudaStream_t st) {
+    switch (p.h) {
+    case 1: launch_f_fused<1, SAVE>(p, grid, st); break;
+    case 2: launch_f_fused<2, SAVE>(p, grid, st); break;
+    case 3: launch_f_fused<3, SAVE>(p, grid, st); break;
+    default: launch_f_fused<4, SAVE>(p, grid, st); break;
+    }
+}
+}  // namespace
 
 extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_buffers *b, void *stream) {
     int rc = check(d);
@@ -503,7 +667,20 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
     const dim3 grid((d->nyp - 2 * p.h + block.x - 1) / block.x, (d->nzp - 2 * p.h + block.y - 1) / block.y, d->n_shots);
     const long long fld = (long long)d->n_shots * p.cells;
     const long long nrec = (long long)d->n_shots * d->n_rec, nsrc = (long long)d->n_shots * d->n_src;
+    // F1 + F2 as one kernel with double-buffered fields (elastic_f_fused): opt-in with FWI_B200_EL_FUSED_FWD=1.
+    // It moves 80 B per cell-update instead of ~100 B, but its three barrier-separated stages measured
+    // 57.6 us per step on C3 against 42.4 us for the two kernels, so the two-kernel form stays the default.
+    const bool fused = getenv("FWI_B200_EL_FUSED_FWD") && atoi(getenv("FWI_B200_EL_FUSED_FWD")) == 1;
+    const dim3 fgrid((d->nyp - 2 * p.h + kTX - 1) / kTX, (d->nzp - 2 * p.h + kTZ - 1) / kTZ, d->n_shots);
+    float *setA[9], *setB[9];
+    for (int k = 0; k < 5; ++k) { setA[k] = b->wave + k * fld; setB[k] = b->wave + (13 + k) * fld; }
+    for (int k = 0; k < 4; ++k) { setA[5 + k] = b->wave + (PSI + k) * fld; setB[5 + k] = b->wave + (18 + k) * fld; }
     for (int n = 0; n < d->nsteps; ++n) {
+        if (fused) {
+            float **in = (n & 1) ? setB : setA, **out = (n & 1) ? setA : setB;
+            for (int k = 0; k < 5; ++k) { p.f[k] = in[k]; p.fo[k] = out[k]; }
+            for (int k = 0; k < 4; ++k) { p.psi_in[k] = in[5 + k]; p.psi_out[k] = out[5 + k]; }
+        }
         if (d->n_rec) {
             launch_pdl(elastic_sample2, dim3((unsigned)((nrec + 127) / 128)), dim3(128), st,
                 p.f[VY], p.f[VZ], p.cells, d->n_shots, d->n_rec, b->rec_cell, b->rec_out + n * nrec,
@@ -511,17 +688,24 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
             fwi::count_launch();
         }
         p.snap = b->snap ? b->snap + (long long)n * 5 * fld : nullptr;
-        if (p.snap) {
-            ELASTIC_LAUNCH_H(elastic_f1, true);
-            ELASTIC_LAUNCH_H(elastic_f2, true);
+        if (fused) {
+            if (p.snap) launch_f_fused_h<true>(p, fgrid, st);
+            else launch_f_fused_h<false>(p, fgrid, st);
+            fwi::count_launch();
         } else {
-            ELASTIC_LAUNCH_H(elastic_f1, false);
-            ELASTIC_LAUNCH_H(elastic_f2, false);
+            if (p.snap) {
+                ELASTIC_LAUNCH_H(elastic_f1, true);
+                ELASTIC_LAUNCH_H(elastic_f2, true);
+            } else {
+                ELASTIC_LAUNCH_H(elastic_f1, false);
+                ELASTIC_LAUNCH_H(elastic_f2, false);
+            }
+            fwi::count_launch(2);
         }
-        fwi::count_launch(2);
         if (d->n_src) {
+            float *sxx = fused ? p.fo[SXX] : p.f[SXX], *szz = fused ? p.fo[SZZ] : p.f[SZZ];
             launch_pdl(elastic_inject2, dim3((unsigned)((nsrc + 127) / 128)), dim3(128), st,
-                p.f[SXX], p.f[SZZ], p.cells, d->n_shots, d->n_src, b->src_cell, b->src_link, b->src_amp + n * nsrc,
+                sxx, szz, p.cells, d->n_shots, d->n_src, b->src_cell, b->src_link, b->src_amp + n * nsrc,
                 b->src_amp + n * nsrc, p.dt);
             fwi::count_launch();
         }

@@ -38,10 +38,13 @@ def _inputs(c):
     return vp, vs, rho, x_s, x_r, src, grad_rec
 
 
+@pytest.mark.parametrize("fused_fwd", ["0", "1"], ids=["two-kernel-forward", "fused-forward"])
 @pytest.mark.parametrize("idx", range(len(CASES)))
-def test_elastic_traces_and_gradients_match_oracle(cuda_lib, idx):
+def test_elastic_traces_and_gradients_match_oracle(cuda_lib, idx, fused_fwd, monkeypatch):
+    """Default kernels (two-kernel forward step, fused adjoint) and the opt-in fused forward step."""
     from oracle import elastic_ref as E
     import physicsbasedfwi2_b200 as pkg
+    monkeypatch.setenv("FWI_B200_EL_FUSED_FWD", fused_fwd)
     c = CASES[idx]
     vp, vs, rho, x_s, x_r, src, grad_rec = _inputs(c)
     dev = torch.device("cuda:0")
