@@ -139,3 +139,34 @@ def test_devito_style_fwi_loss_adapter(cuda_lib):
     assert tuple(x.grad.shape) == (1, 1, 34, 90)
     assert abs(float(x.grad.abs().max()) - 1.0) < 1e-6
     assert K.rel_l2(x.grad[0, 0], gm0 / gm0.abs().max()) <= 1e-4
+
+
+def test_inner_loop_fwi_reduces_the_misfit_and_matches_the_torch_glue(cuda_lib):
+    """models/networks.py:15372-15415 on the B200 kernels: the first misfit equals the one the plain torch
+    expressions of the reference give on the propagator's output, and Adam(lr=10) steps reduce it."""
+    from oracle import misfit_ref as M
+    from physicsbasedfwi2_b200.inversion import inner_loop_fwi
+    from physicsbasedfwi2_b200.scalar import Propagator
+    nz, ny, S, R, nt = 40, 100, 4, 50, 300
+    true = K.layered_model(nz, ny, seed=2, noise=0.0).clamp(1500.0, 4400.0)
+    start = torch.full((nz, ny), 2500.0)
+    x_s, x_r = K.survey(nz, ny, 10.0, S, R, 1, seed=3)
+    wavelet = K.ricker(12.0, nt, 1e-3, 1 / 12.0).reshape(-1, 1, 1)
+    src = wavelet.repeat(1, S, 1).contiguous().to(DEV)
+    with torch.no_grad():
+        observed = Propagator({"vp": true.to(DEV)}, 10.0)(src, x_s.to(DEV), x_r.to(DEV), 1e-3)
+        direct = Propagator({"vp": torch.full((nz, ny), 1500.0, device=DEV)}, 10.0)(src, x_s.to(DEV), x_r.to(DEV), 1e-3)
+        pred0 = Propagator({"vp": start.to(DEV)}, 10.0)(src, x_s.to(DEV), x_r.to(DEV), 1e-3)
+    o = observed - direct
+    obs_norm = o / (o.abs().amax(0, keepdim=True) + 1e-10)
+    first = float(M.trace_misfit(pred0.cpu().double(), obs_norm.cpu().double(), direct.cpu().double(), kind="mse"))
+    mask = torch.zeros(nz, ny, dtype=torch.bool, device=DEV)
+    mask[:3] = True
+    v, losses = inner_loop_fwi(start.to(DEV), observed, wavelet, x_s, x_r, 10.0, 1e-3, num_epochs=12, num_batches=2,
+                               grad_mask=mask)
+    assert len(losses) == 24 and tuple(v.shape) == (nz, ny)
+    l_full = 0.5 * (losses[0] + losses[1])        # two half-batches of the first epoch bracket the full-survey misfit
+    assert abs(l_full - first) < 0.15 * first
+    assert max(losses[-2:]) < 0.95 * min(losses[:2])      # 12 Adam steps of 10 m/s each: a steady decrease
+    assert torch.all(v[:3] == 2500.0)             # masked rows never move
+    assert float(v.min()) >= 1500.0 and float(v.max()) <= 4400.0
