@@ -170,3 +170,28 @@ def test_inner_loop_fwi_reduces_the_misfit_and_matches_the_torch_glue(cuda_lib):
     assert max(losses[-2:]) < 0.95 * min(losses[:2])      # 12 Adam steps of 10 m/s each: a steady decrease
     assert torch.all(v[:3] == 2500.0)             # masked rows never move
     assert float(v.min()) >= 1500.0 and float(v.max()) <= 4400.0
+
+
+@pytest.mark.parametrize("small", ["1", "0"], ids=["cluster-resident", "step-kernel"])
+def test_many_points_per_shot_and_a_very_shallow_grid(cuda_lib, small, monkeypatch):
+    """More receivers than the 512 threads of a CTA of the cluster-resident kernel (its slow-path loops),
+    several sources per shot with repeats, and a grid only 9 rows deep (bands shorter than a cluster)."""
+    from oracle import cpu_ref as O
+    from physicsbasedfwi2_b200.scalar import Propagator
+    monkeypatch.setenv("FWI_B200_SMALL", small)
+    for nz, ny, R, order, pml in ((9, 180, 700, 4, 6), (26, 90, 1100, 8, 3)):
+        v = K.layered_model(nz, ny, seed=8, blob=False)
+        g = torch.Generator().manual_seed(9)
+        S, Ns, nt = 2, 3, 70
+        x_s = torch.stack([torch.randint(0, nz, (S, Ns), generator=g), torch.randint(0, ny, (S, Ns), generator=g)], -1).float() * 10.0
+        x_s[0, 2] = x_s[0, 0]                                   # a repeated source
+        x_r = torch.stack([torch.randint(0, nz, (S, R), generator=g), torch.randint(0, ny, (S, R), generator=g)], -1).float() * 10.0
+        src = torch.randn(nt, S, Ns, generator=g)
+        gr = torch.randn(nt, S, R, generator=g)
+        vg = v.to(DEV).requires_grad_(True)
+        sg = src.to(DEV).requires_grad_(True)
+        rec = Propagator({"vp": vg}, 10.0, pml_width=pml, accuracy=order)(sg, x_s.to(DEV), x_r.to(DEV), 1e-3)
+        (rec * gr.to(DEV)).sum().backward()
+        r0, gv0, gs0 = O.acoustic_gradient(v, 10.0, src, x_s, x_r, 1e-3, grad_rec=gr, order=order, pml_width=pml,
+                                           dtype=torch.float32)
+        assert K.rel_l2(rec, r0) <= 1e-5 and K.rel_l2(vg.grad, gv0) <= 1e-4 and K.rel_l2(sg.grad, gs0) <= 1e-4
