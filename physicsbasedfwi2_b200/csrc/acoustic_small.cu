@@ -56,10 +56,13 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
     const int rows = r1 - r0;
     const int LR = p.rows_per + 2 * H;                     // local rows (with halos), same for every CTA
     const int fld = LR * W;
-    float *U = sm, *UM = sm + fld, *PZ = sm + 2 * fld, *PY = sm + 3 * fld;
+    // pz is double-buffered (PZ read, PZN written, swapped every step): a neighbour may then store the halo rows
+    // of the new pz while this CTA still reads the old ones, and the barrier between the two phases of a step
+    // can be a CTA barrier instead of a cluster barrier
+    float *U = sm, *UM = sm + fld, *PZ = sm + 2 * fld, *PZN = sm + 3 * fld, *PY = sm + 4 * fld;
     // PML profiles of my rows / of all columns: cluster.sync invalidates L1, so per-step __ldg of them would
     // pay an L2 round trip on the critical path of every step
-    float *SZ = sm + (p.wave_pml ? 4 : 2) * fld, *SY = SZ + LR;
+    float *SZ = sm + (p.wave_pml ? 5 : 2) * fld, *SY = SZ + LR;
     CellMap cm;
     cm.ncols = p.nyp - 2 * H; cm.H = H; cm.W = W; cm.r0 = r0; cm.pitch = p.pitch; cm.col0 = p.col0;
     cm.inv = 1.0f / (float)cm.ncols;
@@ -81,6 +84,7 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
         UM[t] = in ? p.wave[gfld + g] : 0.f;
         if (p.wave_pml) {
             PZ[t] = in ? p.wave[2 * gfld + g] : 0.f;
+            PZN[t] = 0.f;
             PY[t] = in ? p.wave[4 * gfld + g] : 0.f;
         }
     }
@@ -212,10 +216,7 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
                 if (c < ncell) { int lr, x; cm.at(c, lr, x); qreg[k] = __ldcs(qr + cm.glob(lr, x)); }
             }
         }
-        // everyone is done reading u / pz halos of this step.  Only reads have to be over (their values have been
-        // consumed), nothing written so far is needed by a peer: a relaxed arrive does not wait for this
-        // step's snapshot stores to drain to L2 the way cluster.sync()'s release would
-        asm volatile("barrier.cluster.arrive.relaxed.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
+        __syncthreads();     // phase B overwrites py in place and the injection touches the new field
         // ---- phase B: memory variables of the frame cells, in place (u is still the old field) ----
         if (p.wave_pml) {
 #pragma unroll
@@ -233,7 +234,7 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
                 for (int j = 1; j <= H; ++j) duz = fmaf(p.cz1[j], U[l + j * W] - U[l - j * W], duz);
 #pragma unroll
                 for (int j = 1; j <= H; ++j) duy = fmaf(p.cy1[j], U[l + j] - U[l - j], duy);
-                PZ[l] = fmaf(p.dt * (sy - sz), duz, fmaf(-p.dt, sz, 1.0f) * PZ[l]);
+                PZN[l] = fmaf(p.dt * (sy - sz), duz, fmaf(-p.dt, sz, 1.0f) * PZ[l]);
                 PY[l] = fmaf(p.dt * (sz - sy), duy, fmaf(-p.dt, sy, 1.0f) * PY[l]);
             }
         }
@@ -259,24 +260,25 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
         if (rows > 0) {
             const int nedge = H * W;
             if (rank > 0) {                      // my first H rows -> the lower halo of the CTA above
-                float *nUM = cluster.map_shared_rank(UM, rank - 1), *nPZ = cluster.map_shared_rank(PZ, rank - 1);
+                float *nUM = cluster.map_shared_rank(UM, rank - 1), *nPZ = cluster.map_shared_rank(PZN, rank - 1);
                 for (int t = tid; t < nedge; t += kNT) {
                     const int src = H * W + t, dst = (H + (r0 - p.row_start[rank - 1])) * W + t;
                     nUM[dst] = UM[src];
-                    if (p.wave_pml) nPZ[dst] = PZ[src];
+                    if (p.wave_pml) nPZ[dst] = PZN[src];
                 }
             }
             if (rank < p.C - 1) {                // my last H rows -> the upper halo of the CTA below
-                float *nUM = cluster.map_shared_rank(UM, rank + 1), *nPZ = cluster.map_shared_rank(PZ, rank + 1);
+                float *nUM = cluster.map_shared_rank(UM, rank + 1), *nPZ = cluster.map_shared_rank(PZN, rank + 1);
                 for (int t = tid; t < nedge; t += kNT) {
                     const int src = rows * W + t, dst = t;
                     nUM[dst] = UM[src];
-                    if (p.wave_pml) nPZ[dst] = PZ[src];
+                    if (p.wave_pml) nPZ[dst] = PZN[src];
                 }
             }
         }
-        cluster.sync();      // halos of the new field are in place
+        cluster.sync();      // halos of the new field and of the new pz are in place
         float *tmp = U; U = UM; UM = tmp;
+        tmp = PZ; PZ = PZN; PZN = tmp;
     }
 
     // ---- store the state back: own rows; fields in the slots the general kernel would leave them in ----
@@ -309,7 +311,7 @@ int try_launch(const SmallParams &p0, cudaStream_t st, bool *launched) {
         cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     }
-    const int nrows = p0.nzp - 2 * H, nf = p0.wave_pml ? 4 : 2;
+    const int nf = p0.wave_pml ? 5 : 2;
     const int cmax = getenv("FWI_B200_SMALL_CLUSTER") ? atoi(getenv("FWI_B200_SMALL_CLUSTER")) : 8;
     for (int C = std::min(cmax, 8); C >= 1; --C) {        // the largest cluster whose shots are all co-resident
         SmallParams p = p0;
