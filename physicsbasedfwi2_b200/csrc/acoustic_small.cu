@@ -97,16 +97,23 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
         }
     }
     // ---- per-cell constants and accumulators in registers ----
+    // cell descriptor: bits 0..11 padded column x, bits 12..23 local row lr, bit 30 = cell of the PML frame,
+    // -1 = no cell (the index arithmetic and the frame test are done once, not every step)
     float wreg[CPT], Greg[ADJ ? CPT : 1], qreg[ADJ ? CPT : 1];
+    int cell[CPT];
     float *G = ADJ ? p.image + gshot : nullptr;
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
         const int c = tid + k * kNT;
         wreg[k] = 0.f;
+        cell[k] = -1;
         if (ADJ) { Greg[k] = 0.f; qreg[k] = 0.f; }
         if (c < ncell) {
             int lr, x;
             cm.at(c, lr, x);
+            const int z = r0 + lr;
+            const bool pml = p.pw > 0 && (all_pml || z < zlo || z >= zhi || x < ylo || x >= yhi);
+            cell[k] = x | (lr << 12) | (pml ? (1 << 30) : 0);
             wreg[k] = __ldg(p.w + cm.glob(lr, x));
             if (ADJ) Greg[k] = G[cm.glob(lr, x)];
         }
@@ -148,7 +155,7 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
 #pragma unroll
         for (int k = 0; k < CPT; ++k) {
             const int c = tid + k * kNT;
-            if (c < ncell) { int lr, x; cm.at(c, lr, x); qreg[k] = __ldcs(qr + cm.glob(lr, x)); }
+            if (cell[k] >= 0) qreg[k] = __ldcs(qr + cm.glob((cell[k] >> 12) & 0xfff, cell[k] & 0xfff));
         }
     }
     cluster.sync();
@@ -174,11 +181,8 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
         float *qw = p.mode == 1 ? p.q_write + (size_t)n * gfld + gshot : nullptr;
 #pragma unroll
         for (int k = 0; k < CPT; ++k) {
-            const int c = tid + k * kNT;
-            if (c >= ncell) break;
-            int lr, x;
-            cm.at(c, lr, x);
-            const int z = r0 + lr;
+            if (cell[k] < 0) break;
+            const int x = cell[k] & 0xfff, lr = (cell[k] >> 12) & 0xfff;
             const int l = cm.loc(lr, x);
             const float u = U[l];
             float lap = p.c0 * u;
@@ -186,7 +190,7 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
             for (int j = 1; j <= H; ++j) lap = fmaf(p.cy2[j], U[l - j] + U[l + j], lap);
 #pragma unroll
             for (int j = 1; j <= H; ++j) lap = fmaf(p.cz2[j], U[l - j * W] + U[l + j * W], lap);
-            const bool pml = p.pw > 0 && (all_pml || z < zlo || z >= zhi || x < ylo || x >= yhi);
+            const bool pml = (cell[k] >> 30) & 1;
             if (ADJ) Greg[k] = fmaf(u, qreg[k], Greg[k]);
             if (!pml) {
                 if (qw) __stcs(qw + cm.glob(lr, x), lap);
@@ -213,7 +217,7 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
 #pragma unroll
             for (int k = 0; k < CPT; ++k) {
                 const int c = tid + k * kNT;
-                if (c < ncell) { int lr, x; cm.at(c, lr, x); qreg[k] = __ldcs(qr + cm.glob(lr, x)); }
+                if (cell[k] >= 0) qreg[k] = __ldcs(qr + cm.glob((cell[k] >> 12) & 0xfff, cell[k] & 0xfff));
             }
         }
         __syncthreads();     // phase B overwrites py in place and the injection touches the new field
@@ -221,12 +225,9 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
         if (p.wave_pml) {
 #pragma unroll
             for (int k = 0; k < CPT; ++k) {
-                const int c = tid + k * kNT;
-                if (c >= ncell) break;
-                int lr, x;
-                cm.at(c, lr, x);
-                const int z = r0 + lr;
-                if (!(all_pml || z < zlo || z >= zhi || x < ylo || x >= yhi)) continue;
+                if (cell[k] < 0) break;
+                if (!((cell[k] >> 30) & 1)) continue;
+                const int x = cell[k] & 0xfff, lr = (cell[k] >> 12) & 0xfff;
                 const int l = cm.loc(lr, x);
                 const float sz = SZ[lr + H], sy = SY[x];
                 float duz = 0.f, duy = 0.f;
@@ -288,10 +289,8 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
     float *gpy = p.wave_pml ? p.wave + (odd ? 5 : 4) * gfld + gshot : nullptr;
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
-        const int c = tid + k * kNT;
-        if (c >= ncell) break;
-        int lr, x;
-        cm.at(c, lr, x);
+        if (cell[k] < 0) break;
+        const int x = cell[k] & 0xfff, lr = (cell[k] >> 12) & 0xfff;
         const int l = cm.loc(lr, x);
         const size_t g = cm.glob(lr, x);
         gu[g] = U[l];
@@ -312,6 +311,7 @@ int try_launch(const SmallParams &p0, cudaStream_t st, bool *launched) {
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     }
     const int nf = p0.wave_pml ? 5 : 2;
+    if (p0.nyp >= 4096 || p0.nzp >= 4096) return FWI_OK;      // cell descriptors pack row and column in 12 bits each
     const int cmax = getenv("FWI_B200_SMALL_CLUSTER") ? atoi(getenv("FWI_B200_SMALL_CLUSTER")) : 8;
     for (int C = std::min(cmax, 8); C >= 1; --C) {        // the largest cluster whose shots are all co-resident
         SmallParams p = p0;
