@@ -59,10 +59,11 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
     // pz is double-buffered (PZ read, PZN written, swapped every step): a neighbour may then store the halo rows
     // of the new pz while this CTA still reads the old ones, and the barrier between the two phases of a step
     // can be a CTA barrier instead of a cluster barrier
-    float *U = sm, *UM = sm + fld, *PZ = sm + 2 * fld, *PZN = sm + 3 * fld, *PY = sm + 4 * fld;
+    // (py likewise, so that the memory variables are advanced in the same sweep as the field: no second phase)
+    float *U = sm, *UM = sm + fld, *PZ = sm + 2 * fld, *PZN = sm + 3 * fld, *PY = sm + 4 * fld, *PYN = sm + 5 * fld;
     // PML profiles of my rows / of all columns: cluster.sync invalidates L1, so per-step __ldg of them would
     // pay an L2 round trip on the critical path of every step
-    float *SZ = sm + (p.wave_pml ? 5 : 2) * fld, *SY = SZ + LR;
+    float *SZ = sm + (p.wave_pml ? 6 : 2) * fld, *SY = SZ + LR;
     CellMap cm;
     cm.ncols = p.nyp - 2 * H; cm.H = H; cm.W = W; cm.r0 = r0; cm.pitch = p.pitch; cm.col0 = p.col0;
     cm.inv = 1.0f / (float)cm.ncols;
@@ -86,6 +87,7 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
             PZ[t] = in ? p.wave[2 * gfld + g] : 0.f;
             PZN[t] = 0.f;
             PY[t] = in ? p.wave[4 * gfld + g] : 0.f;
+            PYN[t] = 0.f;
         }
     }
     for (int t = tid; t < LR + W; t += kNT) {
@@ -204,12 +206,19 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
                 for (int j = 1; j <= H; ++j) dpy = fmaf(p.cy1[j], PY[l + j] - PY[l - j], dpy);
                 const float q = (lap + dpz) + dpy;
                 const float hs = p.hdt * (sz + sy);
-                const float a = 1.0f / (1.0f + hs);
+                const float a = __frcp_rn(1.0f + hs);          // correctly rounded: the same value as 1.0f / (1.0f + hs)
                 const float cu = a * fmaf(-p.dt2, sz * sy, 2.0f);
                 const float cum = a * (hs - 1.0f);
                 const float aw = a * wreg[k];
-                if (qw) __stcs(qw + cm.glob(lr, x), q);
+                float duz = 0.f, duy = 0.f;
+#pragma unroll
+                for (int j = 1; j <= H; ++j) duz = fmaf(p.cz1[j], U[l + j * W] - U[l - j * W], duz);
+#pragma unroll
+                for (int j = 1; j <= H; ++j) duy = fmaf(p.cy1[j], U[l + j] - U[l - j], duy);
                 UM[l] = fmaf(aw, q, fmaf(cu, u, cum * UM[l]));
+                PZN[l] = fmaf(p.dt * (sy - sz), duz, fmaf(-p.dt, sz, 1.0f) * PZ[l]);
+                PYN[l] = fmaf(p.dt * (sz - sy), duy, fmaf(-p.dt, sy, 1.0f) * PY[l]);
+                if (qw) __stcs(qw + cm.glob(lr, x), q);
             }
         }
         if (ADJ && it + 1 < p.nsteps) {      // next step's snapshot: in flight across the barriers
@@ -220,25 +229,7 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
                 if (cell[k] >= 0) qreg[k] = __ldcs(qr + cm.glob((cell[k] >> 12) & 0xfff, cell[k] & 0xfff));
             }
         }
-        __syncthreads();     // phase B overwrites py in place and the injection touches the new field
-        // ---- phase B: memory variables of the frame cells, in place (u is still the old field) ----
-        if (p.wave_pml) {
-#pragma unroll
-            for (int k = 0; k < CPT; ++k) {
-                if (cell[k] < 0) break;
-                if (!((cell[k] >> 30) & 1)) continue;
-                const int x = cell[k] & 0xfff, lr = (cell[k] >> 12) & 0xfff;
-                const int l = cm.loc(lr, x);
-                const float sz = SZ[lr + H], sy = SY[x];
-                float duz = 0.f, duy = 0.f;
-#pragma unroll
-                for (int j = 1; j <= H; ++j) duz = fmaf(p.cz1[j], U[l + j * W] - U[l - j * W], duz);
-#pragma unroll
-                for (int j = 1; j <= H; ++j) duy = fmaf(p.cy1[j], U[l + j] - U[l - j], duy);
-                PZN[l] = fmaf(p.dt * (sy - sz), duz, fmaf(-p.dt, sz, 1.0f) * PZ[l]);
-                PY[l] = fmaf(p.dt * (sz - sy), duy, fmaf(-p.dt, sy, 1.0f) * PY[l]);
-            }
-        }
+        __syncthreads();     // the new field is complete: the injection below adds to cells other threads wrote
         // ---- injection into the new field: runs of equal cells are applied in list order ----
         if (inj_run > 0) {
             float v = fmaf(inj_coef, amp0, UM[inj_l]);
@@ -280,6 +271,7 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
         cluster.sync();      // halos of the new field and of the new pz are in place
         float *tmp = U; U = UM; UM = tmp;
         tmp = PZ; PZ = PZN; PZN = tmp;
+        tmp = PY; PY = PYN; PYN = tmp;
     }
 
     // ---- store the state back: own rows; fields in the slots the general kernel would leave them in ----
@@ -310,7 +302,7 @@ int try_launch(const SmallParams &p0, cudaStream_t st, bool *launched) {
         cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     }
-    const int nf = p0.wave_pml ? 5 : 2;
+    const int nf = p0.wave_pml ? 6 : 2;
     if (p0.nyp >= 4096 || p0.nzp >= 4096) return FWI_OK;      // cell descriptors pack row and column in 12 bits each
     const int cmax = getenv("FWI_B200_SMALL_CLUSTER") ? atoi(getenv("FWI_B200_SMALL_CLUSTER")) : 8;
     for (int C = std::min(cmax, 8); C >= 1; --C) {        // the largest cluster whose shots are all co-resident
