@@ -1115,7 +1115,7 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     // ---- small grids: the whole time loop as one cluster-resident kernel (acoustic_small.cu) ----
     const int small_on = env_int("FWI_B200_SMALL", 1);      // read per call: tests switch paths in-process
     static const int small_cells = env_int("FWI_B200_SMALL_CELLS", 1500000);
-    if (small_on && !link && !getenv("FWI_B200_TRACE") && d->chunk_rows == 0 &&
+    if (small_on && !link && !getenv("FWI_B200_TRACE") && d->chunk_rows == 0 && (mode != 2 || d->adjoint) &&
         (int64_t)d->n_shots * d->nzp * d->nyp <= small_cells) {
         fwi::SmallParams sp = {};
         sp.nzp = d->nzp; sp.nyp = d->nyp; sp.pitch = g.pitch; sp.col0 = g.col0; sp.h = h; sp.pw = d->pml_width;
