@@ -26,6 +26,25 @@ def _ptr(t: Optional[torch.Tensor]):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
+_PROFILE_CACHE = {}
+
+
+def _pml_profiles(nzp, nyp_global, h, pw, dz, dy, vmax, pitch, col0, c0, c1, dev):
+    """Device copies of the PML profiles (sigz [nzp], sigy [pitch] in device columns).  They depend only on
+    the arguments, and the reference rebuilds its Propagator every iteration with the same ones
+    (models/networks.py:5449): computed and uploaded once per distinct key, not once per call."""
+    key = (nzp, nyp_global, h, pw, dz, dy, vmax, pitch, col0, c0, c1, str(dev))
+    hit = _PROFILE_CACHE.get(key)
+    if hit is None:
+        sz = H.sigma_profile(nzp, h, pw, dz, vmax).float()
+        sy = torch.zeros(pitch, dtype=torch.float32)
+        sy[col0:col0 + (c1 - c0)] = H.sigma_profile(nyp_global, h, pw, dy, vmax).float()[c0:c1]
+        if len(_PROFILE_CACHE) >= 64:
+            _PROFILE_CACHE.clear()
+        hit = _PROFILE_CACHE[key] = (sz.to(dev), sy.to(dev))
+    return hit
+
+
 class _Plan:
     """Everything about one call that does not depend on the direction of time."""
 
@@ -70,11 +89,8 @@ class _Plan:
         dti = torch.tensor(self.dti, dtype=torch.float32, device=self.dev)
         self.w = torch.zeros(self.nzp, self.pitch, dtype=torch.float32, device=self.dev)
         self.w[:, self.col0:self.col0 + self.nyp] = (vp * vp) * (dti * dti)
-        sz = H.sigma_profile(self.nzp, self.h, self.pw, self.dz, self.vmax).float()
-        sy = torch.zeros(self.pitch, dtype=torch.float32)
-        sy[self.col0:self.col0 + self.nyp] = H.sigma_profile(self.nyp_global, self.h, self.pw, self.dy,
-                                                             self.vmax).float()[self.c0:self.c1]
-        self.sigz, self.sigy = sz.to(self.dev), sy.to(self.dev)
+        self.sigz, self.sigy = _pml_profiles(self.nzp, self.nyp_global, self.h, self.pw, self.dz, self.dy, self.vmax,
+                                             self.pitch, self.col0, self.c0, self.c1, self.dev)
         self.n_fields, self.n_images = int(lay.wave_fields), int(lay.n_images)
 
     def desc(self, nsteps, adjoint, n_inj, n_smp) -> _lib.AcousticDesc:
