@@ -431,6 +431,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--shots", type=int, default=0, help="shots per GPU per step (0 = fit HBM, max 6)")
     ap.add_argument("--nt", type=int, default=0, help="override the number of time steps (tuning only)")
+    ap.add_argument("--halo-steps", type=int, default=0, help="slab workloads: steps between ghost exchanges (tuning only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg")
     args = ap.parse_args()
@@ -439,6 +440,8 @@ def main():
     w = dict(WORKLOADS[args.workload])
     if args.nt:
         w["nt"] = args.nt
+    if args.halo_steps and w.get("slabs"):
+        w["slabs"] = args.halo_steps
 
     if args.impl == "reference":
         run_reference(args, w)
