@@ -440,8 +440,6 @@ def main():
     w = dict(WORKLOADS[args.workload])
     if args.nt:
         w["nt"] = args.nt
-    if args.halo_steps and w.get("slabs"):
-        w["slabs"] = args.halo_steps
 
     if args.impl == "reference":
         run_reference(args, w)
@@ -451,6 +449,11 @@ def main():
     import physicsbasedfwi2_b200 as pkg
     from physicsbasedfwi2_b200 import _lib
     from physicsbasedfwi2_b200.distributed import allreduce_gradient
+    if w.get("slabs"):
+        # ghost-exchange interval: --halo-steps, else the package's own choice for this slab width
+        from physicsbasedfwi2_b200.slab import auto_halo_steps
+        world_env = int(os.environ.get("WORLD_SIZE", "1"))
+        w["slabs"] = args.halo_steps or auto_halo_steps(w["ny"] + 2 * (w["pml"] + w["order"] // 2), w["order"], world_env)
     from physicsbasedfwi2_b200.scalar import Propagator
     from physicsbasedfwi2_b200.wavelets import ricker
 

@@ -274,7 +274,8 @@ class Propagator(torch.nn.Module):
     inner steps instead of one snapshot per step, and the backward pass recomputes the snapshots
     of one K-step segment at a time: memory O(nt/K + K) fields instead of O(nt), one extra forward),
     ``slabs`` (True or a process group: x-slab domain decomposition of every shot over the ranks of
-    the group with ghost-zone exchange every ``halo_steps`` inner steps, see slab.py; every rank
+    the group with ghost-zone exchange every ``halo_steps`` inner steps - 'auto' picks the interval
+    from the slab width, slab.auto_halo_steps - see slab.py; every rank
     passes identical arguments and receives the full traces and the full gradient; ``exchange`` =
     'peer': ghost columns move by peer stores + flags inside the native time loop, 'p2p': by
     batched NCCL send/recv between halo_steps-long launches).
@@ -282,7 +283,7 @@ class Propagator(torch.nn.Module):
 
     def __init__(self, model: dict, dx, pml_width=None, survey_pad=None, vpmax=None, *,
                  accuracy: int = 4, loc_mode: str = "trunc", chunk_rows: int = 0, checkpoint_every: int = 0,
-                 slabs=False, halo_steps: int = 8, exchange: str = "peer"):
+                 slabs=False, halo_steps=8, exchange: str = "peer"):
         super().__init__()
         if not isinstance(model, dict) or "vp" not in model:
             raise RuntimeError("model must be a dict with key 'vp'")
@@ -315,7 +316,9 @@ class Propagator(torch.nn.Module):
         if slabs is not False and slabs is not None and checkpoint_every:
             raise RuntimeError("slabs and checkpoint_every cannot be combined")
         self.slabs = None if slabs is False else slabs
-        self.halo_steps = int(halo_steps)
+        self.halo_steps = 0 if halo_steps in (None, 'auto') else int(halo_steps)     # 0: slab.auto_halo_steps
+        if self.halo_steps < 0:
+            raise RuntimeError("halo_steps must be 'auto' or >= 1")
         if exchange not in ("peer", "p2p"):
             raise RuntimeError("exchange must be 'peer' (in-loop peer stores over NVLink) or 'p2p' (NCCL send/recv)")
         self.exchange = exchange

@@ -9,7 +9,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from physicsbasedfwi2_b200.slab import SlabGeometry, slab_columns
+from physicsbasedfwi2_b200.slab import SlabGeometry, auto_halo_steps, slab_columns
 
 
 def test_geometry_tiles_the_padded_grid():
@@ -38,6 +38,18 @@ def test_geometry_rejects_slabs_narrower_than_the_ghost_zone():
         SlabGeometry(120, 8, 4, 4, 0, 16)
     with pytest.raises(RuntimeError):
         SlabGeometry(120, 8, 4, 2, 0, 0)
+
+
+def test_auto_halo_steps_follows_the_slab_width():
+    # the two measured optima on the SEAM-sized grid (profiles/r01e_bench_c4dd_*): 2 ranks -> 32, 8 ranks -> 8
+    assert auto_halo_steps(3549, 8, 2) == 32
+    assert auto_halo_steps(3549, 8, 8) == 8
+    assert auto_halo_steps(3549, 8, 4) == 16
+    assert auto_halo_steps(104, 4, 2) == 4          # floor
+    assert auto_halo_steps(100000, 2, 1) == 32      # ceiling
+    for world in (1, 2, 3, 5, 8):                   # the choice always fits the geometry it is made for
+        T = auto_halo_steps(3549, 8, world)
+        SlabGeometry(3549, 8, 20, world, world - 1, T)
 
 
 def _free_port():
@@ -75,8 +87,8 @@ def _worker(rank, world, port, T, order, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,T,order", [(2, 4, 4), (3, 3, 8), (2, 1, 2), (1, 4, 4)])
-def test_slab_gradient_equals_undecomposed(world, T, order):
+@pytest.mark.parametrize("world,T,order", [(2, 4, 4), (3, 3, 8), (2, 1, 2), (1, 4, 4), (2, 0, 4)])
+def test_slab_gradient_equals_undecomposed(world, T, order):       # T = 0: the interval is chosen by auto_halo_steps
     out = mp.Manager().dict()
     mp.spawn(_worker, args=(world, _free_port(), T, order, out), nprocs=world, join=True)
     assert len(out) == world

@@ -86,7 +86,7 @@ def test_segmented_window_plan_on_one_gpu(cuda_lib, T, order):
 
 
 @pytest.mark.parametrize("exchange", ["peer", "p2p"])
-@pytest.mark.parametrize("T,order", [(8, 4), (4, 8), (1, 2)])
+@pytest.mark.parametrize("T,order", [(8, 4), (4, 8), (1, 2), ("auto", 4)])
 def test_two_gpu_slabs_match_oracle_and_single_gpu(cuda_lib, T, order, exchange):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs (gpurun --gpus 2)")
