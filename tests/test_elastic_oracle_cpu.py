@@ -88,3 +88,34 @@ def test_oracle_reproduces_committed_golden_vectors():
                                  pml_width=int(z["pml"]))
         for got, key in zip(out, ("rec", "grad_vp", "grad_vs", "grad_rho", "grad_src")):
             assert K.rel_l2(got, torch.from_numpy(z[key])) < 1e-5, (path, key)   # inputs were rounded to fp32
+
+
+def test_explosion_in_a_homogeneous_solid_is_a_pure_p_wave():
+    """Analytic pin of the elastic scheme: an explosive source (sxx = szz) in a homogeneous solid
+    radiates only a P wave.  It must travel at vp (not vs), decay as 1/sqrt(r) (2-D spreading), be
+    radially symmetric, and leave nothing in the S-arrival window."""
+    nz, ny, nt, dx, dt = 80, 120, 440, 10.0, 1e-3
+    vp = torch.full((nz, ny), 3000.0, dtype=torch.float64)
+    vs, rho = torch.full_like(vp, 1700.0), torch.full_like(vp, 2200.0)
+    x_s = torch.tensor([[[400.0, 300.0]]])
+    # vy lives at (i, j + 1/2): cells 50 / 80 / 9 of row 40 are 205 m, 505 m and -205 m from the source in y;
+    # vz lives at (i + 1/2, j): cells 60 / 19 of column 30 are +205 m / -205 m from it in z
+    cells = [(40, 50), (40, 80), (40, 9), (60, 30), (19, 30)]
+    x_r = torch.tensor([[[z * dx, y * dx] for z, y in cells]])
+    src = K.ricker(15.0, nt, dt, 1 / 15.0).reshape(-1, 1, 1).double() * 1e6
+    with torch.no_grad():
+        r = E.elastic_forward(vp, vs, rho, dx, src, x_s, x_r, dt, order=8, pml_width=10)
+    vy, vz = r[0, :, 0], r[1, :, 0]
+    near, far = vy[:, 0], vy[:, 1]
+    lags = list(range(60, 200))
+    cc = [float((near[:nt - l] * far[l:]).sum()) for l in lags]
+    lag = lags[max(range(len(cc)), key=lambda i: cc[i])]
+    assert abs(lag - 300.0 / 3000.0 / dt) <= 1, lag                       # (505 - 205) m at vp: 100 samples (176 at vs)
+    ratio = float(near.abs().max() / far.abs().max()) ** 2
+    assert abs(ratio - 505.0 / 205.0) < 0.1 * 505.0 / 205.0, ratio        # cylindrical spreading
+    peak = float(near.abs().max())
+    assert float((vy[:, 0] + vy[:, 2]).abs().max()) < 1e-3 * peak         # left / right mirror, opposite sign
+    assert float((vz[:, 3] + vz[:, 4]).abs().max()) < 1e-3 * peak         # below / above
+    assert float((vz[:, 3] - vy[:, 0]).abs().max()) < 1e-3 * peak         # same radial motion along z as along y
+    s_arrival = int((505.0 / 1700.0 + 1 / 15.0) / dt)                     # where an S wave would peak at the far receiver
+    assert float(far[s_arrival - 35:s_arrival + 65].abs().max()) < 0.02 * float(far.abs().max())
