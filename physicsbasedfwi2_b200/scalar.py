@@ -15,6 +15,7 @@ from __future__ import annotations
 import ctypes as C
 from typing import Optional
 
+import numpy as np
 import torch
 import torch.nn.functional as F
 
@@ -86,9 +87,12 @@ class _Plan:
         self.v_pad_global = vp
         vp = vp[:, self.c0:self.c1]
         self.v_pad = vp
-        dti = torch.tensor(self.dti, dtype=torch.float32, device=self.dev)
+        # dt^2 rounded the way an fp32 tensor product would (no host->device scalar copy: that copy is a
+        # synchronisation point and would stop the host from preparing this call under the previous one's kernels)
+        dti32 = np.float32(self.dti)
+        dt2 = float(np.float32(dti32 * dti32))
         self.w = torch.zeros(self.nzp, self.pitch, dtype=torch.float32, device=self.dev)
-        self.w[:, self.col0:self.col0 + self.nyp] = (vp * vp) * (dti * dti)
+        self.w[:, self.col0:self.col0 + self.nyp] = (vp * vp) * dt2
         self.sigz, self.sigy = _pml_profiles(self.nzp, self.nyp_global, self.h, self.pw, self.dz, self.dy, self.vmax,
                                              self.pitch, self.col0, self.c0, self.c1, self.dev)
         self.n_fields, self.n_images = int(lay.wave_fields), int(lay.n_images)
@@ -172,8 +176,14 @@ class _ScalarFunction(torch.autograd.Function):
         dev = plan.dev
         s_cell, s_z, s_y, bad_s = plan.points(x_s, "source", loc_mode)
         r_cell, r_z, r_y, bad_r = plan.points(x_r, "receiver", loc_mode)
-        if bool((bad_s | bad_r).item()):
-            raise RuntimeError("source/receiver location outside the model")
+        # The out-of-model flag travels to pinned memory ahead of the forward launch and is read after it:
+        # the host only waits for work queued before this call, never for this call's own kernels, so the
+        # caller can queue its loss and backward pass while the forward pass runs (points are clamped:
+        # the launch itself is safe either way).
+        bad_host = torch.empty(1, dtype=torch.bool, pin_memory=True)
+        bad_host.copy_((bad_s | bad_r).reshape(1), non_blocking=True)
+        bad_event = torch.cuda.Event()
+        bad_event.record(torch.cuda.current_stream(dev))
         amp = H.resample_up(source_amplitudes.detach().to(dev, torch.float32), plan.ratio).contiguous()
         nti = nt * plan.ratio
         need_v = ctx.needs_input_grad[0]
@@ -200,6 +210,9 @@ class _ScalarFunction(torch.autograd.Function):
                 q = torch.empty(nti * S * plan.stride, dtype=torch.float32, device=dev)
             rec = plan.run(nsteps=nti, adjoint=0, inj=plan.lists(s_cell), inj_amp=amp,
                            smp_cell=r32, n_smp=R, q_write=q)
+        bad_event.synchronize()
+        if bool(bad_host[0]):
+            raise RuntimeError("source/receiver location outside the model")
         out = rec[::plan.ratio].contiguous() if plan.ratio > 1 else rec
         ctx.plan = plan
         ctx.q = q
