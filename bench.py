@@ -9,10 +9,13 @@ of one BATCH of shots per GPU; the 256-shot survey is 256 / (batch x n_gpus) suc
 after the other exactly as the reference mini-batches its shots (models/networks.py:5454-5461).
 The batch is what fits HBM with one snapshot per inner step (k = 1, the parity-graded mode).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--survey]
 
-Under torchrun (N > 1) every rank runs its own shot batch (weak scaling) and the model gradient
-is summed with one NCCL allreduce inside the timed region.  One JSON line on rank 0.
+One step (default, c2) = the gradient of the 32 shots a GPU owns when the 256-shot survey is sharded over 8 GPUs
+(six launches of 6 6 5 5 5 5 shots, gradients accumulated, ONE allreduce): per-GPU work is fixed ("weak") and the
+8-GPU run is the north star's survey itself.  --survey: one step = all 256 shots sharded over the N ranks ("strong").
+Under torchrun (N > 1) a small multi-GPU correctness check runs ahead of the timed region ("multi_gpu_check").
+One JSON line on rank 0, with "roofline", "cpu_baseline", "parity" (GPU vs the CPU sample) and "e2e".
 
 cell-update = one interior model cell advanced one inner time step in one pass for one shot;
 work per step = nz*ny*nt*shots*2.
@@ -158,38 +161,76 @@ def hbm_peak():
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU arm: the oracle port timed on the host cores (cpu_baseline leg and --impl reference)
+# CPU arm: the oracle port timed on the host cores.  ONE code path serves both the --impl reference arm
+# and the GPU arm's cpu_baseline leg (which runs it in a fresh subprocess, so the number does not depend
+# on what the CUDA context, pinned buffers and NCCL threads of the GPU process do to the host).
 # ------------------------------------------------------------------------------------------------
-def cpu_gradient_sample(w, n_steps, v=None):
-    """One fwd+adjoint gradient of ONE shot for n_steps on the C/OpenMP oracle; returns seconds."""
-    from oracle import cpu_ref as O
+def cpu_sample_inputs(w, n_steps):
+    """The bounded sample both CPU legs and the bench line's parity block use: the middle shot of the survey,
+    the first n_steps of the record, misfit 0.5 |rec - obs|^2 against seeded synthetic 'observed' data."""
     from physicsbasedfwi2_b200.wavelets import ricker
-    if v is None:
-        v = synth_model(w)
     x_s, x_r = synth_survey(w, 1, first_shot=w["survey_shots"] // 2)
-    src = ricker(w["freq"], n_steps, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1)
-    g = torch.Generator().manual_seed(2)
-    resid = torch.randn(n_steps, 1, w["n_rec"], generator=g)
-    t0 = time.perf_counter()
-    O.acoustic_gradient(v, w["dx"], src, x_s, x_r, w["dt"], grad_rec=resid, order=w["order"],
-                        pml_width=w["pml"], vpmax=w["vmax"], dtype=torch.float32)
-    return time.perf_counter() - t0
+    src = ricker(w["freq"], n_steps, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1).contiguous()
+    obs = torch.randn(n_steps, 1, w["n_rec"], generator=torch.Generator().manual_seed(2)).mul_(1e-3)
+    return x_s, x_r, src, obs
 
 
-def cpu_baseline(w, target_s=12.0):
+def cpu_reference(w, steps, warmup, step_seconds=6.0, max_steps=400, dump=None):
+    """Times `steps` fwd+adjoint gradients of the bounded sample on the C/OpenMP oracle with every host
+    thread (set explicitly: torchrun exports OMP_NUM_THREADS=1).  Snapshot buffers are allocated and touched
+    once (warm-up) and reused.  Returns the cpu_baseline dict; `dump`: path of an .npz that receives the
+    sample's traces and gradient for the parity block."""
     from oracle import cpu_ref as O
     O.build()
-    cells = w["nz"] * w["ny"]
+    cores = O.set_threads(os.cpu_count() or 1)
     v = synth_model(w)
-    probe = min(w["nt"], 40)
-    t = cpu_gradient_sample(w, probe, v)                       # also warms the page cache / threads
-    per_step = t / probe
-    n = int(max(probe, min(w["nt"], target_s / max(per_step, 1e-9), 600)))
-    t = cpu_gradient_sample(w, n, v)
-    val = cells * n * 2 / t / 1e9
-    return {"value": round(val, 4), "unit": "Gcell-updates/s", "cores": O.num_threads(), "kind": "port",
-            "sample": f"1 shot x {n} of {w['nt']} steps, fwd+adjoint, same grid/order/PML, fp32, "
-                      f"oracle/cpu_ref.c with OpenMP ({t:.1f} s)", "seconds": round(t, 2)}
+    kw = dict(order=w["order"], pml_width=w["pml"], vpmax=w["vmax"], dtype=torch.float32)
+    ws = {}
+
+    def gradient(n):
+        x_s, x_r, src, obs = cpu_sample_inputs(w, n)
+        t0 = time.perf_counter()
+        out = O.acoustic_gradient(v, w["dx"], src, x_s, x_r, w["dt"], observed=obs, workspace=ws, **kw)
+        return time.perf_counter() - t0, out
+
+    probe = min(w["nt"], 24)
+    gradient(probe)                                             # threads, page cache
+    per_step = gradient(probe)[0] / probe
+    n = int(max(10, min(w["nt"], step_seconds / max(per_step, 1e-9), max_steps)))
+    t_warm = gradient(n)[0]                                     # first touch of the n-step snapshot buffer
+    if t_warm > 1.3 * step_seconds:                             # the short probe ran from cache: resize the sample
+        n = int(max(10, n * step_seconds / t_warm))
+        gradient(n)
+    for _ in range(max(0, warmup - 1)):
+        gradient(n)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        _, out = gradient(n)
+    t = time.perf_counter() - t0
+    val = w["nz"] * w["ny"] * n * 2 * steps / t / 1e9
+    if dump:
+        import numpy as np
+        np.savez(dump, rec=out[0].numpy(), grad_v=out[1].numpy(), n=n)
+    return {"value": round(val, 4), "unit": "Gcell-updates/s", "cores": cores, "kind": "port",
+            "sample": f"1 shot x {n} of {w['nt']} steps per step, fwd+adjoint, same grid/order/PML, fp32, "
+                      f"oracle/cpu_ref.c OpenMP, {steps} timed + {max(1, warmup)} warm-up repeats, buffers reused",
+            "seconds": round(t, 2), "sample_steps": n, "ms_per_step": round(1e3 * t / steps, 3)}
+
+
+def cpu_baseline(w, dump=None):
+    """cpu_baseline leg of the GPU arm: the reference arm's own code in a fresh process (2 timed repeats)."""
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--workload", w["name"],
+           "--steps", "2", "--warmup", "1", "--nt", str(w["nt"])]
+    if dump:
+        cmd += ["--dump", dump]
+    env = dict(os.environ)
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "OMP_NUM_THREADS"):
+        env.pop(k, None)
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=900)
+    if r.returncode != 0:
+        raise RuntimeError("cpu_baseline subprocess failed:\n" + r.stdout[-2000:] + r.stderr[-2000:])
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    return line["cpu_baseline"]
 
 
 def cpu_baseline_elastic(w, n=5):
@@ -218,34 +259,25 @@ def cpu_baseline_elastic(w, n=5):
 
 def run_reference(args, w):
     """--impl reference: the reference's CPU path for this workload.  The reference's propagators
-    (deepwave, DENISE) are external and absent, so this is the oracle port (kind 'port')."""
+    (deepwave, DENISE) are external and absent, so this is the oracle port (kind 'port').  Under torchrun
+    rank 0 alone runs it, with every host thread."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle import cpu_ref as O
-    O.build()
-    cells = w["nz"] * w["ny"]
-    v = synth_model(w)
-    probe = min(w["nt"], 30)
-    per_step = cpu_gradient_sample(w, probe, v) / probe
-    n = int(max(10, min(w["nt"], 6.0 / max(per_step, 1e-9), 400)))
-    for _ in range(args.warmup):
-        cpu_gradient_sample(w, n, v)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        cpu_gradient_sample(w, n, v)
-    t = time.perf_counter() - t0
-    val = cells * n * 2 * args.steps / t / 1e9
-    sample = f"1 shot x {n} of {w['nt']} steps per step, fwd+adjoint, fp32, oracle/cpu_ref.c OpenMP"
+    if w.get("elastic"):
+        cb = cpu_baseline_elastic(w)
+        ms = 1e3 * cb["seconds"]
+    else:
+        cb = cpu_reference(w, args.steps, args.warmup, dump=args.dump)
+        ms = cb["ms_per_step"]
+    val = cb["value"]
     line = {"impl": "reference", "metric": "FWI gradient Gcell-updates/s (fwd+adjoint)",
-            "value": round(val, 4), "unit": "Gcell-updates/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(1e3 * t / args.steps, 3),
+            "value": val, "unit": "Gcell-updates/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": bench_config(w, 1, 1, args.workload),
-            "cpu_baseline": {"value": round(val, 4), "unit": "Gcell-updates/s", "cores": O.num_threads(),
-                             "kind": "port", "sample": sample},
-            "e2e": {"value": round(val, 4), "unit": "Gcell-updates/s", "h2d_bytes_per_step": 0,
-                    "d2h_bytes_per_step": 0},
+            "cpu_baseline": cb,
+            "e2e": {"value": val, "unit": "Gcell-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
@@ -385,8 +417,8 @@ def run_c5(args, w, dev, rank, world, local):
     ms, clocks, _ = timed(lambda: iteration(gathers_d), args.steps, ClockSampler(local))
     launches = pkg.kernel_launches() - n0
     loops, _lib.LOOP_TIMES = _lib.LOOP_TIMES, None
-    t_fwd = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag.endswith("_fwd")]
-    t_adj = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag.endswith("_adj")]
+    t_fwd = [a.elapsed_time(b) / n for tag, a, b, n, _ in loops if tag.endswith("_fwd")]
+    t_adj = [a.elapsed_time(b) / n for tag, a, b, n, _ in loops if tag.endswith("_adj")]
     ms_fwd, ms_adj = sum(t_fwd) / len(t_fwd), sum(t_adj) / len(t_adj)
     from physicsbasedfwi2_b200 import _host
     nti = nt * _host.inner_step(w["dt"], w["dx"], w["dx"], w["vmax"])[0]
@@ -422,6 +454,328 @@ def run_c5(args, w, dev, rank, world, local):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def split_batches(n_shots, cap):
+    """[lo, hi) ranges of the launches one rank makes for n_shots shots, at most `cap` shots per launch, sizes
+    as even as possible (32 shots, cap 6 -> 6 6 5 5 5 5 rather than 6 6 6 6 6 2)."""
+    if n_shots <= 0:
+        return []
+    nb = -(-n_shots // cap)
+    base, extra = divmod(n_shots, nb)
+    out, lo = [], 0
+    for k in range(nb):
+        hi = lo + base + (1 if k < extra else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+def multi_gpu_check(w, dev, rank, world):
+    """Driver-visible multi-GPU correctness, run under torchrun ahead of the timed region (the 2-GPU pytest cases
+    skip on a 1-GPU test box).  Shot-parallel: the N-rank gradient (shards + one allreduce) against rank 0
+    computing every shot alone.  Slab workloads: the x-slab result against the undecomposed run."""
+    import torch.distributed as dist
+    from physicsbasedfwi2_b200.distributed import allreduce_gradient, shard_bounds
+    from physicsbasedfwi2_b200.scalar import Propagator
+    from physicsbasedfwi2_b200.wavelets import ricker
+    small = dict(w, nz=160, ny=520 if not w.get("slabs") else 96 * world + 40, nt=240, n_rec=64, rec_stride=4,
+                 survey_shots=2 * world)
+    if w.get("slabs"):
+        small["survey_shots"] = 2
+    v = synth_model(small).to(dev)
+    S = small["survey_shots"]
+    x_s, x_r = synth_survey(small, S)
+    src = ricker(small["freq"], small["nt"], small["dt"], 1.0 / small["freq"]).reshape(-1, 1, 1).repeat(1, S, 1).contiguous()
+    obs = torch.randn(small["nt"], S, small["n_rec"], generator=torch.Generator().manual_seed(5)).mul_(1e-3)
+    x_s, x_r, src, obs = (t.to(dev) for t in (x_s, x_r, src, obs))
+    kw = dict(pml_width=small["pml"], accuracy=small["order"], vpmax=small["vmax"])
+
+    def grad(lo, hi, **extra):
+        vg = v.clone().requires_grad_(True)
+        rec = Propagator({"vp": vg}, small["dx"], **kw, **extra)(src[:, lo:hi], x_s[lo:hi], x_r[lo:hi], small["dt"])
+        loss = 0.5 * ((rec - obs[:, lo:hi]) ** 2).sum()
+        loss.backward()
+        return vg.grad, loss.detach(), rec.detach()
+
+    def rel(a, b):
+        return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-300))
+
+    out = {"grid": f"{small['nz']}x{small['ny']}", "shots": S, "steps": small["nt"], "ranks": world}
+    if w.get("slabs"):
+        g_dd, l_dd, rec_dd = grad(0, S, slabs=True, halo_steps=4)
+        g_1, l_1, rec_1 = grad(0, S)
+        out.update(mode="x-slab vs undecomposed", traces=rel(rec_dd, rec_1), grad_v=rel(g_dd, g_1),
+                   loss=abs(float(l_dd) - float(l_1)) / abs(float(l_1)))
+        ok = out["traces"] <= 1e-5 and out["grad_v"] <= 1e-4
+    else:
+        lo, hi = shard_bounds(S, rank, world)
+        g_loc, l_loc, _ = grad(lo, hi)
+        g_n, l_n = allreduce_gradient(g_loc, l_loc)
+        g_1, l_1, _ = grad(0, S)                 # every rank computes the reference; rank 0's comparison is reported
+        out.update(mode="shot-parallel N ranks + one allreduce vs one GPU", grad_v=rel(g_n, g_1),
+                   loss=abs(float(l_n) - float(l_1)) / abs(float(l_1)))
+        ok = out["grad_v"] <= 1e-6 and out["loss"] <= 1e-6
+    flag = torch.tensor([1.0 if ok else 0.0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    out["ok"] = bool(flag.item() == 1.0)
+    for k in ("traces", "grad_v", "loss"):
+        if k in out:
+            out[k] = float(f"{out[k]:.3e}")
+    return out
+
+
+def run_gpu(args, w, dev, rank, world, local):
+    import torch.distributed as dist
+    import physicsbasedfwi2_b200 as pkg
+    from physicsbasedfwi2_b200 import _host, _lib
+    from physicsbasedfwi2_b200.distributed import allreduce_gradient, shard_bounds
+    from physicsbasedfwi2_b200.scalar import Propagator
+    from physicsbasedfwi2_b200.wavelets import ricker
+
+    nz, ny, nt = w["nz"], w["ny"], w["nt"]
+    elastic, slabs = bool(w.get("elastic")), bool(w.get("slabs"))
+    P = w["pml"] + w["order"] // 2
+    nti = nt * (1 if elastic else _host.inner_step(w["dt"], w["dx"], w["dx"], w["vmax"])[0])
+    # shots per launch: one q snapshot per inner step per shot must fit HBM next to the wavefields
+    per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nti + 8) * (5 if elastic else 1)
+    if w.get("ckpt"):
+        per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (6 * (nti // w["ckpt"] + 2) + w["ckpt"] + 24)
+    if slabs:
+        cols = (ny + 2 * P) // world + 2 * w["slabs"] * (w["order"] // 2) + 64
+        per_shot = (nz + 2 * P) * cols * 4 * (nti + 16)
+    free, _ = torch.cuda.mem_get_info(dev)
+    # 6 shots per launch is where the C2 kernel pair was tuned (7 fit, but leave the allocator no slack)
+    full_nt = WORKLOADS[args.workload]["nt"]              # the cap must not change with a --nt override (ncu runs)
+    cap = 16 if (w.get("ckpt") or per_shot * (full_nt / nt) < (2 << 30)) else 6
+    cap = args.shots or max(1, min(cap, w["survey_shots"], int((0.6 if w.get("ckpt") else 0.88) * free // per_shot)))
+
+    # shots of one step on this rank.  Default for the shot-parallel acoustic survey (C2): the 1/8 slice of the
+    # survey a GPU owns when the 256 shots are sharded over 8 GPUs (32 shots = six launches of 6 6 5 5 5 5), so
+    # that the 8-GPU point IS the north star's survey and the smaller N are the same per-GPU work ("weak").
+    # --survey: the whole survey sharded over the N ranks ("strong").  Other workloads: one launch per step.
+    total = w["survey_shots"]
+    if args.survey and not slabs:
+        lo, hi = shard_bounds(total, rank, world)
+        first, n_rank, scaling = lo, hi - lo, "strong"
+    elif args.workload == "c2" and not args.shots and not args.one_batch:
+        n_rank = max(1, total // 8)
+        first, scaling = (rank * n_rank) % total, "weak"
+    else:
+        n_rank, first, scaling = cap, (0 if slabs else rank * cap), ("strong" if slabs else "weak")
+    batches = split_batches(n_rank, cap)
+    shots_step = n_rank if slabs else (total if scaling == "strong" else n_rank * world)
+
+    v_host = synth_model(w).pin_memory()
+    x_s_h, x_r_h = synth_survey(w, n_rank, first_shot=first)
+    src_h = ricker(w["freq"], nt, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1).repeat(1, n_rank, 1).contiguous().pin_memory()
+    gen = torch.Generator().manual_seed(2 + (0 if slabs else rank))
+    obs_shape = (2, nt, n_rank, w["n_rec"]) if elastic else (nt, n_rank, w["n_rec"])
+    obs_h = torch.randn(*obs_shape, generator=gen).mul_(1e-3).pin_memory()   # "observed" data
+    x_s_h, x_r_h = x_s_h.pin_memory(), x_r_h.pin_memory()
+    grad_h = torch.empty(nz, ny).pin_memory()
+    loss_h = torch.empty(1).pin_memory()
+
+    def gradient(v_d, src_d, xs_d, xr_d, obs_d):
+        """The call sequence of the reference (models/networks.py:5449,5464,5476,5491) for one launch of shots."""
+        v_d = v_d.detach().requires_grad_(True)
+        if elastic:
+            vs_d = v_d.detach() / math.sqrt(3.0)
+            vs_d[:24] = 0.0
+            rho_d = 310.0 * v_d.detach() ** 0.25
+            prop = pkg.Propagator({"vp": v_d, "vs": vs_d, "rho": rho_d}, w["dx"], pml_width=w["pml"],
+                                  accuracy=w["order"], vpmax=w["vmax"])
+        else:
+            prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"],
+                              checkpoint_every=w.get("ckpt", 0), slabs=slabs and world > 1,
+                              halo_steps=w.get("slabs") or 8)
+        rec = prop(src_d, xs_d, xr_d, w["dt"])
+        loss = 0.5 * ((rec - obs_d) ** 2).sum()
+        loss.backward()
+        return v_d.grad, loss.detach()
+
+    sdim = 2 if elastic else 1          # shot dimension of the observed data
+    # per-launch inputs: pinned host copies (the e2e leg uploads them every step) and device-resident ones
+    host_b = [tuple(t.narrow(d, lo, hi - lo).contiguous().pin_memory()
+                    for t, d in ((src_h, 1), (x_s_h, 0), (x_r_h, 0), (obs_h, sdim))) for lo, hi in batches]
+    dev_b = [tuple(t.to(dev) for t in hb) for hb in host_b]
+    v_d = v_host.to(dev)
+
+    def step(v_in, per_launch, to_dev):
+        """All launches of this rank's shots, gradients accumulated, then ONE allreduce."""
+        v_cur = to_dev(v_in)
+        g_acc, l_acc = None, None
+        for tens in per_launch:
+            g, l = gradient(v_cur, *(to_dev(t) for t in tens))
+            g_acc = g if g_acc is None else g_acc.add_(g)
+            l_acc = l if l_acc is None else l_acc + l
+        if slabs:
+            return g_acc, l_acc           # slab mode: traces and gradient are already whole on every rank
+        return allreduce_gradient(g_acc, l_acc)
+
+    def step_resident():
+        return step(v_d, dev_b, lambda t: t)
+
+    def step_e2e():
+        g, l = step(v_host, host_b, lambda t: t.to(dev, non_blocking=True))
+        grad_h.copy_(g, non_blocking=True)
+        loss_h.copy_(l.reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return g, l
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, sampler=None):
+        barrier()
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), clocks, out
+
+    mgc = None
+    if world > 1 and not elastic and not args.no_check:
+        mgc = multi_gpu_check(w, dev, rank, world)
+
+    for _ in range(args.warmup):
+        g, l = step_resident()
+    torch.cuda.synchronize()
+    if not bool(torch.isfinite(g).all()) or not math.isfinite(float(l.detach())):
+        raise RuntimeError("non-finite gradient / misfit in the benchmark step")
+
+    _lib.LOOP_TIMES = []
+    n0 = pkg.kernel_launches()
+    ms, clocks, _ = timed(step_resident, args.steps, ClockSampler(local))
+    launches = pkg.kernel_launches() - n0
+    loops = _lib.LOOP_TIMES
+    _lib.LOOP_TIMES = None
+
+    cells = nz * ny
+    work = cells * nti * shots_step * 2                 # cell-updates (inner steps) per step, whole job
+    value = work * args.steps / (ms * 1e-3) / 1e9
+
+    e2e = None
+    if not args.no_e2e:
+        e_steps = args.steps if ms / args.steps < 2500 else max(1, min(args.steps, 3))   # long steps: 3 e2e repeats
+        step_e2e()
+        ms_e, _, _ = timed(step_e2e, e_steps)
+        h2d = v_host.numel() * 4 + sum(t.numel() * t.element_size() for hb in host_b for t in hb)
+        d2h = grad_h.numel() * 4 + 4
+        e2e = {"value": round(work * e_steps / (ms_e * 1e-3) / 1e9, 3), "unit": "Gcell-updates/s",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e_steps,
+               "ms_per_step": round(ms_e / e_steps, 3)}
+
+    # ---- roofline from the native time loops of the timed region (CUDA events on the launching stream) ----
+    # per pass: algorithmic bytes per cell-update (DESIGN.md 5.1): forward + snapshot 20 B, adjoint + imaging 28 B,
+    # forward only (checkpoint pass, MODE 0) 16 B; elastic 80 / 120 B
+    bytes_of = {"acoustic_fwd": B_FWD, "acoustic_fwd0": 16.0, "acoustic_adj": B_ADJ,
+                "elastic_fwd": B_FWD_EL, "elastic_adj": B_ADJ_EL}
+    div = world if slabs else 1                          # a slab launch advances 1/world of each shot
+    agg = {}
+    for tag, a, b, n, shots in loops:
+        t = agg.setdefault(tag, {"ms": 0.0, "launches": 0, "bytes": 0.0, "cell_updates": 0.0})
+        t["ms"] += a.elapsed_time(b)
+        t["launches"] += n
+        t["cell_updates"] += float(cells) * shots * n / div
+        t["bytes"] += float(cells) * shots * n / div * bytes_of[tag]
+
+    if rank == 0:
+        peak, peak_src = hbm_peak()
+        tot_ms = sum(t["ms"] for t in agg.values())
+        tot_bytes = sum(t["bytes"] for t in agg.values())
+        ach = tot_bytes / (tot_ms * 1e-3) / 1e9
+        kname = ("elastic step (f1 + f2 forward, b2 + b1 fused adjoint; one time step = one 'launch')"
+                 if elastic else "acoustic_step_kernel (forward MODE 1 + adjoint MODE 2" +
+                 (" + forward-only MODE 0 of the checkpoint pass)" if "acoustic_fwd0" in agg else " pair)"))
+        roof = {"bound": "hbm", "kernel": kname, "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(ach / peak, 4), "algorithmic_frac": round(ach / peak, 4), "dram_frac": None,
+                "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_cell_update": {k: bytes_of[k] for k in agg},
+                "kernel_share_of_step": round(tot_ms / ms, 4)}
+        names = {"acoustic_fwd": "forward", "acoustic_fwd0": "forward_only", "acoustic_adj": "adjoint",
+                 "elastic_fwd": "forward", "elastic_adj": "adjoint"}
+        for tag, t in agg.items():
+            a_k = t["bytes"] / (t["ms"] * 1e-3) / 1e9
+            roof[names[tag]] = {"ms_per_launch": round(t["ms"] / t["launches"], 5), "launches": t["launches"],
+                                "achieved": round(a_k, 1), "frac": round(a_k / peak, 4)}
+        # measured DRAM traffic (ncu --set full, one launch of each kernel at the 6-shot launch size; profiles/)
+        prof = os.path.join(ROOT, "profiles", "traffic.json")
+        tr = None
+        if os.path.exists(prof):
+            try:
+                tr = json.load(open(prof)).get(args.workload)
+            except Exception:
+                tr = None
+        if tr:
+            roof["traffic"] = tr
+            fwd_k, adj_k = ("elastic_fwd", "elastic_adj") if elastic else ("acoustic_fwd", "acoustic_adj")
+            s_ref = float(tr.get("shots_per_launch", 6 if not elastic else 5))
+            if fwd_k in agg and adj_k in agg and len(agg) == 2:
+                # scale the captured bytes per launch to the launches timed here by their shot counts
+                dram = sum(tr[k2] * agg[k]["cell_updates"] / (cells * s_ref / div)
+                           for k, k2 in ((fwd_k, "forward_bytes_per_launch"), (adj_k, "adjoint_bytes_per_launch")))
+                roof["dram_frac"] = round(dram / (tot_ms * 1e-3) / 1e9 / peak, 4)
+        cfg = bench_config(w, cap, world, args.workload)
+        cfg.update(shots_per_gpu_per_step=n_rank, launches_per_gpu_per_step=[hi - lo for lo, hi in batches],
+                   shots_per_step=shots_step, first_shot_of_rank0=first,
+                   survey=("whole 256-shot survey sharded over the ranks, one allreduce" if scaling == "strong" and not slabs
+                           else f"{n_rank} shots per GPU per step (the per-GPU share of the survey on 8 GPUs), one allreduce per step"))
+        line = {"metric": "FWI gradient Gcell-updates/s (fwd+adjoint)", "value": round(value, 3),
+                "unit": "Gcell-updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": scaling,
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg, "roofline": roof,
+                "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}
+        if mgc is not None:
+            line["multi_gpu_check"] = mgc
+        if world == 1 and not args.no_cpu:
+            if elastic:
+                line["cpu_baseline"] = cpu_baseline_elastic(w)
+            else:
+                import tempfile
+                dump = os.path.join(tempfile.gettempdir(), f"fwi_bench_cpu_{os.getpid()}.npz")
+                line["cpu_baseline"] = cpu_baseline(w, dump=dump)
+                line["parity"] = parity_block(w, dump, dev)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def parity_block(w, dump, dev):
+    """The CPU sample the cpu_baseline leg just ran (one shot, n steps; traces and model gradient kept in `dump`)
+    recomputed on the GPU through the public API: rel-L2 of traces and gradient (north star: 1e-5 / 1e-4)."""
+    import numpy as np
+    from physicsbasedfwi2_b200.scalar import Propagator
+    z = np.load(dump)
+    n = int(z["n"])
+    x_s, x_r, src, obs = (t.to(dev) for t in cpu_sample_inputs(w, n))
+    vg = synth_model(w).to(dev).requires_grad_(True)
+    rec = Propagator({"vp": vg}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"])(src, x_s, x_r, w["dt"])
+    (0.5 * ((rec - obs) ** 2).sum()).backward()
+
+    def rel(a, b):
+        a, b = a.detach().double().cpu(), torch.from_numpy(b).double()
+        return float(f"{float((a - b).norm() / b.norm()):.3e}")
+    out = {"traces": rel(rec, z["rec"]), "grad_v": rel(vg.grad, z["grad_v"]),
+           "sample": f"1 shot x {n} steps of this workload, GPU (public API) vs oracle/cpu_ref.c fp32",
+           "tolerance": {"traces": 1e-5, "grad_v": 1e-4}}
+    out["ok"] = out["traces"] <= 1e-5 and out["grad_v"] <= 1e-4
+    try:
+        os.remove(dump)
+    except OSError:
+        pass
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -434,10 +788,15 @@ def main():
     ap.add_argument("--halo-steps", type=int, default=0, help="slab workloads: steps between ghost exchanges (tuning only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg")
+    ap.add_argument("--survey", action="store_true", help="one step = the WHOLE survey sharded over the ranks (strong scaling)")
+    ap.add_argument("--one-batch", action="store_true", help="c2: one launch of shots per step instead of the 32-shot slice")
+    ap.add_argument("--no-check", action="store_true", help="skip the multi-GPU correctness check ahead of the timed region")
+    ap.add_argument("--dump", default=None, help="--impl reference: .npz receiving the CPU sample's traces / gradient")
     args = ap.parse_args()
-    if args.warmup < 3:
+    if args.warmup < 3 and args.impl != "reference":
         args.warmup = 3
     w = dict(WORKLOADS[args.workload])
+    w["name"] = args.workload
     if args.nt:
         w["nt"] = args.nt
 
@@ -474,154 +833,7 @@ def main():
     if w.get("e2e_iteration"):
         return run_c5(args, w, dev, rank, world, local)
 
-    nz, ny, nt = w["nz"], w["ny"], w["nt"]
-    # shots per step: one q snapshot per inner step per shot must fit HBM next to the wavefields
-    P = w["pml"] + w["order"] // 2
-    from physicsbasedfwi2_b200 import _host
-    nti = nt * (1 if w.get("elastic") else _host.inner_step(w["dt"], w["dx"], w["dx"], w["vmax"])[0])
-    per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nti + 8) * (5 if w.get("elastic") else 1)
-    if w.get("ckpt"):
-        per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (6 * (nti // w["ckpt"] + 2) + w["ckpt"] + 24)
-    if w.get("slabs"):
-        cols = (ny + 2 * P) // world + 2 * w["slabs"] * (w["order"] // 2) + 64
-        per_shot = (nz + 2 * P) * cols * 4 * (nti + 16)
-    free, _ = torch.cuda.mem_get_info(dev)
-    # 6 shots per launch is where the C2 kernel pair was tuned (7 fit, but run at 67 % instead of 75 % of the roofline)
-    full_nt = WORKLOADS[args.workload]["nt"]              # the cap must not change with a --nt override (ncu runs)
-    cap = 16 if (w.get("ckpt") or per_shot * (full_nt / nt) < (2 << 30)) else 6
-    batch = args.shots or max(1, min(cap, w["survey_shots"], int((0.6 if w.get("ckpt") else 0.88) * free // per_shot)))
-
-    v_host = synth_model(w).pin_memory()
-    x_s_h, x_r_h = synth_survey(w, batch, first_shot=0 if w.get("slabs") else rank * batch)
-    src_h = ricker(w["freq"], nt, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1).repeat(1, batch, 1).contiguous().pin_memory()
-    gen = torch.Generator().manual_seed(2 + (0 if w.get("slabs") else rank))
-    obs_shape = (2, nt, batch, w["n_rec"]) if w.get("elastic") else (nt, batch, w["n_rec"])
-    obs_h = torch.randn(*obs_shape, generator=gen).mul_(1e-3).pin_memory()   # "observed" data
-    x_s_h, x_r_h = x_s_h.pin_memory(), x_r_h.pin_memory()
-    grad_h = torch.empty(nz, ny).pin_memory()
-    loss_h = torch.empty(1).pin_memory()
-
-    def gradient(v_d, src_d, xs_d, xr_d, obs_d):
-        """The call sequence of the reference (models/networks.py:5449,5464,5476,5491)."""
-        v_d = v_d.detach().requires_grad_(True)
-        if w.get("elastic"):
-            vs_d = v_d.detach() / math.sqrt(3.0)
-            vs_d[:24] = 0.0
-            rho_d = 310.0 * v_d.detach() ** 0.25
-            prop = pkg.Propagator({"vp": v_d, "vs": vs_d, "rho": rho_d}, w["dx"], pml_width=w["pml"],
-                                  accuracy=w["order"], vpmax=w["vmax"])
-        else:
-            prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"],
-                              checkpoint_every=w.get("ckpt", 0), slabs=bool(w.get("slabs")) and world > 1,
-                              halo_steps=w.get("slabs") or 8)
-        rec = prop(src_d, xs_d, xr_d, w["dt"])
-        loss = 0.5 * ((rec - obs_d) ** 2).sum()
-        loss.backward()
-        if w.get("slabs"):
-            return v_d.grad, loss           # slab mode: traces and gradient are already whole on every rank
-        g, l = allreduce_gradient(v_d.grad, loss)
-        return g, l
-
-    # device-resident inputs for `value`
-    v_d, src_d, xs_d, xr_d, obs_d = (t.to(dev) for t in (v_host, src_h, x_s_h, x_r_h, obs_h))
-
-    def step_resident():
-        return gradient(v_d, src_d, xs_d, xr_d, obs_d)
-
-    def step_e2e():
-        tens = [t.to(dev, non_blocking=True) for t in (v_host, src_h, x_s_h, x_r_h, obs_h)]
-        g, l = gradient(*tens)
-        grad_h.copy_(g, non_blocking=True)
-        loss_h.copy_(l.reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return g, l
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps, sampler=None):
-        barrier()
-        if sampler:
-            sampler.start()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            out = fn()
-        e1.record()
-        barrier()
-        clocks = sampler.stop() if sampler else None
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item()), clocks, out
-
-    for _ in range(args.warmup):
-        g, l = step_resident()
-    torch.cuda.synchronize()
-    if not bool(torch.isfinite(g).all()) or not math.isfinite(float(l.detach())):
-        raise RuntimeError("non-finite gradient / misfit in the benchmark step")
-
-    _lib.LOOP_TIMES = []
-    n0 = pkg.kernel_launches()
-    ms, clocks, _ = timed(step_resident, args.steps, ClockSampler(local))
-    launches = pkg.kernel_launches() - n0
-    loops = _lib.LOOP_TIMES
-    _lib.LOOP_TIMES = None
-    t_fwd = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag.endswith("_fwd")]
-    t_adj = [a.elapsed_time(b) / n for tag, a, b, n in loops if tag.endswith("_adj")]
-    ms_fwd, ms_adj = sum(t_fwd) / len(t_fwd), sum(t_adj) / len(t_adj)      # ms per launch
-
-    cells = nz * ny
-    work = cells * nti * batch * (1 if w.get("slabs") else world) * 2   # cell-updates (inner steps) per step, whole job
-    value = work * args.steps / (ms * 1e-3) / 1e9
-
-    e2e = None
-    if not args.no_e2e:
-        step_e2e()
-        ms_e, _, _ = timed(step_e2e, args.steps)
-        h2d = sum(t.numel() * t.element_size() for t in (v_host, src_h, x_s_h, x_r_h, obs_h))
-        d2h = grad_h.numel() * 4 + 4
-        e2e = {"value": round(work * args.steps / (ms_e * 1e-3) / 1e9, 3), "unit": "Gcell-updates/s",
-               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "ms_per_step": round(ms_e / args.steps, 3)}
-
-    if rank == 0:
-        peak, peak_src = hbm_peak()
-        unit_launch = cells * batch // (world if w.get("slabs") else 1)   # cell-updates one launch performs
-        bf, ba = (B_FWD_EL, B_ADJ_EL) if w.get("elastic") else (B_FWD, B_ADJ)
-        ach_f = unit_launch * bf / (ms_fwd * 1e-3) / 1e9
-        ach_a = unit_launch * ba / (ms_adj * 1e-3) / 1e9
-        ach = unit_launch * (bf + ba) / ((ms_fwd + ms_adj) * 1e-3) / 1e9
-        kname = ("elastic step (f1 + f2 forward, b2a + b2b + b1a + b1b adjoint; one time step = one 'launch')"
-                 if w.get("elastic") else "acoustic_step_kernel (forward MODE 1 + adjoint MODE 2 pair)")
-        roof = {"bound": "hbm", "kernel": kname,
-                "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
-                "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_cell_update": {"forward": bf, "adjoint": ba},
-                "forward": {"ms_per_launch": round(ms_fwd, 5), "achieved": round(ach_f, 1), "frac": round(ach_f / peak, 4)},
-                "adjoint": {"ms_per_launch": round(ms_adj, 5), "achieved": round(ach_a, 1), "frac": round(ach_a / peak, 4)},
-                "kernel_share_of_step": round((ms_fwd + ms_adj) * nti * args.steps / ms, 4)}
-        prof = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(prof):
-            try:
-                roof["traffic"] = json.load(open(prof)).get(args.workload)
-            except Exception:
-                pass
-        line = {"metric": "FWI gradient Gcell-updates/s (fwd+adjoint)", "value": round(value, 3),
-                "unit": "Gcell-updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
-                "scaling": "strong" if w.get("slabs") else "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": bench_config(w, batch, world, args.workload), "roofline": roof,
-                "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}
-        if world == 1 and not args.no_cpu:
-            line["cpu_baseline"] = cpu_baseline_elastic(w) if w.get("elastic") else cpu_baseline(w)
-        print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    return run_gpu(args, w, dev, rank, world, local)
 
 
 if __name__ == "__main__":

@@ -53,6 +53,15 @@ int fwi_oracle_num_threads(void) {
 #endif
 }
 
+/* bench.py's CPU legs set the thread count explicitly: torchrun exports OMP_NUM_THREADS=1 */
+void fwi_oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 #define REAL float
 #define FMA fmaf
 #define NAME(x) x##_f32

@@ -41,6 +41,12 @@ def num_threads() -> int:
     return int(lib().fwi_oracle_num_threads())
 
 
+def set_threads(n: int) -> int:
+    """OpenMP threads of the C oracle (bench.py's CPU legs: torchrun exports OMP_NUM_THREADS=1)."""
+    lib().fwi_oracle_set_threads(ctypes.c_int(int(n)))
+    return num_threads()
+
+
 def _ptr(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
 
@@ -97,14 +103,26 @@ class AcousticSetup:
         return (c[..., 0] * self.nyp + c[..., 1]).to(torch.int32).contiguous().numpy()
 
 
+def _buffer(workspace, name, shape, dtype):
+    """Zero-initialised array; with a `workspace` dict the array is kept and handed out again (same shape), so a
+    timed repeat neither allocates nor first-touches gigabytes of snapshots (a CPU code would reuse them too).
+    Stale contents are harmless: every cell the adjoint reads is rewritten by the forward pass before it."""
+    if workspace is None:
+        return np.zeros(shape, dtype=dtype)
+    a = workspace.get(name)
+    if a is None or a.shape != tuple(shape) or a.dtype != dtype:
+        a = workspace[name] = np.zeros(shape, dtype=dtype)
+    return a
+
+
 def acoustic_forward(v, dx, source_amplitudes, x_s, x_r, dt, *, order=4, pml_width=10,
-                     vpmax=None, loc_mode="trunc", dtype=torch.float64, save=False):
+                     vpmax=None, loc_mode="trunc", dtype=torch.float64, save=False, workspace=None):
     su = AcousticSetup(v, dx, dt, order, pml_width, vpmax, dtype)
     nt, S, _ = source_amplitudes.shape
     amp = T.upsample(source_amplitudes.detach().to(dtype), su.ratio).contiguous().numpy()
     nti = nt * su.ratio
     sc, rc = su.cells(x_s, loc_mode), su.cells(x_r, loc_mode)
-    q = np.zeros((nti, S, su.nzp * su.nyp), dtype=su.npdtype) if save else None
+    q = _buffer(workspace, "q", (nti, S, su.nzp * su.nyp), su.npdtype) if save else None
     rec = run(su.npdtype, su.nzp, su.nyp, order, pml_width, S, su.dz, su.dy, su.dti, su.w,
               su.sigz, su.sigy, nti, 0, sc, amp, 0, rc, 0, q_write=q)
     rec = torch.from_numpy(rec[::su.ratio].copy())
@@ -114,11 +132,11 @@ def acoustic_forward(v, dx, source_amplitudes, x_s, x_r, dt, *, order=4, pml_wid
 
 
 def acoustic_gradient(v, dx, source_amplitudes, x_s, x_r, dt, grad_rec=None, observed=None, *,
-                      order=4, pml_width=10, vpmax=None, loc_mode="trunc", dtype=torch.float64):
+                      order=4, pml_width=10, vpmax=None, loc_mode="trunc", dtype=torch.float64, workspace=None):
     """Returns (rec, grad_v [nz, ny], grad_src [nt, S, Ns]) with the hand-written adjoint."""
     rec, (su, q, sc, rc, amp) = acoustic_forward(
         v, dx, source_amplitudes, x_s, x_r, dt, order=order, pml_width=pml_width, vpmax=vpmax,
-        loc_mode=loc_mode, dtype=dtype, save=True)
+        loc_mode=loc_mode, dtype=dtype, save=True, workspace=workspace)
     nt, S, Ns = source_amplitudes.shape
     nti = nt * su.ratio
     g = grad_rec.to(dtype) if grad_rec is not None else (rec - observed.to(dtype))

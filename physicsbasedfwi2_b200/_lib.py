@@ -156,7 +156,7 @@ def kernel_launches() -> int:
 
 # ---- optional time-loop timing (bench.py's roofline leg) ---------------------------------------
 # When LOOP_TIMES is a list, every native time loop is bracketed by CUDA events recorded on the
-# stream the kernels are launched on; entries are (tag, start_event, end_event, n_launches).
+# stream the kernels are launched on; entries are (tag, start_event, end_event, n_launches, n_shots).
 LOOP_TIMES = None
 
 
@@ -169,10 +169,10 @@ def time_loop_begin(stream):
     return ev
 
 
-def time_loop_end(stream, ev, tag, n_launches):
+def time_loop_end(stream, ev, tag, n_launches, n_shots=1):
     if ev is None:
         return
     import torch
     end = torch.cuda.Event(enable_timing=True)
     end.record(stream)
-    LOOP_TIMES.append((tag, ev, end, int(n_launches)))
+    LOOP_TIMES.append((tag, ev, end, int(n_launches), int(n_shots)))

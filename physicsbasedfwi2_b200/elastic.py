@@ -136,7 +136,7 @@ class _ElasticFunction(torch.autograd.Function):
         with torch.cuda.device(dev):
             ev = _lib.time_loop_begin(cur)
             _lib.check(L.fwi_elastic_forward(C.byref(desc), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_forward")
-            _lib.time_loop_end(cur, ev, "elastic_fwd", nti)
+            _lib.time_loop_end(cur, ev, "elastic_fwd", nti, S)
         out = rec[:, ::ratio].contiguous() if ratio > 1 else rec
         ctx.saved = (vp.detach(), vs.detach(), rho.detach(), params, prof_z, prof_y, s_cell, r_cell, s_link, r_link, snap, desc)
         ctx.meta = (nt, S, Ns, R, nti, ratio, P, dev)
@@ -168,7 +168,7 @@ class _ElasticFunction(torch.autograd.Function):
         with torch.cuda.device(dev):
             ev = _lib.time_loop_begin(cur)
             _lib.check(L.fwi_elastic_backward(C.byref(desc), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_backward")
-            _lib.time_loop_end(cur, ev, "elastic_adj", nti)
+            _lib.time_loop_end(cur, ev, "elastic_adj", nti, S)
         gvp = gvs = grho = gs = None
         if need_model:
             gpar = grad.sum(1)                       # fixed-order sum over shots

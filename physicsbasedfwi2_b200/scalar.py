@@ -156,7 +156,9 @@ class _Plan:
             else:
                 _lib.check(fn(C.byref(d), C.byref(b), C.c_void_p(cur.cuda_stream)),
                            "fwi_acoustic_backward" if adjoint else "fwi_acoustic_forward")
-            _lib.time_loop_end(cur, ev, "acoustic_adj" if adjoint else "acoustic_fwd", nsteps)
+            # tags: forward with snapshots (MODE 1), forward only (MODE 0: direct wave, checkpoint pass), adjoint
+            tag = "acoustic_adj" if adjoint else ("acoustic_fwd" if q_write is not None else "acoustic_fwd0")
+            _lib.time_loop_end(cur, ev, tag, nsteps, self.S)
         return smp_out
 
 

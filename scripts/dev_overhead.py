@@ -25,6 +25,6 @@ for (nz, ny, S, R, nt) in ((70, 70, 5, 70, 1000), (100, 300, 10, 101, 1000), (15
     for _ in range(5): grad()
     torch.cuda.synchronize()
     wall = (time.perf_counter() - t0) / 5
-    loops = sum(a.elapsed_time(b) for _, a, b, _ in _lib.LOOP_TIMES) / 5
+    loops = sum(a.elapsed_time(b) for _, a, b, _, _ in _lib.LOOP_TIMES) / 5
     _lib.LOOP_TIMES = None
     print(f"{nz}x{ny} S={S} nt={nt}: wall {wall*1e3:.2f} ms per gradient, native loops {loops:.2f} ms, rest {wall*1e3-loops:.2f} ms", flush=True)

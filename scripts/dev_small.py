@@ -21,5 +21,5 @@ for wl in ("c1", "c5"):
         rec = Propagator({"vp": vv}, w["dx"], **kw)(src, x_s.to(dev), x_r.to(dev), w["dt"])
         rec.square().sum().backward()
         torch.cuda.synchronize()
-        t = [(tag, a.elapsed_time(b) / n * 1e3) for tag, a, b, n in _lib.LOOP_TIMES]
+        t = [(tag, a.elapsed_time(b) / n * 1e3) for tag, a, b, n, _ in _lib.LOOP_TIMES]
     print(wl, "us/step: fwd no-snapshot %.2f, fwd snapshot %.2f, adjoint %.2f" % (t[0][1], t[1][1], t[2][1]), flush=True)

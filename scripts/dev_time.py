@@ -26,7 +26,7 @@ for r in range(reps):
     (0.5 * ((rec - obs) ** 2).sum()).backward()
     torch.cuda.synchronize()
     wall = time.time() - t0
-    out = {tag: a.elapsed_time(b) / n * 1e3 for tag, a, b, n in _lib.LOOP_TIMES}
+    out = {tag: a.elapsed_time(b) / n * 1e3 for tag, a, b, n, _ in _lib.LOOP_TIMES}
     cells = w["nz"] * w["ny"] * S
     print(f"rep {r} shots {S} nt {nt} wall {wall:.3f}s", {k: f"{x:.1f} us/launch" for k, x in out.items()},
           "GB/s fwd %.0f adj %.0f" % (cells * 20 / out["acoustic_fwd"] / 1e3, cells * 28 / out["acoustic_adj"] / 1e3),

@@ -23,7 +23,30 @@ KEEP = [
     "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__cycles_active.avg",
     "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
     "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "smsp__inst_executed.sum",
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_ld.sum",
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_st.sum",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram__cycles_active.avg.pct_of_peak_sustained_elapsed",
+    "smsp__warps_active.avg.per_cycle_active", "smsp__warps_eligible.avg.per_cycle_active",
+    "smsp__issue_active.avg.per_cycle_active", "sm__cycles_elapsed.max",
 ]
+
+
+def stall_table(f, d):
+    """Warp-state section of --set full: every metric whose name says 'stall' (the names differ between ncu
+    versions: smsp__average_warp_latency_issue_stalled_*, smsp__average_warps_issue_stalled_*_per_issue_active,
+    smsp__warp_issue_stalled_*_per_warp_active), largest first."""
+    rows = []
+    for h, (v, u) in d.items():
+        if "stall" not in h:
+            continue
+        try:
+            rows.append((float(v.replace(",", "")), h, u))
+        except ValueError:
+            pass
+    f.write(f"# warp stall reasons ({len(rows)} metrics with 'stall' in the name; zero rows omitted)\n")
+    for x, h, u in sorted(rows, reverse=True):
+        if x != 0:
+            f.write(f"{h:100s} {x:12.3f} {u}\n")
 
 
 def launches(tag):
@@ -65,14 +88,9 @@ def full(tag, name):
         for k in KEEP:
             if k in d:
                 f.write(f"{k:70s} {d[k][0]:>16s} {d[k][1]}\n")
-        f.write("# warp stall reasons (pct of warp-active cycles) > 3%\n")
-        for h, (v, u) in d.items():
-            if "issue_stalled" in h and h.endswith("_per_warp_active.pct"):
-                try:
-                    if float(v.replace(",", "")) > 3:
-                        f.write(f"{h:90s} {v:>10s}\n")
-                except ValueError:
-                    pass
+        stall_table(f, d)
+    # the whole raw page of this launch, for anything the summary leaves out
+    open(os.path.join(PROF, f"{tag}_{name}.raw.csv"), "w").write(raw)
 
     def num(k):
         v, u = d[k]
@@ -100,6 +118,7 @@ def full_multi(tag, name, note):
             for k in KEEP:
                 if k in d:
                     f.write(f"{k:70s} {d[k][0]:>16s} {d[k][1]}\n")
+            stall_table(f, d)
 
             def num(k):
                 v, u = d[k]

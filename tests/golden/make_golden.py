@@ -94,6 +94,34 @@ def main_elastic():
         print(name, "rec", tuple(rec.shape), float(rec.abs().max()), "grad_vp", float(gvp.abs().max()))
 
 
+def main_c1(shots=(2, 7), nt=600):
+    """C1-sized vector (100 x 300, dx 10 m, 15 Hz, order 4, pml 10, MSE against the data of the
+    unperturbed layered model): 2 of the 10 shots, 600 of the 1000 steps, fp64 torch autograd."""
+    from tests import _baseline as B
+    here = os.path.dirname(os.path.abspath(__file__))
+    c = B.c1(nt=nt)
+    idx = list(shots)
+    x_s, x_r, src = c["x_s"][idx], c["x_r"][idx], c["src"][:, idx].double()
+    with torch.no_grad():
+        obs = T.acoustic_forward(c["v_true"].double(), c["dx"], src, x_s, x_r, c["dt"], order=4, pml_width=10)
+        obs = obs.float().double()      # the data is stored (and handed to the kernels) in fp32
+    v = c["v"].double().requires_grad_(True)
+    s = src.clone().requires_grad_(True)
+    rec = T.acoustic_forward(v, c["dx"], s, x_s, x_r, c["dt"], order=4, pml_width=10)
+    # J = <grad_rec, rec> with grad_rec = d(MSE)/d(rec) of the fp64 traces, rounded to fp32 as it is stored: the
+    # gradient check then tests the adjoint, not the fp32 cancellation in (rec - obs)
+    grad_rec = (2.0 * (rec.detach() - obs) / rec.numel()).float().double()
+    (rec * grad_rec).sum().backward()
+    np.savez_compressed(
+        os.path.join(here, "c1_autograd_2shots.npz"), v=c["v"].numpy(), x_s=x_s.numpy(), x_r=x_r.numpy(),
+        src=src.float().numpy(), obs=obs.float().numpy(), grad_rec=grad_rec.float().numpy(),
+        mse=float(torch.nn.functional.mse_loss(rec.detach(), obs)),
+        dx=np.float64(c["dx"]), dt=c["dt"], order=4, pml=10,
+        rec=rec.detach().float().numpy(), grad_v=v.grad.numpy(), grad_src=s.grad.float().numpy())
+    print("c1_autograd_2shots rec", tuple(rec.shape), float(rec.abs().max()), "grad_v", float(v.grad.abs().max()))
+
+
 if __name__ == "__main__":
     main()
     main_elastic()
+    main_c1()

@@ -157,3 +157,22 @@ def test_location_outside_model_raises():
     bad[0, 0, 1] = 1e6
     with pytest.raises(RuntimeError):
         O.acoustic_forward(v, 10.0, src, x_s, bad, 1e-3)
+
+
+def test_c_oracle_matches_c1_size_autograd_golden():
+    """The hand-written adjoint of oracle/cpu_ref.c against fp64 torch autograd at BASELINE config 1's size
+    (tests/golden/c1_autograd_2shots.npz: 100 x 300, 2 of the 10 shots, 600 of the 1000 steps; J = <g, rec> with
+    g the MSE residual of the fp64 traces).  Traces and the source gradient are stored in fp32 (hence 3e-7), the
+    model gradient in fp64."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "c1_autograd_2shots.npz"))
+    t = {k: torch.from_numpy(z[k]) for k in ("v", "x_s", "x_r", "src", "obs", "grad_rec", "rec", "grad_v", "grad_src")}
+    kw = dict(order=int(z["order"]), pml_width=int(z["pml"]))
+    args = (t["v"], float(z["dx"]), t["src"], t["x_s"], t["x_r"], float(z["dt"]))
+    rec, gv, gs = O.acoustic_gradient(*args, grad_rec=t["grad_rec"], dtype=torch.float64, **kw)
+    assert K.rel_l2(rec, t["rec"]) < 3e-7
+    assert K.rel_l2(gv, t["grad_v"]) < 1e-9
+    assert K.rel_l2(gs, t["grad_src"]) < 3e-7
+    assert abs(float(torch.nn.functional.mse_loss(rec, t["obs"].double())) - float(z["mse"])) < 1e-9 * float(z["mse"])
+    # the fp32 build against the fp64 vector: fp32 round-off of 600 steps of the recurrence
+    rec32, gv32, gs32 = O.acoustic_gradient(*args, grad_rec=t["grad_rec"], dtype=torch.float32, **kw)
+    assert K.rel_l2(rec32, t["rec"]) < 5e-5 and K.rel_l2(gv32, t["grad_v"]) < 2e-4 and K.rel_l2(gs32, t["grad_src"]) < 2e-4
