@@ -298,36 +298,40 @@ def bench_config(w, batch, world, name):
 # C5: end-to-end physics-guided iteration (generator CNN + propagator gradient + optimiser step)
 # ------------------------------------------------------------------------------------------------
 def make_generator(n_shots, nz, ny, vmin, vmax):
-    """Encoder-decoder velocity generator with the interface of the reference's Auto22 net
-    (models/networks.py:5136-5294: shot gathers [1, shots, nt/4, receivers] -> 8-number latent ->
-    velocity image [1, 1, nz, ny] scaled into [vmin, vmax]).  Ordinary PyTorch, random weights:
-    the CNN is outside the propagator path and only has to have the right shapes and cost."""
+    """Velocity generator with the layer shapes of the reference's Auto22 net (models/networks.py:5136-5294;
+    blocks :2276-2314, :2482-2524): encoder on the gathers decimated 4x in time [1, shots, 1000, 200], four blocks of
+    2 x (3x3 conv, batch norm, LeakyReLU 0.1) + 2x2 average pooling (ceil) with 16/32/64/128 channels ->
+    [1, 128, 63, 13] -> Linear -> 8-number latent -> Linear -> [1, 128, 19, 25] -> three blocks of bilinear 2x
+    upsampling + 2 x (conv, norm, LeakyReLU) with 64/32/16 channels -> crop to [nz, ny] -> 1x1 conv -> sigmoid ->
+    vmin + f (vmax - vmin).  Written here from those shapes, random weights: bench.py may not read /root/reference
+    on the GPU box, and the CNN is outside the propagator path - it has to have the reference's cost, not its code."""
     import torch.nn as nn
 
+    def conv2(i, o):
+        return [nn.Conv2d(i, o, 3, 1, 1), nn.BatchNorm2d(o), nn.LeakyReLU(0.1),
+                nn.Conv2d(o, o, 3, 1, 1), nn.BatchNorm2d(o), nn.LeakyReLU(0.1)]
+
     def down(i, o):
-        return nn.Sequential(nn.Conv2d(i, o, 3, padding=1), nn.BatchNorm2d(o), nn.ReLU(inplace=True),
-                             nn.Conv2d(o, o, 3, padding=1), nn.BatchNorm2d(o), nn.ReLU(inplace=True), nn.MaxPool2d(2, ceil_mode=True))
+        return nn.Sequential(*conv2(i, o), nn.AvgPool2d(2, 2, ceil_mode=True))
 
     def up(i, o):
-        return nn.Sequential(nn.Upsample(scale_factor=2, mode="bilinear", align_corners=False),
-                             nn.Conv2d(i, o, 3, padding=1), nn.BatchNorm2d(o), nn.ReLU(inplace=True),
-                             nn.Conv2d(o, o, 3, padding=1), nn.BatchNorm2d(o), nn.ReLU(inplace=True))
+        return nn.Sequential(nn.UpsamplingBilinear2d(scale_factor=2), *conv2(i, o))
 
     class Generator(nn.Module):
         def __init__(self):
             super().__init__()
             f = [16, 32, 64, 128]
             self.enc = nn.Sequential(down(n_shots, f[0]), down(f[0], f[1]), down(f[1], f[2]), down(f[2], f[3]))
-            self.h0, self.w0 = (nz + 7) // 8, (ny + 7) // 8
+            self.h0, self.w0 = (nz + 1 + 7) // 8, (ny + 7) // 8          # 19 x 25 for 151 x 200
             self.to_latent = nn.LazyLinear(8)
             self.from_latent = nn.Linear(8, f[3] * self.h0 * self.w0)
             self.dec = nn.Sequential(up(f[3], f[2]), up(f[2], f[1]), up(f[1], f[0]))
             self.head = nn.Conv2d(f[0], 1, 1)
 
         def forward(self, gathers):
-            z = self.to_latent(torch.flatten(self.enc(gathers[:, :, 1::4, :]), 1))
+            z = self.to_latent(torch.flatten(self.enc(gathers[:, :, 1:4001:4, :]), 1))
             x = self.from_latent(z).view(-1, 128, self.h0, self.w0)
-            x = self.head(self.dec(x)[:, :, :nz, :ny])
+            x = self.head(self.dec(x)[:, :, 1:1 + nz, :ny].contiguous())
             return vmin + torch.sigmoid(x) * (vmax - vmin)
 
     return Generator()

@@ -131,19 +131,17 @@ def acoustic_forward(v, dx, source_amplitudes, x_s, x_r, dt, *, order=4, pml_wid
     return rec
 
 
-def acoustic_gradient(v, dx, source_amplitudes, x_s, x_r, dt, grad_rec=None, observed=None, *,
-                      order=4, pml_width=10, vpmax=None, loc_mode="trunc", dtype=torch.float64, workspace=None):
-    """Returns (rec, grad_v [nz, ny], grad_src [nt, S, Ns]) with the hand-written adjoint."""
-    rec, (su, q, sc, rc, amp) = acoustic_forward(
-        v, dx, source_amplitudes, x_s, x_r, dt, order=order, pml_width=pml_width, vpmax=vpmax,
-        loc_mode=loc_mode, dtype=dtype, save=True, workspace=workspace)
+def acoustic_adjoint(state, grad_rec, source_amplitudes, dtype=torch.float64):
+    """Hand-written adjoint of acoustic_forward(save=True): `state` is what that call returned next to the traces.
+    Returns (grad_v [nz, ny], grad_src [nt, S, Ns]) for J = <grad_rec, rec>."""
+    su, q, sc, rc, amp = state
     nt, S, Ns = source_amplitudes.shape
     nti = nt * su.ratio
-    g = grad_rec.to(dtype) if grad_rec is not None else (rec - observed.to(dtype))
+    g = grad_rec.to(dtype)
     g_in = np.zeros((nti, S, g.shape[2]), dtype=su.npdtype)
     g_in[::su.ratio] = g.numpy()
     G = np.zeros((S, su.nzp * su.nyp), dtype=su.npdtype)
-    gs = run(su.npdtype, su.nzp, su.nyp, order, pml_width, S, su.dz, su.dy, su.dti, su.w,
+    gs = run(su.npdtype, su.nzp, su.nyp, su.order, su.pw, S, su.dz, su.dy, su.dti, su.w,
              su.sigz, su.sigy, nti, 1, rc, g_in, 1, sc, 1, q_read=q, G=G)
     # dJ/dv_pad = (2 / v_pad) * (G + scatter_src(sum_n gs_n * s_n)), then fold the replicate pad
     Gt = torch.from_numpy(G).sum(0)
@@ -153,9 +151,21 @@ def acoustic_gradient(v, dx, source_amplitudes, x_s, x_r, dt, grad_rec=None, obs
     gpad = (2.0 / su.v_pad) * Gt.reshape(su.nzp, su.nyp)
     grad_v = fold_replicate_pad(gpad, su.P)
     # adjoint of the FFT upsampling: apply autograd to the linear map
-    s = source_amplitudes.detach().to(dtype).clone().requires_grad_(True)
-    (T.upsample(s, su.ratio) * gs_t).sum().backward()
-    return rec, grad_v, s.grad
+    with torch.enable_grad():            # (callable from inside an autograd Function's backward)
+        s = source_amplitudes.detach().to(dtype).clone().requires_grad_(True)
+        (gs_s,) = torch.autograd.grad((T.upsample(s, su.ratio) * gs_t).sum(), s)
+    return grad_v, gs_s
+
+
+def acoustic_gradient(v, dx, source_amplitudes, x_s, x_r, dt, grad_rec=None, observed=None, *,
+                      order=4, pml_width=10, vpmax=None, loc_mode="trunc", dtype=torch.float64, workspace=None):
+    """Returns (rec, grad_v [nz, ny], grad_src [nt, S, Ns]) with the hand-written adjoint."""
+    rec, state = acoustic_forward(
+        v, dx, source_amplitudes, x_s, x_r, dt, order=order, pml_width=pml_width, vpmax=vpmax,
+        loc_mode=loc_mode, dtype=dtype, save=True, workspace=workspace)
+    g = grad_rec.to(dtype) if grad_rec is not None else (rec - observed.to(dtype))
+    grad_v, grad_s = acoustic_adjoint(state, g, source_amplitudes, dtype)
+    return rec, grad_v, grad_s
 
 
 def fold_replicate_pad(gpad: torch.Tensor, P: int) -> torch.Tensor:

@@ -1,0 +1,118 @@
+"""The drop-in claim on the B200: `import deepwave` answered by shim/deepwave (the CUDA product), driven through the
+call sequence of the reference's own `prop` methods, against fixtures the reference's UNMODIFIED code produced.
+
+tests/golden/prop_auto22.npz / prop_auto.npz were written by tests/golden/make_prop_golden.py, which imports
+/root/reference/models/networks.py as it is and runs `AutoMarmousi22_Net.prop` (:5314-5510) / `Auto_Net.prop`
+(:2711-2850) on the seeded inputs of tests/_prop_cases.py (the reference cannot travel to the GPU box, so its
+outputs do, as fixtures).  Here tests/_prop_cases.replay_* - the same statements, line by line - runs on cuda:0 with
+shim/deepwave and must return what the reference returned: the z^2-weighted, water-masked gradient, the L1 loss of
+the direct-wave-subtracted, max-normalised traces, and the traces themselves.
+
+Also here: the optimiser side of the drop-in.  The reference drives the gradient with Adam and with
+FullBatchLBFGS (functions/LBFGS.py, tested unmodified on the CPU in tests/test_reference_prop_cpu.py); on the GPU
+box torch.optim.LBFGS with a strong-Wolfe line search makes the same demands on the autograd.Function: many
+closure evaluations per step, forwards whose graphs are dropped without a backward, interleaved graphs.
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from tests import _cases as K
+from tests import _prop_cases as PC
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module")
+def deepwave(cuda_lib):
+    sys.path.insert(0, os.path.join(ROOT, "shim"))
+    try:
+        import deepwave as dw
+    finally:
+        sys.path.remove(os.path.join(ROOT, "shim"))
+    import physicsbasedfwi2_b200 as pkg
+    assert dw.scalar.Propagator is pkg.scalar.Propagator          # the shim IS the product, not a stand-in
+    return dw
+
+
+def test_auto22_prop_sequence_reproduces_the_reference_fixture(deepwave):
+    z = np.load(os.path.join(GOLD, "prop_auto22.npz"))
+    grad, loss, pred = PC.replay_auto22(deepwave, PC.auto22_inputs(), DEV)
+    assert tuple(pred.shape) == (4001, 9, 200) and pred.is_cuda
+    et = K.rel_l2(pred[::64, :, ::4], torch.from_numpy(z["pred_sub"]))
+    eg = K.rel_l2(grad, torch.from_numpy(z["grad"]))
+    assert et <= 1e-5, f"traces rel-L2 {et:.3e}"
+    assert eg <= 1e-4, f"masked gradient rel-L2 {eg:.3e}"
+    assert abs(loss - float(z["loss"])) <= 1e-5 * float(z["loss"]), (loss, float(z["loss"]))
+    assert float(grad[PC.auto22_inputs()["true"][0, 0].to(DEV) == 1500].abs().max()) == 0.0
+
+
+def test_auto_net_prop_sequence_reproduces_the_reference_fixture(deepwave):
+    z = np.load(os.path.join(GOLD, "prop_auto.npz"))
+    grad, _, pred = PC.replay_auto(deepwave, PC.auto_inputs(), DEV)
+    et = K.rel_l2(pred[::16], torch.from_numpy(z["pred_sub"]))
+    eg = K.rel_l2(grad, torch.from_numpy(z["grad"]))
+    assert et <= 1e-5, f"traces rel-L2 {et:.3e}"
+    assert eg <= 1e-4, f"gradient rel-L2 {eg:.3e}"
+
+
+def _small_problem():
+    nz, ny, dx, nt, dt = 40, 64, 10.0, 200, 1e-3
+    v_true = K.layered_model(nz, ny, seed=3, noise=0.0).to(DEV)
+    x_s, x_r = K.survey(nz, ny, dx, 3, 16, 1, seed=1)
+    src = K.ricker(20.0, nt, dt, 0.05).reshape(-1, 1, 1).repeat(1, 3, 1).contiguous().to(DEV)
+    return v_true, x_s.to(DEV), x_r.to(DEV), src, dx, dt
+
+
+def test_lbfgs_line_search_closure_reentrancy(deepwave):
+    """Closure shaped like models/AutoElMar22LBFGS_model.py:477-498 (forward + backward inside the closure)."""
+    import physicsbasedfwi2_b200 as pkg
+    v_true, x_s, x_r, src, dx, dt = _small_problem()
+    with torch.no_grad():
+        obs = deepwave.scalar.Propagator({"vp": v_true}, dx)(src, x_s, x_r, dt)
+    v = torch.nn.Parameter(torch.full_like(v_true, 2300.0))
+    opt = torch.optim.LBFGS([v], lr=1.0, history_size=10, max_iter=4, line_search_fn="strong_wolfe")
+    calls, losses = [0], []
+
+    def closure():
+        opt.zero_grad()
+        calls[0] += 1
+        loss = 1e6 * torch.nn.functional.mse_loss(deepwave.scalar.Propagator({"vp": v}, dx)(src, x_s, x_r, dt), obs)
+        loss.backward()
+        losses.append(float(loss))
+        return loss
+
+    n0 = pkg.kernel_launches()
+    for _ in range(3):
+        opt.step(closure)
+    assert calls[0] >= 6, calls                                     # several fwd+adjoint pairs per step
+    assert pkg.kernel_launches() - n0 >= 2 * calls[0]               # every one of them ran the CUDA time loops
+    assert min(losses) < 0.5 * losses[0], losses
+    assert bool(torch.isfinite(v).all())
+
+
+def test_interleaved_graphs_and_dropped_forwards(deepwave):
+    """Two graphs alive at once, backward in the opposite order, a forward whose graph is never used."""
+    v_true, x_s, x_r, src, dx, dt = _small_problem()
+    va = (v_true * 0.95).requires_grad_(True)
+    vb = (v_true * 1.05).requires_grad_(True)
+    g = torch.randn(src.shape[0], 3, 16, device=DEV, generator=torch.Generator(DEV).manual_seed(1))
+
+    def single(v):
+        v = v.detach().clone().requires_grad_(True)
+        (deepwave.scalar.Propagator({"vp": v}, dx)(src, x_s, x_r, dt) * g).sum().backward()
+        return v.grad
+
+    ga, gb = single(va), single(vb)
+    ra = deepwave.scalar.Propagator({"vp": va}, dx)(src, x_s, x_r, dt)
+    rb = deepwave.scalar.Propagator({"vp": vb}, dx)(src, x_s, x_r, dt)
+    _ = deepwave.scalar.Propagator({"vp": va}, dx)(src, x_s, x_r, dt)          # dropped without a backward
+    (rb * g).sum().backward()
+    (ra * g).sum().backward()
+    assert torch.equal(va.grad, ga) and torch.equal(vb.grad, gb)
