@@ -792,6 +792,7 @@ def main():
     ap.add_argument("--halo-steps", type=int, default=0, help="slab workloads: steps between ghost exchanges (tuning only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg")
+    ap.add_argument("--pml", type=int, default=-1, help="override the PML width (tuning only: 0 = PML-free grid)")
     ap.add_argument("--survey", action="store_true", help="one step = the WHOLE survey sharded over the ranks (strong scaling)")
     ap.add_argument("--one-batch", action="store_true", help="c2: one launch of shots per step instead of the 32-shot slice")
     ap.add_argument("--no-check", action="store_true", help="skip the multi-GPU correctness check ahead of the timed region")
@@ -803,6 +804,8 @@ def main():
     w["name"] = args.workload
     if args.nt:
         w["nt"] = args.nt
+    if args.pml >= 0:
+        w["pml"] = args.pml
 
     if args.impl == "reference":
         run_reference(args, w)

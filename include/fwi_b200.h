@@ -155,6 +155,39 @@ int fwi_acoustic_run_slab(const fwi_acoustic_desc *desc, const fwi_acoustic_buff
 int fwi_acoustic_forward(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);
 int fwi_acoustic_backward(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);
 
+/* ---- host-side preparation as device kernels ------------------------------------------------ */
+/* What deepwave's Python layer does around its native time loop for the call at models/networks.py:5449,5464 and
+ * its backward (:5491): pad the model (replicate), scale it to w = v^2 dt^2, build the PML profiles; turn metre
+ * coordinates into cells and the sorted injection lists of fwi_acoustic_buffers; fold the image of the adjoint pass
+ * back through the padding into dJ/dv.  Three launches instead of ~125 eager torch micro-kernels per gradient. */
+typedef struct fwi_model_desc {
+    int32_t nz, ny;           /* model extents (z slow, y fast) */
+    int32_t order;            /* spatial accuracy: 2, 4, 6 or 8 */
+    int32_t pml_width;
+    int32_t c0, c1;           /* window [c0, c1) of padded columns this rank works on (x-slabs); c1 <= 0: the whole grid */
+    double dz, dy, dt;        /* grid spacings and INNER time step */
+    double vmax;              /* velocity the inner step and the PML profiles are built for */
+} fwi_model_desc;
+
+/* v [nz][ny] -> w [nzp][pitch] (layout of fwi_acoustic_get_layout for the padded window), sigz [nzp], sigy [pitch]. */
+int fwi_acoustic_prepare_model(const fwi_model_desc *m, const float *v, float *w, float *sigz, float *sigy, void *stream);
+
+/* x [n_shots][n][2] metres (z, y) -> cell [n_shots][n] (device cell z * pitch + col, clamped into the model) and the
+ * lists fwi_acoustic_run takes: row_start [n_shots][nzp + 1], sorted_cell / sorted_col [n_shots * n] (stable sort by
+ * (shot, cell)).  loc_round 0: cell = floor(x / d + 1e-6); 1: round half to even.  *bad (device int32, caller zeroes it)
+ * is set to 1 when a point lies outside the model (the launch stays safe: points are clamped). */
+int fwi_acoustic_plan_points(const fwi_model_desc *m, const float *x, int32_t n_shots, int32_t n, int32_t loc_round,
+                             int32_t *cell, int32_t *row_start, int32_t *sorted_cell, int32_t *sorted_col, int32_t *bad,
+                             void *stream);
+
+/* dJ/dv [nz][ny] = fold( (2 / v_pad) * (sum_s image[s] + source-cell term) ): image [n_shots][nzp][pitch] from
+ * fwi_acoustic_backward, gs [nsteps][n_shots][n_src] its sampled field (smp_out), amp the forward injection amplitudes,
+ * src_cell [n_shots][n_src] device cells; gs may be NULL (no source term).  workspace: fwi_acoustic_fold_workspace_floats. */
+int64_t fwi_acoustic_fold_workspace_floats(const fwi_model_desc *m, int32_t n_shots, int32_t n_src);
+int fwi_acoustic_fold_gradient(const fwi_model_desc *m, int32_t n_shots, const float *image, const float *gs,
+                               const float *amp, const int32_t *src_cell, int32_t n_src, int32_t nsteps, const float *v,
+                               float *workspace, float *grad_v, void *stream);
+
 /* ---- elastic (2-D P-SV, velocity-stress staggered grid, C-PML) -------------------------- */
 /* Replaces what the reference reaches through pyapi_denise: Denise.grad(model, src, rec)
  * (models/networks.py:9173) = elastic forward + adjoint + correlation, gradients read back at

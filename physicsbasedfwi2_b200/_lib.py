@@ -12,8 +12,8 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_HERE, "csrc")
-SO_PATH = os.path.join(_HERE, "libfwi_b200.so")
-_SOURCES = ["common.cu", "acoustic.cu", "acoustic_small.cu", "elastic.cu", "misfit.cu"]
+SO_PATH = os.environ.get("FWI_B200_LIB") or os.path.join(_HERE, "libfwi_b200.so")   # (env: tuning variants, scripts/dev_variants.sh)
+_SOURCES = ["common.cu", "acoustic.cu", "acoustic_small.cu", "elastic.cu", "misfit.cu", "host_kernels.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
 
@@ -38,6 +38,12 @@ class AcousticBuffers(C.Structure):
                 ("inj_col", C.c_void_p), ("inj_amp", C.c_void_p), ("smp_cell", C.c_void_p),
                 ("smp_out", C.c_void_p), ("q_write", C.c_void_p), ("q_read", C.c_void_p),
                 ("image", C.c_void_p), ("unit_table", C.c_void_p)]
+
+
+class ModelDesc(C.Structure):
+    _fields_ = [("nz", C.c_int32), ("ny", C.c_int32), ("order", C.c_int32), ("pml_width", C.c_int32),
+                ("c0", C.c_int32), ("c1", C.c_int32), ("dz", C.c_double), ("dy", C.c_double), ("dt", C.c_double),
+                ("vmax", C.c_double)]
 
 
 class SlabLink(C.Structure):
@@ -129,6 +135,15 @@ def lib() -> C.CDLL:
     L.fwi_slab_status.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]
     L.fwi_slab_exchanges.argtypes = [C.c_int32, C.c_int32]
     L.fwi_slab_exchanges.restype = C.c_int32
+    L.fwi_acoustic_prepare_model.argtypes = [C.POINTER(ModelDesc)] + [C.c_void_p] * 5
+    L.fwi_acoustic_prepare_model.restype = C.c_int
+    L.fwi_acoustic_plan_points.argtypes = [C.POINTER(ModelDesc), C.c_void_p, C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 6
+    L.fwi_acoustic_plan_points.restype = C.c_int
+    L.fwi_acoustic_fold_workspace_floats.argtypes = [C.POINTER(ModelDesc), C.c_int32, C.c_int32]
+    L.fwi_acoustic_fold_workspace_floats.restype = C.c_int64
+    L.fwi_acoustic_fold_gradient.argtypes = ([C.POINTER(ModelDesc), C.c_int32] + [C.c_void_p] * 4 + [C.c_int32, C.c_int32]
+                                             + [C.c_void_p] * 4)
+    L.fwi_acoustic_fold_gradient.restype = C.c_int
     L.fwi_trace_misfit_workspace_bytes.argtypes = [C.POINTER(MisfitDesc)]
     L.fwi_trace_misfit_workspace_bytes.restype = C.c_int64
     L.fwi_trace_misfit.argtypes = [C.POINTER(MisfitDesc)] + [C.c_void_p] * 6

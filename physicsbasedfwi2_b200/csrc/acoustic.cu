@@ -38,10 +38,29 @@
 namespace {
 
 // warps per CTA and resident CTAs per SM (warps are independent; this is scheduling granularity):
-// forward 2 x 6 warps with a 3-deep ring, adjoint (more operands per row) 3 x 3 warps, 2-deep
-__host__ __device__ constexpr int warps_per_cta(int MODE) { return MODE == 2 ? 3 : 6; }
-__host__ __device__ constexpr int ctas_per_sm(int MODE) { return MODE == 2 ? 3 : 2; }
+// forward / advance-only 2 x 6 warps with a 3-deep ring, imaging launches (more operands per row) 2 x 4 warps, 2-deep
+// (the FWI_CFG_* macros exist so that scripts/dev_variants.sh can build tuning variants; the defaults are the product)
+#ifndef FWI_CFG_W1
+#define FWI_CFG_W1 6
+#define FWI_CFG_C1 2
+#define FWI_CFG_D1 3
+#endif
+#ifndef FWI_CFG_W2
+#define FWI_CFG_W2 4      // 2 x 4 warps: a multiple of the 4 schedulers (3 x 3 measured 3.5 % slower: uneven warps per scheduler)
+#define FWI_CFG_C2 2
+#define FWI_CFG_D2 2
+#endif
+#ifndef FWI_CFG_W3
+#define FWI_CFG_W3 4
+#define FWI_CFG_C3 2
+#define FWI_CFG_D3 2
+#endif
+// MODE 0: advance only; 1: advance + write the snapshot q; 2: read q_n, image, advance; 3: read q_n and q_{n+1},
+// image both steps (the pairing of run_impl), advance
+__host__ __device__ constexpr int warps_per_cta(int MODE) { return MODE == 3 ? FWI_CFG_W3 : (MODE == 2 ? FWI_CFG_W2 : FWI_CFG_W1); }
+__host__ __device__ constexpr int ctas_per_sm(int MODE) { return MODE == 3 ? FWI_CFG_C3 : (MODE == 2 ? FWI_CFG_C2 : FWI_CFG_C1); }
 constexpr int kSegInt = 0, kSegBand = 1, kSegSide = 2;
+constexpr int kMaxUnits = 16384;   // bound on resident warps of any device this could run on
 
 // one run of rows [zb, ze) of a column strip starting at device column x0 of shot s; only columns
 // in [cmin, cmax) are stored
@@ -64,7 +83,7 @@ struct StepParams {
     // wavefield of this step inside the wave workspace / of this step's snapshot
     CUtensorMap tm_wave_u, tm_wave_o, tm_w, tm_q, tm_g;
     CUtensorMap ts_wave_u, ts_wave_o, ts_w, ts_q, ts_g;   // the same tensors with the narrow boxes of side strips
-    int row_u, row_um, row_pz, row_py, row_q;
+    int row_u, row_um, row_pz, row_py, row_q, row_q2;   // row_q2: snapshot of the step imaged together with this one (MODE 3)
     const float *u;
     float *um;
     const float *pz, *py;
@@ -139,14 +158,17 @@ constexpr int kRB = 4;        // rows per TMA box / ring block (>= H)
 constexpr int kRowU = 136;    // a ring row of u / py: 4-column halo | 128 own columns | 4-column halo
 constexpr int kRowO = 128;    // a ring row of everything else
 constexpr int kBlkU = kRB * kRowU, kBlkO = kRB * kRowO;   // floats per ring block
-__host__ __device__ constexpr int do_int(int MODE) { return MODE == 2 ? 2 : 3; }   // ring depth (blocks in flight) of interior segments
-constexpr int kDOBand = 1;    // ring depth of top/bottom band segments
+__host__ __device__ constexpr int do_int(int MODE) { return MODE == 3 ? FWI_CFG_D3 : (MODE == 2 ? FWI_CFG_D2 : FWI_CFG_D1); }   // ring depth (blocks in flight) of interior segments
+#ifndef FWI_CFG_DBAND
+#define FWI_CFG_DBAND 1
+#endif
+constexpr int kDOBand = FWI_CFG_DBAND;    // ring depth of top/bottom band segments
 constexpr int kBarFloats = 32;  // 8 mbarriers at the head of the warp's region (keeps blocks 128-byte aligned)
 
 // operand blocks fetched per iteration by side strips: u-, w (+ snapshot, image in the adjoint)
-__host__ __device__ constexpr int n_ops(int MODE) { return MODE == 2 ? 4 : 2; }
+__host__ __device__ constexpr int n_ops(int MODE) { return MODE == 3 ? 5 : (MODE == 2 ? 4 : 2); }
 // ... and by 128-column strips, which read w (shared by all shots, L2 resident) with plain loads
-__host__ __device__ constexpr int n_ops_ring(int MODE) { return MODE == 2 ? 3 : 1; }
+__host__ __device__ constexpr int n_ops_ring(int MODE) { return MODE == 3 ? 4 : (MODE == 2 ? 3 : 1); }
 __host__ __device__ constexpr int ring_floats(int MODE, bool PML, int DO) {
     return (DO + 1) * kBlkU + DO * n_ops_ring(MODE) * kBlkO + (PML ? (DO + 2) * kBlkO + DO * kBlkU : 0);
 }
@@ -227,10 +249,11 @@ __device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, f
         tma_g2s(U + su * kBlkU, &p.tm_wave_u, x0 - 4, p.row_u + srow + z0 + H, bar);
         float *o = OPS + so * NOPS * kBlkO;
         tma_g2s(o, &p.tm_wave_o, x0, p.row_um + srow + z0, bar);
-        if (MODE == 2) {
+        if (MODE >= 2) {
             tma_g2s(o + kBlkO, &p.tm_q, x0, p.row_q + srow + z0, bar);
             tma_g2s(o + 2 * kBlkO, &p.tm_g, x0, srow + z0, bar);
         }
+        if (MODE == 3) tma_g2s(o + 3 * kBlkO, &p.tm_q, x0, p.row_q2 + srow + z0, bar);
         if (PML) {
             tma_g2s(PZ + sp * kBlkO, &p.tm_wave_o, x0, p.row_pz + srow + z0 + H, bar);
             tma_g2s(PY + so * kBlkU, &p.tm_wave_u, x0 - 4, p.row_py + srow + z0, bar);
@@ -258,6 +281,10 @@ __device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, f
     F4 sy;
 #pragma unroll
     for (int j = 0; j < 4; ++j) sy.a[j] = PML ? __ldg(p.sigy + colL + j) : 0.f;
+    // sigma_y == 0 on all 128 columns of the strip (a top / bottom band strip away from the corners): the coefficient
+    // fields are then the same for every cell of a row and are evaluated once per row - the general expressions with
+    // sigma_y = 0, so the same bits
+    const bool sy_zero = PML && __all_sync(0xffffffffu, sy.a[0] == 0.f && sy.a[1] == 0.f && sy.a[2] == 0.f && sy.a[3] == 0.f);
     mbar_wait(barP, (phase >> DO) & 1u);
     phase ^= 1u << DO;
 #pragma unroll
@@ -349,36 +376,61 @@ __device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, f
                         for (int q = 0; q < 4; ++q) { pyv[q] = t0.a[q]; pyv[4 + q] = t1.a[q]; pyv[8 + q] = t2.a[q]; }
                     }
                     F4 pzn, pyn;
+                    float duz[4], dpy[4], duy[4];
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const float uc0 = v[4 + q];
-                        float duz = 0.f, dpy = 0.f, duy = 0.f;
+                        duz[q] = 0.f; dpy[q] = 0.f; duy[q] = 0.f;
 #pragma unroll
                         for (int k = 1; k <= H; ++k) {
-                            duz = fmaf(p.cz1[k], W[r + H + k].a[q] - W[r + H - k].a[q], duz);
-                            dpy = fmaf(p.cy1[k], pyv[4 + q + k] - pyv[4 + q - k], dpy);
-                            duy = fmaf(p.cy1[k], v[4 + q + k] - v[4 + q - k], duy);
+                            duz[q] = fmaf(p.cz1[k], W[r + H + k].a[q] - W[r + H - k].a[q], duz[q]);
+                            dpy[q] = fmaf(p.cy1[k], pyv[4 + q + k] - pyv[4 + q - k], dpy[q]);
+                            duy[q] = fmaf(p.cy1[k], v[4 + q + k] - v[4 + q - k], duy[q]);
                         }
-                        const float qq = (lap.a[q] + dpz.a[q]) + dpy;
-                        const float hs = p.hdt * (sz + sy.a[q]);
-                        const float a = 1.0f / (1.0f + hs);
-                        const float cu = a * fmaf(-p.dt2, sz * sy.a[q], 2.0f);
-                        const float cum = a * (hs - 1.0f);
-                        const float aw = a * cW.a[q];
-                        qv.a[q] = qq;
-                        un.a[q] = fmaf(aw, qq, fmaf(cu, uc0, cum * cM.a[q]));
-                        pzn.a[q] = fmaf(p.dt * (sy.a[q] - sz), duz, fmaf(-p.dt, sz, 1.0f) * pzc.a[q]);
-                        pyn.a[q] = fmaf(p.dt * (sz - sy.a[q]), duy, fmaf(-p.dt, sy.a[q], 1.0f) * pyv[4 + q]);
+                        qv.a[q] = (lap.a[q] + dpz.a[q]) + dpy[q];
+                    }
+                    if (sy_zero) {       // warp-uniform: straight-line code on both sides, the four cells interleave
+                        const float hs = p.hdt * sz;
+                        const float a0 = 1.0f / (1.0f + hs);
+                        const float cu0 = a0 * 2.0f;
+                        const float cum0 = a0 * (hs - 1.0f);
+                        const float cpz1 = p.dt * (0.0f - sz);
+                        const float cpz2 = fmaf(-p.dt, sz, 1.0f);
+                        const float cpy1 = p.dt * sz;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            un.a[q] = fmaf(a0 * cW.a[q], qv.a[q], fmaf(cu0, v[4 + q], cum0 * cM.a[q]));
+                            pzn.a[q] = fmaf(cpz1, duz[q], cpz2 * pzc.a[q]);
+                            pyn.a[q] = fmaf(cpy1, duy[q], pyv[4 + q]);
+                        }
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const float hs = p.hdt * (sz + sy.a[q]);
+                            const float a = 1.0f / (1.0f + hs);
+                            const float cu = a * fmaf(-p.dt2, sz * sy.a[q], 2.0f);
+                            const float cum = a * (hs - 1.0f);
+                            const float aw = a * cW.a[q];
+                            un.a[q] = fmaf(aw, qv.a[q], fmaf(cu, v[4 + q], cum * cM.a[q]));
+                            pzn.a[q] = fmaf(p.dt * (sy.a[q] - sz), duz[q], fmaf(-p.dt, sz, 1.0f) * pzc.a[q]);
+                            pyn.a[q] = fmaf(p.dt * (sz - sy.a[q]), duy[q], fmaf(-p.dt, sy.a[q], 1.0f) * pyv[4 + q]);
+                        }
                     }
                     st_masked<false>(p.pzn + sb + off, col, pzn, sg.cmin, sg.cmax, true);
                     st_masked<false>(p.pyn + sb + off, col, pyn, sg.cmin, sg.cmax, true);
                 }
                 st_masked<false>(um + off, col, un, sg.cmin, sg.cmax, true);
                 if (MODE == 1) st_masked<true>(p.qw + sb + off, col, qv, sg.cmin, sg.cmax, true);
-                if (MODE == 2) {
-                    // image of this shot: G += field * q_read (single owner per cell: deterministic)
+                if (MODE >= 2) {
+                    // image of this shot: G += field * q_read (single owner per cell: deterministic).  MODE 3 first
+                    // adds the product the previous step left out: its field is this step's u- (cM), in the same
+                    // order of additions as one imaging per step
                     const F4 cQ = lds4(o + kBlkO);
                     F4 g = lds4(o + 2 * kBlkO);
+                    if (MODE == 3) {
+                        const F4 cQ2 = lds4(o + 3 * kBlkO);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) g.a[q] = fmaf(cM.a[q], cQ2.a[q], g.a[q]);
+                    }
 #pragma unroll
                     for (int q = 0; q < 4; ++q) g.a[q] = fmaf(v[4 + q], cQ.a[q], g.a[q]);
                     st_masked<false>(p.G + sb + off, col, g, sg.cmin, sg.cmax, true);
@@ -437,10 +489,11 @@ __device__ __forceinline__ void march_side(const StepParams &p, const Seg &sg, f
         float *o = OPS + so * NOPS * kSideBlkO;
         tma_g2s(o, &p.ts_wave_o, x0, p.row_um + srow + z0, bar);
         tma_g2s(o + kSideBlkO, &p.ts_w, x0, z0, bar);
-        if (MODE == 2) {
+        if (MODE >= 2) {
             tma_g2s(o + 2 * kSideBlkO, &p.ts_q, x0, p.row_q + srow + z0, bar);
             tma_g2s(o + 3 * kSideBlkO, &p.ts_g, x0, srow + z0, bar);
         }
+        if (MODE == 3) tma_g2s(o + 4 * kSideBlkO, &p.ts_q, x0, p.row_q2 + srow + z0, bar);
         tma_g2s(PY + so * kSideBlkU, &p.ts_wave_u, x0 - 4, p.row_py + srow + z0, bar);
     };
 
@@ -456,6 +509,19 @@ __device__ __forceinline__ void march_side(const StepParams &p, const Seg &sg, f
     F4 sy;
 #pragma unroll
     for (int j = 0; j < 4; ++j) sy.a[j] = __ldg(p.sigy + colL + j);
+    // coefficients of a row with sigma_z == 0 (all rows of a side segment), per column: a, cu = 2a, cum,
+    // dt (sy - 0), dt (0 - sy), 1 - dt sy - the general expressions evaluated with sigma_z = 0
+    F4 ca, ccu, ccum, cdts, cpy1, cpy2;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float hs = p.hdt * sy.a[j];
+        ca.a[j] = 1.0f / (1.0f + hs);
+        ccu.a[j] = ca.a[j] * 2.0f;
+        ccum.a[j] = ca.a[j] * (hs - 1.0f);
+        cdts.a[j] = p.dt * sy.a[j];
+        cpy1.a[j] = p.dt * (0.0f - sy.a[j]);
+        cpy2.a[j] = fmaf(-p.dt, sy.a[j], 1.0f);
+    }
     mbar_wait(barP, (phase >> 4) & 1u);
     phase ^= 1u << 4;
 
@@ -520,33 +586,51 @@ __device__ __forceinline__ void march_side(const StepParams &p, const Seg &sg, f
         const float sz = __ldg(p.sigz + min(row, p.ze - 1));
         const size_t off = (size_t)min(row, p.ze - 1) * p.pitch;
         F4 un, qv, pzn, pyn;
+        float duy4[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const float uc0 = v[4 + q];
             float dpy = 0.f, duy = 0.f;
 #pragma unroll
             for (int k = 1; k <= H; ++k) {
                 dpy = fmaf(p.cy1[k], pyv[4 + q + k] - pyv[4 + q - k], dpy);
                 duy = fmaf(p.cy1[k], v[4 + q + k] - v[4 + q - k], duy);
             }
-            const float qq = (lap.a[q] + dpz.a[q]) + dpy;
-            const float hs = p.hdt * (sz + sy.a[q]);
-            const float a = 1.0f / (1.0f + hs);
-            const float cu = a * fmaf(-p.dt2, sz * sy.a[q], 2.0f);
-            const float cum = a * (hs - 1.0f);
-            const float aw = a * cW.a[q];
-            qv.a[q] = qq;
-            un.a[q] = fmaf(aw, qq, fmaf(cu, uc0, cum * cM.a[q]));
-            pzn.a[q] = fmaf(p.dt * (sy.a[q] - sz), duz4.a[q], fmaf(-p.dt, sz, 1.0f) * pzc.a[q]);
-            pyn.a[q] = fmaf(p.dt * (sz - sy.a[q]), duy, fmaf(-p.dt, sy.a[q], 1.0f) * pyv[4 + q]);
+            qv.a[q] = (lap.a[q] + dpz.a[q]) + dpy;
+            duy4[q] = duy;
+        }
+        if (__all_sync(0xffffffffu, sz == 0.f)) {
+            // (every row of a side segment: the column coefficients of the segment prologue, same bits)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                un.a[q] = fmaf(ca.a[q] * cW.a[q], qv.a[q], fmaf(ccu.a[q], v[4 + q], ccum.a[q] * cM.a[q]));
+                pzn.a[q] = fmaf(cdts.a[q], duz4.a[q], pzc.a[q]);
+                pyn.a[q] = fmaf(cpy1.a[q], duy4[q], cpy2.a[q] * pyv[4 + q]);
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float hs = p.hdt * (sz + sy.a[q]);
+                const float a = 1.0f / (1.0f + hs);
+                const float cu = a * fmaf(-p.dt2, sz * sy.a[q], 2.0f);
+                const float cum = a * (hs - 1.0f);
+                const float aw = a * cW.a[q];
+                un.a[q] = fmaf(aw, qv.a[q], fmaf(cu, v[4 + q], cum * cM.a[q]));
+                pzn.a[q] = fmaf(p.dt * (sy.a[q] - sz), duz4.a[q], fmaf(-p.dt, sz, 1.0f) * pzc.a[q]);
+                pyn.a[q] = fmaf(p.dt * (sz - sy.a[q]), duy4[q], fmaf(-p.dt, sy.a[q], 1.0f) * pyv[4 + q]);
+            }
         }
         st_masked<false>(p.pzn + sb + off, col, pzn, cmin, cmax, rowok);
         st_masked<false>(p.pyn + sb + off, col, pyn, cmin, cmax, rowok);
         st_masked<false>(um + off, col, un, cmin, cmax, rowok);
         if (MODE == 1) st_masked<true>(p.qw + sb + off, col, qv, cmin, cmax, rowok);
-        if (MODE == 2) {
+        if (MODE >= 2) {
             const F4 cQ = lds4(o + 2 * kSideBlkO);
             F4 g = lds4(o + 3 * kSideBlkO);
+            if (MODE == 3) {
+                const F4 cQ2 = lds4(o + 4 * kSideBlkO);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) g.a[q] = fmaf(cM.a[q], cQ2.a[q], g.a[q]);
+            }
 #pragma unroll
             for (int q = 0; q < 4; ++q) g.a[q] = fmaf(v[4 + q], cQ.a[q], g.a[q]);
             st_masked<false>(p.G + sb + off, col, g, cmin, cmax, rowok);
@@ -635,8 +719,11 @@ __global__ void __launch_bounds__(warps_per_cta(MODE) * 32, ctas_per_sm(MODE)) a
     if (p.trace && lane == 0) {
         unsigned long long t_end;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
         p.trace[2 * unit] = t_start;
         p.trace[2 * unit + 1] = t_end;
+        p.trace[2 * kMaxUnits + unit] = smid;                       // the SM the unit ran on
     }
 }
 
@@ -689,7 +776,7 @@ struct Geom {
     int max_rows;     // cap on the rows of one segment (chunk_rows; 0 = none)
 };
 
-constexpr int kMaxUnits = 16384;   // bound on resident warps of any device this could run on
+// (kMaxUnits, the bound on resident warps of any device this could run on, is defined at the top of the file)
 
 Geom make_geom(const fwi_acoustic_desc *d) {
     Geom g;
@@ -762,6 +849,11 @@ int64_t max_segments(const std::vector<Col> &cols, const Geom &g) {
     return 2 * n + 3 * (int64_t)kMaxUnits + 8;
 }
 
+// bytes of one work table: segments, then the unit offsets (16-byte aligned)
+inline int64_t table_bytes(int64_t max_segs) {
+    return max_segs * (int64_t)sizeof(Seg) + ((kMaxUnits + 1) * (int64_t)sizeof(int) + 15) / 16 * 16;
+}
+
 struct CostModel {
     double band, side, seg;
     int min_rows;
@@ -772,9 +864,20 @@ struct CostModel {
 // 3.0x (forward) / 3.4x (adjoint) the time of an interior row, a side-strip row about 1.0x.
 CostModel cost_model(const Geom &g, int mode = 1) {
     CostModel c;
-    c.band = env_dbl("FWI_B200_COST_BAND", mode == 2 ? 3.4 : 3.0);   // cost of a band row relative to an interior row
-    c.side = env_dbl("FWI_B200_COST_SIDE", 1.0);   // cost of one row of a side segment
-    c.seg = env_dbl("FWI_B200_COST_SEG", mode == 2 ? 9.0 : 6.0);     // prologue of a segment, in interior rows
+    // defaults per kernel mode (0 advance only, 1 + snapshot write, 2 imaging, 3 paired imaging); the environment
+    // overrides are tuning aids: FWI_B200_COST_BAND[_M<mode>] etc.
+    // (r02 sweep on C2, profiles/r02b_cost_sweep.txt: the advance-only and forward launches are bandwidth-bound on
+    // their interior rows, so a latency-bound band row weighs 5 interior rows there)
+    static const double band_d[4] = {5.0, 5.0, 3.4, 3.4}, side_d[4] = {1.0, 1.0, 1.0, 1.0}, seg_d[4] = {6.0, 6.0, 9.0, 9.0};
+    auto env_mode = [&](const char *name, double dflt) {
+        char buf[64];
+        snprintf(buf, sizeof(buf), "%s_M%d", name, mode);
+        return env_dbl(buf, env_dbl(name, dflt));
+    };
+    const int m = mode < 0 ? 0 : (mode > 3 ? 3 : mode);
+    c.band = env_mode("FWI_B200_COST_BAND", band_d[m]);   // cost of a band row relative to an interior row
+    c.side = env_mode("FWI_B200_COST_SIDE", side_d[m]);   // cost of one row of a side segment
+    c.seg = env_mode("FWI_B200_COST_SEG", seg_d[m]);      // prologue of a segment, in interior rows
     c.min_rows = env_int("FWI_B200_MINROWS", 4);
     if (g.max_rows > 0) c.min_rows = std::min(c.min_rows, g.max_rows);
     if (c.min_rows < 1) c.min_rows = 1;
@@ -1050,7 +1153,8 @@ extern "C" int fwi_acoustic_get_layout(const fwi_acoustic_desc *desc, fwi_acoust
     out->wave_fields = desc->pml_width > 0 ? 6 : 2;
     out->chunk_rows = g.max_rows;
     out->units_per_shot = (int32_t)(cols.size() / desc->n_shots);
-    out->unit_table_bytes = max_segments(cols, g) * (int64_t)sizeof(Seg) + (kMaxUnits + 1) * (int64_t)sizeof(int);
+    // up to three work tables per call (an adjoint loop alternates advance-only, paired-imaging and single-imaging launches)
+    out->unit_table_bytes = 3 * table_bytes(max_segments(cols, g));
     return FWI_OK;
 }
 
@@ -1141,39 +1245,64 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
         if (launched) return FWI_OK;
     }
 
-    // ---- work table: one cost-balanced unit per resident warp ----
+    // ---- work tables: one cost-balanced unit per resident warp, one table per kernel mode the loop launches ----
+    // Adjoint with imaging: G += field * q costs an 8-byte read-modify-write of the image per cell per step.  The field
+    // of the previous step is still on hand as this step's u-, so two steps are imaged by ONE pass over G: iterations
+    // alternate between an advance-only launch (MODE 0, 16 B per cell) and a launch that images both steps (MODE 3),
+    // the additions to G staying in the order one imaging per step makes them - results are bit-identical.  An odd
+    // last iteration images alone (MODE 2).  FWI_B200_PAIR=0 keeps one imaging per step.
+    const bool pair = mode == 2 && env_int("FWI_B200_PAIR", 1) != 0 && d->nsteps >= 2;
     int sms = 0;
-    const int occ = mode == 2 ? resident_h<2>(h, &sms) : (mode == 1 ? resident_h<1>(h, &sms) : resident_h<0>(h, &sms));
-    if (occ <= 0 || sms <= 0) {
-        fwi::set_error("acoustic step kernel cannot be resident on this device (occupancy %d): %s", occ,
-                       cudaGetErrorString(cudaGetLastError()));
-        return FWI_ERR_CUDA;
-    }
-    const int kNW = warps_per_cta(mode);
-    int n_units = std::min(kMaxUnits, sms * occ * kNW);
-    const int units_env = env_int("FWI_B200_UNITS", 0);
-    if (units_env > 0) n_units = std::min(kMaxUnits, units_env);
+    struct Table { int mode, n_units, blocks; Seg *d_segs; int *d_units; };
+    Table tables[3];
+    int n_tables = 0;
+    const int want[3] = {pair ? 0 : mode, pair ? 3 : -1, pair && (d->nsteps & 1) ? 2 : -1};
     thread_local std::vector<Col> cols;
     thread_local std::vector<Seg> segs;
     thread_local std::vector<int> unit_start;
-    build_units(d, g, n_units, cols, segs, unit_start, mode);
     list_columns(d, g, cols);
-    n_units = (int)unit_start.size() - 1;
-    FWI_CHECK_ARG((int64_t)segs.size() <= max_segments(cols, g), "internal: work table overflow");
-    Seg *d_segs = static_cast<Seg *>(b->unit_table);
-    int *d_units = reinterpret_cast<int *>(d_segs + max_segments(cols, g));
-    FWI_CHECK_CUDA(cudaMemcpyAsync(d_segs, segs.data(), segs.size() * sizeof(Seg), cudaMemcpyHostToDevice, st));
-    FWI_CHECK_CUDA(cudaMemcpyAsync(d_units, unit_start.data(), unit_start.size() * sizeof(int),
-                                   cudaMemcpyHostToDevice, st));
-    // (pageable source: cudaMemcpyAsync returns once the host data has been staged, so the vectors
-    // may be reused by the next call)
+    const int64_t max_segs = max_segments(cols, g);
+    for (int t = 0; t < 3; ++t) {
+        const int m = want[t];
+        if (m < 0) continue;
+        const int occ = m == 3 ? resident_h<3>(h, &sms) : (m == 2 ? resident_h<2>(h, &sms) : (m == 1 ? resident_h<1>(h, &sms) : resident_h<0>(h, &sms)));
+        if (occ <= 0 || sms <= 0) {
+            fwi::set_error("acoustic step kernel (mode %d) cannot be resident on this device (occupancy %d): %s", m, occ,
+                           cudaGetErrorString(cudaGetLastError()));
+            return FWI_ERR_CUDA;
+        }
+        const int nw = warps_per_cta(m);
+        int n_units = std::min(kMaxUnits, sms * occ * nw);
+        const int units_env = env_int("FWI_B200_UNITS", 0);
+        if (units_env > 0) n_units = std::min(kMaxUnits, units_env);
+        build_units(d, g, n_units, cols, segs, unit_start, m);
+        list_columns(d, g, cols);
+        n_units = (int)unit_start.size() - 1;
+        FWI_CHECK_ARG((int64_t)segs.size() <= max_segs, "internal: work table overflow");
+        Table &T = tables[n_tables];
+        T.mode = m; T.n_units = n_units; T.blocks = ceil_div(n_units, nw);
+        char *base = static_cast<char *>(b->unit_table) + (size_t)n_tables * table_bytes(max_segs);
+        T.d_segs = reinterpret_cast<Seg *>(base);
+        T.d_units = reinterpret_cast<int *>(base + max_segs * sizeof(Seg));
+        FWI_CHECK_CUDA(cudaMemcpyAsync(T.d_segs, segs.data(), segs.size() * sizeof(Seg), cudaMemcpyHostToDevice, st));
+        FWI_CHECK_CUDA(cudaMemcpyAsync(T.d_units, unit_start.data(), unit_start.size() * sizeof(int),
+                                       cudaMemcpyHostToDevice, st));
+        // (pageable source: cudaMemcpyAsync returns once the host data has been staged, so the vectors
+        // may be reused for the next table and by the next call)
+        ++n_tables;
+    }
+    auto table_of = [&](int m) -> const Table & {
+        for (int t = 0; t < n_tables; ++t)
+            if (tables[t].mode == m) return tables[t];
+        return tables[0];
+    };
 
     StepParams p;
     p.nzp = d->nzp; p.pitch = g.pitch;
     p.zs = g.zs; p.ze = g.ze; p.ys = g.ys; p.ye = g.ye;
     p.stride = (long long)d->nzp * g.pitch;
     p.S = d->n_shots;
-    p.segs = d_segs; p.unit_start = d_units; p.n_units = n_units;
+    p.segs = tables[0].d_segs; p.unit_start = tables[0].d_units; p.n_units = tables[0].n_units;
     p.w = b->w; p.sigz = b->sigz; p.sigy = b->sigy;
     p.inj_row_start = b->inj_row_start; p.inj_cell = b->inj_cell; p.inj_col = b->inj_col;
     p.n_inj = d->n_inj; p.inj_scale_a = d->inj_scale_a;
@@ -1196,7 +1325,7 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     if ((rc = make_map(&p.tm_wave_u, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kRowU)) != FWI_OK) return rc;
     if ((rc = make_map(&p.tm_wave_o, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kRowO)) != FWI_OK) return rc;
     if ((rc = make_map(&p.tm_w, b->w, d->nzp, g.pitch, kRowO)) != FWI_OK) return rc;
-    if (mode == 2) {
+    if (mode >= 2) {
         if ((rc = make_map(&p.tm_q, b->q_read, (int64_t)d->nsteps * fld_rows, g.pitch, kRowO)) != FWI_OK) return rc;
         if ((rc = make_map(&p.tm_g, b->image, fld_rows, g.pitch, kRowO)) != FWI_OK) return rc;
     } else {
@@ -1207,7 +1336,7 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
         if ((rc = make_map(&p.ts_wave_u, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kSideU)) != FWI_OK) return rc;
         if ((rc = make_map(&p.ts_wave_o, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kSideO)) != FWI_OK) return rc;
         if ((rc = make_map(&p.ts_w, b->w, d->nzp, g.pitch, kSideO)) != FWI_OK) return rc;
-        if (mode == 2) {
+        if (mode >= 2) {
             if ((rc = make_map(&p.ts_q, b->q_read, (int64_t)d->nsteps * fld_rows, g.pitch, kSideO)) != FWI_OK) return rc;
             if ((rc = make_map(&p.ts_g, b->image, fld_rows, g.pitch, kSideO)) != FWI_OK) return rc;
         } else {
@@ -1226,10 +1355,9 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     p.trace = nullptr;
     if (trace_path) {
         static unsigned long long *d_trace = nullptr;
-        if (!d_trace) cudaMalloc(&d_trace, 2 * sizeof(unsigned long long) * kMaxUnits);
+        if (!d_trace) cudaMalloc(&d_trace, 3 * sizeof(unsigned long long) * kMaxUnits);
         p.trace = d_trace;
     }
-    int blocks = ceil_div(n_units, kNW);
     SlabXfer push = {}, unpack = {};
     unsigned exchanges = 0;
     if (link) {
@@ -1258,14 +1386,22 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
         p.row_pz = pz ? (int)((pz - b->wave) / g.pitch) : 0;
         p.row_py = py ? (int)((py - b->wave) / g.pitch) : 0;
         p.row_q = n * fld_rows;
+        p.row_q2 = (n + 1) * fld_rows;
+        // which launch this iteration is: see the comment on `pair` above
+        int m = mode;
+        if (pair) m = (it & 1) ? 3 : (it + 1 < d->nsteps ? 0 : 2);
+        const Table &T = table_of(m);
+        p.segs = T.d_segs; p.unit_start = T.d_units; p.n_units = T.n_units;
+        const int blocks = T.blocks;
         p.qw = b->q_write ? b->q_write + (size_t)n * fld : nullptr;
         p.qr = b->q_read ? b->q_read + (size_t)n * fld : nullptr;
         p.G = b->image;
         p.inj_amp = d->n_inj ? b->inj_amp + (size_t)n * d->n_shots * d->n_inj : nullptr;
         p.smp_out = d->n_smp ? b->smp_out + (size_t)n * d->n_shots * d->n_smp : nullptr;
         cudaError_t e;
-        if (mode == 2) e = launch_h<2>(h, p, blocks, st);
-        else if (mode == 1) e = launch_h<1>(h, p, blocks, st);
+        if (m == 3) e = launch_h<3>(h, p, blocks, st);
+        else if (m == 2) e = launch_h<2>(h, p, blocks, st);
+        else if (m == 1) e = launch_h<1>(h, p, blocks, st);
         else e = launch_h<0>(h, p, blocks, st);
         if (e != cudaSuccess) {
             fwi::set_error("acoustic step launch failed at step %d: %s", n, cudaGetErrorString(e));
@@ -1304,11 +1440,23 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
         }
     }
     if (p.trace) {
+        // (dev aid: the trace is of the last launch; segs / unit_start are those of the last table built - run with
+        // FWI_B200_PAIR=0 or an even step count so that the two coincide)
+        const int n_units = (int)unit_start.size() - 1;
         std::vector<unsigned long long> tr(2 * (size_t)n_units);
         cudaStreamSynchronize(st);
         cudaMemcpy(tr.data(), p.trace, tr.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
-        if (FILE *f = fopen(trace_path, mode == 2 ? "a" : "w")) {
+        static int trace_call = 0;
+        char path[512];
+        snprintf(path, sizeof(path), "%s.%d", trace_path, trace_call++);     // one file per call
+        if (FILE *f = fopen(path, "w")) {
             unsigned long long t0 = ~0ull;
+            std::vector<int> smid(n_units);
+            {
+                std::vector<unsigned long long> sm(n_units);
+                cudaMemcpy(sm.data(), p.trace + 2 * kMaxUnits, sm.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+                for (int k = 0; k < n_units; ++k) smid[k] = (int)sm[k];
+            }
             for (int k = 0; k < n_units; ++k) t0 = std::min(t0, tr[2 * k]);
             const CostModel cm = cost_model(g, mode);
             for (int k = 0; k < n_units; ++k) {
@@ -1319,8 +1467,8 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
                     (segs[q].type == kSegInt ? ni : segs[q].type == kSegBand ? nb : ns) += rows;
                     cost += rows * cm.rate(segs[q].type) + cm.seg;
                 }
-                fprintf(f, "%d %d %llu %llu %d %d %d %d %.1f\n", mode, k, tr[2 * k] - t0, tr[2 * k + 1] - t0,
-                        unit_start[k + 1] - unit_start[k], ni, nb, ns, cost);
+                fprintf(f, "%d %d %llu %llu %d %d %d %d %.1f %d\n", mode, k, tr[2 * k] - t0, tr[2 * k + 1] - t0,
+                        unit_start[k + 1] - unit_start[k], ni, nb, ns, cost, smid[k]);
             }
             fclose(f);
         }

@@ -26,7 +26,7 @@ extern "C" {
 
 const char *fwi_last_error(void) { return fwi::g_err; }
 
-int fwi_version(void) { return 6; }
+int fwi_version(void) { return 7; }
 
 int64_t fwi_kernel_launches(void) { return fwi::g_launches.load(std::memory_order_relaxed); }
 
