@@ -91,6 +91,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     """Compile every CUDA source for sm_100a into the in-tree libfwi_b200.so (nvcc cross-compiles
     without a GPU)."""
     if not force and not is_stale():
+        build_ext()
         return SO_PATH
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
@@ -101,7 +102,60 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
     if verbose:
         print(r.stderr)
+    build_ext(force=True)
     return SO_PATH
+
+
+EXT_PATH = os.path.join(_HERE, "_b200fwi_torch.so")
+_EXT_SRC = os.path.join(_CSRC, "torch_ext.cpp")
+
+
+def ext_is_stale() -> bool:
+    if not os.path.exists(EXT_PATH):
+        return True
+    t = os.path.getmtime(EXT_PATH)
+    return any(os.path.getmtime(d) > t for d in (_EXT_SRC, os.path.join(_HERE, "..", "include", "fwi_b200.h")))
+
+
+def build_ext(force: bool = False) -> str:
+    """Compile csrc/torch_ext.cpp (TORCH_LIBRARY(b200fwi)) into the in-tree _b200fwi_torch.so, linked against
+    libfwi_b200.so next to it ($ORIGIN rpath) and the torch libraries of this interpreter."""
+    if not force and not ext_is_stale():
+        return EXT_PATH
+    import sysconfig
+    import torch
+    from torch.utils import cpp_extension as CE
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else (shutil.which("g++") or "g++")
+    cuda_home = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    inc = [f"-I{p}" for p in CE.include_paths()] + [f"-I{cuda_home}/include", f"-I{sysconfig.get_paths()['include']}"]
+    tlib = os.path.join(os.path.dirname(torch.__file__), "lib")
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
+           "-DTORCH_EXTENSION_NAME=_b200fwi_torch", *inc, _EXT_SRC, "-o", EXT_PATH,
+           f"-L{_HERE}", "-l:libfwi_b200.so", f"-L{tlib}", "-ltorch", "-ltorch_cpu", "-lc10", "-ltorch_cuda", "-lc10_cuda",
+           f"-L{cuda_home}/lib64", "-lcudart", "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{tlib}"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("building the TORCH_LIBRARY extension failed:\n" + r.stdout[-3000:] + r.stderr[-3000:])
+    return EXT_PATH
+
+
+_ops = None
+
+
+def ops():
+    """torch.ops.b200fwi (loads _b200fwi_torch.so).  Never falls back to anything else."""
+    global _ops
+    if _ops is None:
+        import torch
+        if not os.path.exists(EXT_PATH):
+            raise RuntimeError(f"{EXT_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(there is no CPU or PyTorch fallback for the propagator)")
+        lib()                                  # libfwi_b200.so first: the extension links against it
+        torch.ops.load_library(EXT_PATH)
+        _ops = torch.ops.b200fwi
+        if int(_ops.abi_version()) != int(lib().fwi_version()):
+            raise RuntimeError("_b200fwi_torch.so and libfwi_b200.so disagree on the ABI version: rebuild")
+    return _ops
 
 
 _lib = None

@@ -162,7 +162,20 @@ class _Plan:
         return smp_out
 
 
+def _settle(wave: torch.Tensor, nsteps: int, n_fields: int) -> torch.Tensor:
+    """The library starts every call with (u, u-) = fields (0, 1) and rotates the pairs each step: after an odd number
+    of steps put the fields back in that order so that the state can be carried into another call."""
+    if nsteps % 2 == 0:
+        return wave
+    perm = [1, 0, 3, 2, 5, 4][:n_fields]
+    return wave.view(n_fields, -1)[perm].contiguous().view(-1)
+
+
 class _ScalarFunction(torch.autograd.Function):
+    """forward / backward of the scalar propagator on the TORCH_LIBRARY(b200fwi) operators (csrc/torch_ext.cpp):
+    plan -> prepare (model pad + scale + PML profiles, one kernel) -> plan_points (cells + sorted lists, one kernel per
+    point set) -> run (the native time loop) [-> fold (image -> dJ/dv) in backward]."""
+
     @staticmethod
     def forward(ctx, v, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, loc_mode,
                 chunk_rows, checkpoint_every=0):
@@ -173,54 +186,64 @@ class _ScalarFunction(torch.autograd.Function):
             raise RuntimeError(f"source_locations must be [{S}, {Ns}, 2], got {tuple(x_s.shape)}")
         if x_r.dim() != 3 or x_r.shape[0] != S or x_r.shape[2] != 2:
             raise RuntimeError(f"receiver_locations must be [{S}, n_receivers, 2], got {tuple(x_r.shape)}")
+        if loc_mode not in ("trunc", "round"):
+            raise RuntimeError(f"unknown loc_mode {loc_mode!r}")
+        if not v.is_cuda:
+            raise RuntimeError("model['vp'] must be a CUDA tensor: this propagator has no CPU path")
+        O = _lib.ops()
         R = int(x_r.shape[1])
-        plan = _Plan(v, dx, dt, order, pml_width, vpmax, S, chunk_rows)
-        dev = plan.dev
-        s_cell, s_z, s_y, bad_s = plan.points(x_s, "source", loc_mode)
-        r_cell, r_z, r_y, bad_r = plan.points(x_r, "receiver", loc_mode)
-        # The out-of-model flag travels to pinned memory ahead of the forward launch and is read after it:
-        # the host only waits for work queued before this call, never for this call's own kernels, so the
-        # caller can queue its loss and backward pass while the forward pass runs (points are clamped:
-        # the launch itself is safe either way).
-        bad_host = torch.empty(1, dtype=torch.bool, pin_memory=True)
-        bad_host.copy_((bad_s | bad_r).reshape(1), non_blocking=True)
-        bad_event = torch.cuda.Event()
-        bad_event.record(torch.cuda.current_stream(dev))
-        amp = H.resample_up(source_amplitudes.detach().to(dev, torch.float32), plan.ratio).contiguous()
-        nti = nt * plan.ratio
-        need_v = ctx.needs_input_grad[0]
-        need_s = ctx.needs_input_grad[1]
-        q = None
-        r32 = r_cell.to(torch.int32).contiguous()
-        K = int(checkpoint_every)
+        dz, dy = H.spacing(dx)
+        dev = v.device
+        geo = (int(order), int(pml_width), dz, dy)
+        meta = O.scalar_plan(v, float(dt), dz, dy, int(order), int(pml_width), float(vpmax) if vpmax is not None else -1.0,
+                             S, int(chunk_rows), 0, 0)
+        ratio, n_fields, stride = int(meta[1]), int(meta[7]), int(meta[8])
+        vd = v.detach()
+        w, sigz, sigy = O.scalar_prepare(vd, meta, *geo, 0, 0)
+        bad = torch.zeros(1, dtype=torch.int32, device=dev)
+        rnd = loc_mode == "round"
+        s_cell, s_start, s_sc, s_so = O.scalar_plan_points(x_s, vd, meta, bad, *geo, rnd, 0, 0)
+        r_cell, r_start, r_sc, r_so = O.scalar_plan_points(x_r, vd, meta, bad, *geo, rnd, 0, 0)
+        # The out-of-model flag travels to pinned memory ahead of the time loop and is read after the loop is queued:
+        # the host only waits for work queued before this call, never for this call's own kernels
+        flag = O.flag_begin(bad)
+        amp = H.resample_up(source_amplitudes.detach().to(dev, torch.float32), ratio).contiguous()
+        nti = nt * ratio
+        need_v, need_s = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        cur = torch.cuda.current_stream(dev)
+
+        def run(nsteps, amp_n, wave, q_write):
+            ev = _lib.time_loop_begin(cur)
+            out = O.scalar_run(w, sigz, sigy, wave, s_start, s_sc, s_so, amp_n, r_cell, q_write, None, None, meta, S,
+                               nsteps, False, *geo, int(chunk_rows))
+            _lib.time_loop_end(cur, ev, "acoustic_fwd" if q_write is not None else "acoustic_fwd0", nsteps, S)
+            return out
+
+        q, K = None, int(checkpoint_every)
         ctx.ckpt = None
-        if need_v and K > 0 and K < nti:
-            # wavefield checkpointing: keep the state every K steps instead of a snapshot per step;
-            # backward() recomputes the snapshots of one segment at a time
-            wave, ckpts, parts = plan.new_wave(), [], []
-            lists = plan.lists(s_cell)
-            for t0 in range(0, nti, K):
-                n = min(K, nti - t0)
-                ckpts.append(wave.clone())
-                parts.append(plan.run(nsteps=n, adjoint=0, inj=lists, inj_amp=amp[t0:t0 + n], smp_cell=r32,
-                                      n_smp=R, wave=wave))
-                wave = plan.settle(wave, n)
-            rec = torch.cat(parts, 0)
-            ctx.ckpt = (K, ckpts)
-        else:
-            if need_v:
-                q = torch.empty(nti * S * plan.stride, dtype=torch.float32, device=dev)
-            rec = plan.run(nsteps=nti, adjoint=0, inj=plan.lists(s_cell), inj_amp=amp,
-                           smp_cell=r32, n_smp=R, q_write=q)
-        bad_event.synchronize()
-        if bool(bad_host[0]):
-            raise RuntimeError("source/receiver location outside the model")
-        out = rec[::plan.ratio].contiguous() if plan.ratio > 1 else rec
-        ctx.plan = plan
+        wave = torch.zeros(n_fields * S * stride, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            if need_v and 0 < K < nti:
+                # wavefield checkpointing: keep the state every K steps instead of a snapshot per step;
+                # backward() recomputes the snapshots of one segment at a time
+                ckpts, parts = [], []
+                for t0 in range(0, nti, K):
+                    n = min(K, nti - t0)
+                    ckpts.append(wave.clone())
+                    parts.append(run(n, amp[t0:t0 + n], wave, None))
+                    wave = _settle(wave, n, n_fields)
+                rec = torch.cat(parts, 0)
+                ctx.ckpt = (K, ckpts)
+            else:
+                if need_v:
+                    q = torch.empty(nti * S * stride, dtype=torch.float32, device=dev)
+                rec = run(nti, amp, wave, q)
+        O.flag_end(flag)
+        out = rec[::ratio].contiguous() if ratio > 1 else rec
+        ctx.saved = (vd, meta, w, sigz, sigy, s_cell, r_cell, r_start, r_sc, r_so, s_start, s_sc, s_so)
         ctx.q = q
         ctx.amp = amp if need_v else None
-        ctx.r32 = r32
-        ctx.geom = (s_cell, r_cell, r_z, r_y, nt, S, Ns, R, nti)
+        ctx.dims = (nt, S, Ns, R, nti, ratio, n_fields, stride, geo, int(chunk_rows))
         ctx.need = (need_v, need_s)
         ctx.src_like = source_amplitudes.detach()
         return out
@@ -228,50 +251,54 @@ class _ScalarFunction(torch.autograd.Function):
     @staticmethod
     @torch.autograd.function.once_differentiable
     def backward(ctx, grad_rec):
-        plan: _Plan = ctx.plan
-        s_cell, r_cell, r_z, r_y, nt, S, Ns, R, nti = ctx.geom
+        O = _lib.ops()
+        vd, meta, w, sigz, sigy, s_cell, r_cell, r_start, r_sc, r_so, s_start, s_sc, s_so = ctx.saved
+        nt, S, Ns, R, nti, ratio, n_fields, stride, geo, chunk_rows = ctx.dims
         need_v, need_s = ctx.need
-        dev = plan.dev
+        dev = vd.device
         g = grad_rec.to(dev, torch.float32)
-        if plan.ratio > 1:
+        if ratio > 1:
             g_in = torch.zeros(nti, S, R, dtype=torch.float32, device=dev)
-            g_in[::plan.ratio] = g
+            g_in[::ratio] = g
         else:
             g_in = g.contiguous()
-        image = None
-        if need_v:
-            image = torch.zeros(int(plan.lay.n_images) * plan.stride, dtype=torch.float32, device=dev)
-        s32 = s_cell.to(torch.int32).contiguous()
-        if ctx.ckpt is not None:
-            K, ckpts = ctx.ckpt
-            qseg = torch.empty(K * S * plan.stride, dtype=torch.float32, device=dev)
-            awave, parts = plan.new_wave(), []
-            src_lists, rec_lists = plan.lists(s_cell), plan.lists(r_cell)
-            starts = list(range(0, nti, K))
-            for t0 in reversed(starts):
-                n = min(K, nti - t0)
-                plan.run(nsteps=n, adjoint=0, inj=src_lists, inj_amp=ctx.amp[t0:t0 + n], smp_cell=ctx.r32,
-                         n_smp=0, q_write=qseg, wave=ckpts.pop())
-                parts.append(plan.run(nsteps=n, adjoint=1, inj=rec_lists, inj_amp=g_in[t0:t0 + n].contiguous(),
-                                      smp_cell=s32, n_smp=Ns, q_read=qseg, image=image, wave=awave))
-                awave = plan.settle(awave, n)
-            gs = torch.cat(parts[::-1], 0)
-            ctx.ckpt = None
-        else:
-            gs = plan.run(nsteps=nti, adjoint=1, inj=plan.lists(r_cell), inj_amp=g_in, smp_cell=s32, n_smp=Ns,
-                          q_read=ctx.q if need_v else None, image=image)
-        grad_v = grad_s = None
-        if need_v:
-            G = image.view(int(plan.lay.n_images), plan.nzp, plan.pitch).sum(0)
-            G = G[:, plan.col0:plan.col0 + plan.nyp].contiguous()
-            # the source term of dJ/dw: mu/a sampled at the source cells times the wavelet
-            flat = G.view(-1)
-            pcell = ((s_cell // plan.pitch) * plan.nyp + (s_cell % plan.pitch - plan.col0)).reshape(-1)
-            flat.index_add_(0, pcell, (gs * ctx.amp).sum(0).reshape(-1))
-            gpad = (2.0 / plan.v_pad) * G
-            grad_v = H.replicate_pad_adjoint(gpad, plan.P)
+        image = torch.zeros(S * stride, dtype=torch.float32, device=dev) if need_v else None
+        cur = torch.cuda.current_stream(dev)
+
+        def run(nsteps, adjoint, wave, amp_n, q_write=None, q_read=None):
+            ev = _lib.time_loop_begin(cur)
+            if adjoint:
+                out = O.scalar_run(w, sigz, sigy, wave, r_start, r_sc, r_so, amp_n, s_cell, None, q_read,
+                                   image if q_read is not None else None, meta, S, nsteps, True, *geo, chunk_rows)
+                tag = "acoustic_adj"
+            else:
+                out = O.scalar_run(w, sigz, sigy, wave, s_start, s_sc, s_so, amp_n, r_cell[:, :0], q_write, None, None, meta,
+                                   S, nsteps, False, *geo, chunk_rows)
+                tag = "acoustic_fwd"
+            _lib.time_loop_end(cur, ev, tag, nsteps, S)
+            return out
+
+        with torch.cuda.device(dev):
+            awave = torch.zeros(n_fields * S * stride, dtype=torch.float32, device=dev)
+            if ctx.ckpt is not None:
+                K, ckpts = ctx.ckpt
+                qseg = torch.empty(K * S * stride, dtype=torch.float32, device=dev)
+                parts = []
+                for t0 in reversed(range(0, nti, K)):
+                    n = min(K, nti - t0)
+                    run(n, False, ckpts.pop(), ctx.amp[t0:t0 + n], q_write=qseg)
+                    parts.append(run(n, True, awave, g_in[t0:t0 + n].contiguous(), q_read=qseg))
+                    awave = _settle(awave, n, n_fields)
+                gs = torch.cat(parts[::-1], 0)
+                ctx.ckpt = None
+            else:
+                gs = run(nti, True, awave, g_in, q_read=ctx.q if need_v else None)
+            grad_v = grad_s = None
+            if need_v:
+                # dJ/dv = fold((2 / v_pad) (sum_s image_s + source term)): one native call (csrc/host_kernels.cu)
+                grad_v = O.scalar_fold(image, gs, ctx.amp, s_cell, vd, meta, S, *geo)
         if need_s:
-            grad_s = H.resample_up_adjoint(gs, plan.ratio, ctx.src_like.to(dev, torch.float32))
+            grad_s = H.resample_up_adjoint(gs, ratio, ctx.src_like.to(dev, torch.float32))
             grad_s = grad_s.to(ctx.src_like.device, ctx.src_like.dtype)
         ctx.q = None
         return grad_v, grad_s, None, None, None, None, None, None, None, None, None, None

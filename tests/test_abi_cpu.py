@@ -137,3 +137,18 @@ def test_misfit_and_slab_entry_points_check_arguments_on_the_host():
     link = _lib.SlabLink(8, 15, 1, 0, 0, 0, 0, 0, None, None, None, 0, 0)      # ghost_cols != 8 * 2
     assert L.fwi_acoustic_run_slab(ctypes.byref(ad), ctypes.byref(_lib.AcousticBuffers()), ctypes.byref(link), None) == -1
     assert b"ghost_cols" in L.fwi_last_error()
+
+
+def test_torch_library_extension_loads_and_registers_every_operator():
+    """csrc/torch_ext.cpp: TORCH_LIBRARY(b200fwi) - the PyTorch C++ operators over the C ABI (no compute without a GPU)."""
+    import torch
+    from physicsbasedfwi2_b200 import _lib
+    ops = _lib.ops()
+    for name in ("scalar_plan", "scalar_prepare", "scalar_plan_points", "scalar_run", "scalar_fold", "flag_begin", "flag_end",
+                 "abi_version"):
+        assert hasattr(ops, name), name
+    assert int(ops.abi_version()) == int(_lib.lib().fwi_version())
+    with pytest.raises(RuntimeError, match="CUDA tensor"):           # TORCH_CHECK -> RuntimeError, like deepwave
+        ops.scalar_plan(torch.zeros(4, 4), 1e-3, 10.0, 10.0, 4, 10, -1.0, 1, 0, 0, 0)
+    with pytest.raises(RuntimeError, match="2-D"):
+        ops.scalar_plan(torch.zeros(4), 1e-3, 10.0, 10.0, 4, 10, -1.0, 1, 0, 0, 0)

@@ -63,7 +63,9 @@ def _worker(rank, world, port, T, order, out, exchange="peer"):
                                            order=order, pml_width=p["pw"], dtype=torch.float32)
         out[rank] = dict(oracle=(K.rel_l2(rec, r0), K.rel_l2(gv, gv0), K.rel_l2(gs, gs0)),
                          single=(K.rel_l2(rec, r1), K.rel_l2(gv, gv1), K.rel_l2(gs, gs1)),
-                         exact=bool(torch.equal(rec, r1) and torch.equal(gv, gv1)))
+                         # traces bitwise; the gradient to round-off: the undecomposed path folds the padding with the
+                         # native kernel (csrc/host_kernels.cu), the slab path with torch ops - edge cells sum in another order
+                         exact=bool(torch.equal(rec, r1) and K.rel_l2(gv, gv1) <= 5e-7))
     finally:
         dist.destroy_process_group()
 
