@@ -60,6 +60,10 @@ WORKLOADS = {
     # trace normalisation, L1 misfit (fused kernel) -> adjoint -> generator backward -> Adam step.
     "c5": dict(nz=151, ny=200, dx=10.0, order=4, pml=10, nt=4001, dt=1e-3, freq=8.0, n_rec=200, rec_stride=1,
                z_acq=0, survey_shots=18, vmin=1500.0, vmax=4500.0, e2e_iteration=True),
+    # the reference's inner-loop FWI (models/networks.py:15278-15423, VaeLatentNoPhy_Net.prop):
+    # 101 x 101, dx 10 m, 15 Hz, 800 steps of 1.5 ms, 10 shots x 101 receivers at z = 0, 100 Adam(lr=10) iterations
+    "f3": dict(nz=101, ny=101, dx=10.0, order=4, pml=10, nt=800, dt=1.5e-3, freq=15.0, n_rec=101, rec_stride=1,
+               z_acq=0, survey_shots=10, vmin=1500.0, vmax=4400.0, inner_loop=100),
     "c1": dict(nz=100, ny=300, dx=10.0, order=4, pml=10, nt=1000, dt=1e-3, freq=15.0, n_rec=101,
                rec_stride=3, z_acq=0, survey_shots=10, vmin=1500.0, vmax=3500.0),
 }
@@ -455,6 +459,53 @@ def run_c5(args, w, dev, rank, world, local):
         dist.destroy_process_group()
 
 
+def run_f3(args, w, dev):
+    """One step = the reference's whole inner loop (100 x: clamp, forward, misfit, adjoint, Adam) on one GPU:
+    captured CUDA graph replays against the same loop driven from Python with a host sync per iteration."""
+    import physicsbasedfwi2_b200 as pkg
+    from physicsbasedfwi2_b200 import _host
+    from physicsbasedfwi2_b200.inversion import inner_loop_fwi
+    from physicsbasedfwi2_b200.scalar import Propagator
+    from physicsbasedfwi2_b200.wavelets import ricker
+    nz, ny, nt, S, R, E = w["nz"], w["ny"], w["nt"], w["survey_shots"], w["n_rec"], w["inner_loop"]
+    x_s = torch.zeros(S, 1, 2)
+    x_s[:, 0, 1] = torch.arange(S).float() * (101 * w["dx"] / S)
+    x_r = torch.zeros(S, R, 2)
+    x_r[:, :, 1] = (torch.arange(R).float() * w["dx"])[None]
+    wavelet = ricker(w["freq"], nt, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1)
+    true = synth_model(w).to(dev)
+    with torch.no_grad():
+        observed = Propagator({"vp": true}, w["dx"], vpmax=w["vmax"])(wavelet.repeat(1, S, 1).contiguous().to(dev),
+                                                                      x_s.to(dev), x_r.to(dev), w["dt"])
+    start = torch.full((nz, ny), 2500.0, device=dev)
+
+    def loop(graph):
+        return inner_loop_fwi(start, observed, wavelet, x_s, x_r, w["dx"], w["dt"], num_epochs=E, lr=10.0,
+                              vmin=w["vmin"], vmax=w["vmax"], kind="mse", graph=graph)
+
+    out = {}
+    for graph in (True, False):
+        for _ in range(max(1, args.warmup // 3)):
+            loop(graph)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            v, losses = loop(graph)
+        torch.cuda.synchronize()
+        out[graph] = (time.perf_counter() - t0) / args.steps
+    nti = nt * _host.inner_step(w["dt"], w["dx"], w["dx"], w["vmax"])[0]
+    work = nz * ny * nti * S * 2 * E
+    line = {"metric": "FWI gradient Gcell-updates/s (fwd+adjoint)", "value": round(work / out[True] / 1e9, 3),
+            "unit": "Gcell-updates/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(1e3 * out[True], 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"f3: inner-loop FWI of models/networks.py:15278-15423: {nz}x{ny}, {S} shots x {R} receivers, "
+                                   f"{nt} steps (x{nti // nt} inner), {E} Adam iterations per step; one CUDA graph replayed"},
+            "ms_per_iteration": {"cuda_graph": round(1e3 * out[True] / E, 4), "python_loop": round(1e3 * out[False] / E, 4)},
+            "first_last_misfit": [losses[0], losses[-1]], "gpu_launches": int(pkg.kernel_launches())}
+    print(json.dumps(line), flush=True)
+
+
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
@@ -839,6 +890,8 @@ def main():
 
     if w.get("e2e_iteration"):
         return run_c5(args, w, dev, rank, world, local)
+    if w.get("inner_loop"):
+        return run_f3(args, w, dev)
 
     return run_gpu(args, w, dev, rank, world, local)
 

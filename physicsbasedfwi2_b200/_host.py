@@ -61,9 +61,8 @@ def resample_up(x: torch.Tensor, ratio: int) -> torch.Tensor:
     spec = torch.fft.rfft(x, dim=0)
     if n % 2 == 0:
         # the Nyquist bin of the short signal is split between +-n/2 of the long one
-        half = torch.ones(spec.shape[0], dtype=x.dtype, device=x.device)
-        half[-1] = 0.5
-        spec = spec * half.reshape((-1,) + (1,) * (x.dim() - 1))
+        # (no host scalar written into a device tensor: this runs inside CUDA-graph captures)
+        spec = torch.cat([spec[:-1], spec[-1:] * 0.5], dim=0)
     pad = torch.zeros((m // 2 + 1 - spec.shape[0],) + tuple(x.shape[1:]), dtype=spec.dtype,
                       device=x.device)
     return torch.fft.irfft(torch.cat([spec, pad], dim=0), n=m, dim=0) * ratio

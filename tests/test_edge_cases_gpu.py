@@ -172,6 +172,39 @@ def test_inner_loop_fwi_reduces_the_misfit_and_matches_the_torch_glue(cuda_lib):
     assert float(v.min()) >= 1500.0 and float(v.max()) <= 4400.0
 
 
+def test_inner_loop_cuda_graph_replays_match_the_eager_loop(cuda_lib):
+    """The loop of models/networks.py:15372-15415 in its own geometry (101 x 101, dx 10 m, 15 Hz, dt 1.5 ms, 10 shots x
+    101 receivers at z = 0, Adam lr 10, clamp [1500, 4400]): captured as one CUDA graph per batch index and replayed
+    (no host sync, losses read back once) against the same loop run eagerly."""
+    from physicsbasedfwi2_b200.inversion import inner_loop_fwi
+    from physicsbasedfwi2_b200.scalar import Propagator
+    nz = ny = 101
+    S, R, nt, dt, dx = 10, 101, 240, 1.5e-3, 10.0
+    true = K.layered_model(nz, ny, seed=4, noise=0.0).clamp(1500.0, 4400.0)
+    start = torch.full((nz, ny), 2400.0)
+    x_s = torch.zeros(S, 1, 2)
+    x_s[:, 0, 1] = torch.arange(S).float() * (101 * dx / S)
+    x_r = torch.zeros(S, R, 2)
+    x_r[:, :, 1] = (torch.arange(R).float() * dx)[None]
+    wavelet = K.ricker(15.0, nt, dt, 1 / 15.0).reshape(-1, 1, 1)
+    with torch.no_grad():
+        observed = Propagator({"vp": true.to(DEV)}, dx, vpmax=4400.0)(wavelet.repeat(1, S, 1).contiguous().to(DEV),
+                                                                      x_s.to(DEV), x_r.to(DEV), dt)
+    outs = {}
+    for graph, nb, shuffle in ((False, 1, False), (True, 1, False), (False, 2, False), (True, 2, False), (True, 2, True)):
+        torch.manual_seed(0)
+        v, losses = inner_loop_fwi(start.to(DEV), observed, wavelet, x_s, x_r, dx, dt, num_epochs=9, num_batches=nb,
+                                   graph=graph, shuffle=shuffle)
+        assert len(losses) == 9 * nb and all(l == l and l > 0 for l in losses)
+        outs[(graph, nb, shuffle)] = (v, losses)
+    for nb in (1, 2):
+        (v0, l0), (v1, l1) = outs[(False, nb, False)], outs[(True, nb, False)]
+        assert max(abs(a - b) / a for a, b in zip(l0, l1)) < 1e-5, (l0, l1)
+        assert K.rel_l2(v1, v0) < 1e-6
+        assert l0[-1] < l0[0]
+    assert outs[(True, 2, True)][1][-1] < outs[(True, 2, True)][1][0]        # shuffled batches: still a descent
+
+
 @pytest.mark.parametrize("small", ["1", "0"], ids=["cluster-resident", "step-kernel"])
 def test_many_points_per_shot_and_a_very_shallow_grid(cuda_lib, small, monkeypatch):
     """More receivers than the 512 threads of a CTA of the cluster-resident kernel (its slow-path loops),
