@@ -255,6 +255,28 @@ int fwi_trace_misfit_backward(const fwi_misfit_desc *desc, const float *pred, co
                               const float *obs, const float *grad_loss, float *grad_pred, void *workspace,
                               void *stream);
 
+/* ---- the steps either side of the elastic gradient (DENISE glue of the reference's elastic `prop`) ----------- */
+/* Frequency stage of d.add_fwi_stage(fc_low=0.0, fc_high=10.0, ...) (models/networks.py:9147): Butterworth low-pass of
+ * even `order` on every trace of in [nt][n_traces] (traces fast), zero initial state; zero_phase: a second pass
+ * backwards in time (the operator is then symmetric: it is its own adjoint).  in == out is allowed. */
+typedef struct fwi_butter_desc {
+    int32_t nt, n_traces;
+    int32_t order;            /* even, 2..16 */
+    int32_t zero_phase;
+    double dt, fc_low, fc_high; /* fc_low must be 0 (low-pass) */
+} fwi_butter_desc;
+int fwi_butterworth_lowpass(const fwi_butter_desc *desc, const float *in, float *out, void *stream);
+
+/* Gradient post-processing of models/networks.py:9194-9240, in place on three [nz][ny] gradients: rho gradient times
+ * (row index)^depth_pow, rows [0, water_rows) of all three zeroed, each gradient scaled by max|model| / max|gradient|,
+ * rho additionally times rho_factor plus rho_offset.  stats: 6 floats of device scratch (the maxima, left for inspection). */
+typedef struct fwi_gradpost_desc {
+    int32_t nz, ny, water_rows;
+    double depth_pow, rho_factor, rho_offset;   /* 1.5, 0.5, 1e-10 in the reference */
+} fwi_gradpost_desc;
+int fwi_elastic_gradient_post(const fwi_gradpost_desc *desc, float *grad_vp, float *grad_vs, float *grad_rho,
+                              const float *vp, const float *vs, const float *rho, float *stats, void *stream);
+
 /* ---- common ---------------------------------------------------------------------------- */
 
 const char *fwi_last_error(void);     /* thread-local, never NULL */

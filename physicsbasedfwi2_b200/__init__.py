@@ -12,6 +12,7 @@ from . import misfit  # noqa: F401
 from . import slab  # noqa: F401
 from . import fwiloss  # noqa: F401
 from . import inversion  # noqa: F401
+from . import denise_glue  # noqa: F401
 from ._lib import build, kernel_launches, lib  # noqa: F401
 
 
@@ -23,4 +24,4 @@ def Propagator(model: dict, dx, *args, **kwargs):
     return scalar.Propagator(model, dx, *args, **kwargs)
 
 
-__all__ = ["scalar", "elastic", "misfit", "slab", "fwiloss", "inversion", "wavelets", "Propagator", "build", "lib", "kernel_launches"]
+__all__ = ["scalar", "elastic", "misfit", "slab", "fwiloss", "inversion", "denise_glue", "wavelets", "Propagator", "build", "lib", "kernel_launches"]

@@ -13,7 +13,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_HERE, "csrc")
 SO_PATH = os.environ.get("FWI_B200_LIB") or os.path.join(_HERE, "libfwi_b200.so")   # (env: tuning variants, scripts/dev_variants.sh)
-_SOURCES = ["common.cu", "acoustic.cu", "acoustic_small.cu", "elastic.cu", "misfit.cu", "host_kernels.cu"]
+_SOURCES = ["common.cu", "acoustic.cu", "acoustic_small.cu", "elastic.cu", "misfit.cu", "host_kernels.cu", "glue.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
 
@@ -60,6 +60,16 @@ SLAB_HEADER_BYTES = 256
 class MisfitDesc(C.Structure):
     _fields_ = [("nt", C.c_int32), ("n_traces", C.c_int32), ("kind", C.c_int32), ("normalize", C.c_int32),
                 ("eps", C.c_float)]
+
+
+class ButterDesc(C.Structure):
+    _fields_ = [("nt", C.c_int32), ("n_traces", C.c_int32), ("order", C.c_int32), ("zero_phase", C.c_int32),
+                ("dt", C.c_double), ("fc_low", C.c_double), ("fc_high", C.c_double)]
+
+
+class GradPostDesc(C.Structure):
+    _fields_ = [("nz", C.c_int32), ("ny", C.c_int32), ("water_rows", C.c_int32), ("depth_pow", C.c_double),
+                ("rho_factor", C.c_double), ("rho_offset", C.c_double)]
 
 
 class ElasticDesc(C.Structure):
@@ -204,6 +214,10 @@ def lib() -> C.CDLL:
     L.fwi_trace_misfit.restype = C.c_int
     L.fwi_trace_misfit_backward.argtypes = [C.POINTER(MisfitDesc)] + [C.c_void_p] * 7
     L.fwi_trace_misfit_backward.restype = C.c_int
+    L.fwi_butterworth_lowpass.argtypes = [C.POINTER(ButterDesc), C.c_void_p, C.c_void_p, C.c_void_p]
+    L.fwi_butterworth_lowpass.restype = C.c_int
+    L.fwi_elastic_gradient_post.argtypes = [C.POINTER(GradPostDesc)] + [C.c_void_p] * 8
+    L.fwi_elastic_gradient_post.restype = C.c_int
     L.fwi_elastic_wave_floats.argtypes = [C.POINTER(ElasticDesc)]
     L.fwi_elastic_wave_floats.restype = C.c_int64
     for name in ("fwi_elastic_forward", "fwi_elastic_backward"):

@@ -126,3 +126,17 @@ def test_injection_lists_leave_out_masked_points():
                 assert int(cell[s, int(col[e])]) == int(c[e])
                 seen.append((s, int(col[e])))
     assert sorted(seen) == sorted((s, j) for s in range(S) for j in range(n) if bool(keep[s, j]))
+
+
+def test_su_reader_round_trip(tmp_path):
+    """SU seismograms (the files the reference's elastic prop shuffles at models/networks.py:9051-9071)."""
+    import numpy as np
+    from physicsbasedfwi2_b200.denise_glue import denise_geometry, read_su, write_su
+    tr = np.random.default_rng(0).standard_normal((7, 301)).astype(np.float32)
+    p = str(tmp_path / "seis_x.su.shot1")
+    write_su(p, tr, 2e-3)
+    back, dt = read_su(p)
+    assert back.shape == (7, 301) and np.array_equal(back, tr) and abs(dt - 2e-3) < 1e-12
+    x_s, x_r = denise_geometry([3, 0, 45, 7, 12, 20])
+    assert tuple(x_s.shape) == (6, 1, 2) and tuple(x_r.shape) == (6, 370, 2)          # 370 receivers, :8994-9001
+    assert float(x_s[2, 0, 1]) == 400.0 + 45 * 160.0 and float(x_r[0, -1, 1]) == 7780.0 and float(x_r[0, 0, 0]) == 460.0
