@@ -637,7 +637,7 @@ def run_gpu(args, w, dev, rank, world, local):
             vs_d[:24] = 0.0
             rho_d = 310.0 * v_d.detach() ** 0.25
             prop = pkg.Propagator({"vp": v_d, "vs": vs_d, "rho": rho_d}, w["dx"], pml_width=w["pml"],
-                                  accuracy=w["order"], vpmax=w["vmax"])
+                                  accuracy=w["order"], vpmax=w["vmax"], checkpoint_every=w.get("ckpt", 0))
         else:
             prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"],
                               checkpoint_every=w.get("ckpt", 0), slabs=slabs and world > 1,

@@ -202,6 +202,10 @@ typedef struct fwi_elastic_desc {
     int32_t n_src;            /* explosive sources per shot */
     int32_t n_rec;            /* two-component receivers per shot */
     double dz, dy, dt;
+    int32_t source_kind;      /* 0: explosive (sxx, szz += dt s; DENISE QUELLTYPB 1), 1: vertical force (vz += dt bz s;
+                                 QUELLTYPB 2, models/networks.py:10452), 2: horizontal force (vy += dt by s) */
+    int32_t adj_parity;       /* backward in segments (wavefield checkpointing): number of adjoint steps already taken
+                                 on this wave / scratch pair, modulo 2 (the memory variables ping-pong between them) */
 } fwi_elastic_desc;
 
 typedef struct fwi_elastic_buffers {
@@ -215,7 +219,8 @@ typedef struct fwi_elastic_buffers {
     const int32_t *src_cell;  /* [n_shots][n_src] cell = z*nyp + y */
     const int32_t *src_link;  /* [n_shots][n_src] chains of points sharing a cell: bits 0..29 = index of the
                                  next point of the chain + 1 (0 = last), bit 30 set = not the first of its chain */
-    const float *src_amp;     /* [nsteps][n_shots][n_src] (forward) */
+    const float *src_amp;     /* [nsteps][n_shots][n_src] (forward; backward too when source_kind != 0: the force
+                                 sources depend on the buoyancy, whose image gets a source-cell term) */
     const int32_t *rec_cell;  /* [n_shots][n_rec] */
     const int32_t *rec_link;  /* [n_shots][n_rec] as src_link (used by the adjoint injection) */
     float *rec_out;           /* [2][nsteps][n_shots][n_rec]: vy, vz recorded before each step (forward) */

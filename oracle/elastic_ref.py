@@ -119,8 +119,13 @@ def _dm(f, dim, h, c, inv_d):
 
 
 def elastic_forward(vp, vs, rho, dx, source_amplitudes, x_s, x_r, dt, *, order: int = 4, pml_width: int = 10,
-                    vpmax: Optional[float] = None, pml_freq: float = 25.0, loc_mode: str = "trunc"):
-    """Differentiable forward model (vp, vs, rho, source_amplitudes) -> [2, nt, S, R] (vy, vz)."""
+                    vpmax: Optional[float] = None, pml_freq: float = 25.0, loc_mode: str = "trunc",
+                    source: str = "explosive"):
+    """Differentiable forward model (vp, vs, rho, source_amplitudes) -> [2, nt, S, R] (vy, vz).
+    source: 'explosive' (sxx, szz += dt s; DENISE QUELLTYPB 1, the reference's default), 'fz' (vertical force:
+    vz += dt bz s; QUELLTYPB 2, models/networks.py:10452) or 'fy' (horizontal force: vy += dt by s)."""
+    if source not in ("explosive", "fz", "fy"):
+        raise RuntimeError(f"unknown source kind {source!r}")
     dtype = vp.dtype
     dz, dy = _pair(dx)
     nz, ny = vp.shape
@@ -179,10 +184,19 @@ def elastic_forward(vp, vs, rho, dx, source_amplitudes, x_s, x_r, dt, *, order: 
         d7 = _dp(vy, 0, h, c, 1.0 / dz); psi[6] = bzh * psi[6] + azh * d7
         d8 = _dp(vz, 1, h, c, 1.0 / dy); psi[7] = byh * psi[7] + ayh * d8
         e3 = (d7 + psi[6]) + (d8 + psi[7])
-        inj = torch.zeros(S, nzp * nyp, dtype=dtype).scatter_add(1, s_lin, dti * amp[n]).reshape(S, nzp, nyp)
-        sxx = sxx + F.pad(dti * (l2m_i * e1 + lam_i * e2), pad4) + inj
-        szz = szz + F.pad(dti * (lam_i * e1 + l2m_i * e2), pad4) + inj
+        sxx = sxx + F.pad(dti * (l2m_i * e1 + lam_i * e2), pad4)
+        szz = szz + F.pad(dti * (lam_i * e1 + l2m_i * e2), pad4)
         syz = syz + F.pad((dti * mu_i) * e3, pad4)
+        if source == "explosive":
+            inj = torch.zeros(S, nzp * nyp, dtype=dtype).scatter_add(1, s_lin, dti * amp[n]).reshape(S, nzp, nyp)
+            sxx, szz = sxx + inj, szz + inj
+        else:
+            b = (bz if source == "fz" else by).reshape(-1)[s_lin]                 # buoyancy at the source cells [S, Ns]
+            inj = torch.zeros(S, nzp * nyp, dtype=dtype).scatter_add(1, s_lin, (dti * b) * amp[n]).reshape(S, nzp, nyp)
+            if source == "fz":
+                vz = vz + inj
+            else:
+                vy = vy + inj
     return torch.stack([torch.stack(rec_y, 0), torch.stack(rec_z, 0)], 0)
 
 

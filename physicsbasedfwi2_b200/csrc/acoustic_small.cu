@@ -295,12 +295,14 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
 template <int H, int CPT, bool ADJ>
 int try_launch(const SmallParams &p0, cudaStream_t st, bool *launched) {
     auto kern = acoustic_small_kernel<H, CPT, ADJ>;
-    static int max_smem = -1;
-    if (max_smem < 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
+    static int smem_of[64];               // per device: function attributes are per device (0 = not set yet)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int max_smem = (dev >= 0 && dev < 64) ? smem_of[dev] : 0;
+    if (max_smem == 0) {
         cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (dev >= 0 && dev < 64) smem_of[dev] = max_smem;
     }
     const int nf = p0.wave_pml ? 6 : 2;
     if (p0.nyp >= 4096 || p0.nzp >= 4096) return FWI_OK;      // cell descriptors pack row and column in 12 bits each

@@ -532,49 +532,86 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_f_fused
     }
 }
 
-// ---- point kernels: one thread per shot walks that shot's list (fixed order: deterministic) ----
-// out[k][s][r] = field_k[s][cell[s][r]] for k = 0 (a) and 1 (b), scaled
-__global__ void elastic_sample2(const float *a, const float *b, long long cells, int S, int n, const int *cell,
-                                float *out_a, float *out_b, float scale) {
+// ---- point kernels (one launch per time step: the injection that ends a step and the sampling that begins the next
+// one touch different fields, so they share a launch; deterministic: points that share a cell are chained by `link`
+// (bits 0..29: index of the next point in the same cell + 1, 0 = none; bit 30 set: not the first of its chain) and
+// added by the first one in list order) ----
+struct PointArgs {
+    long long cells;
+    int S;
+    // sampling: out_a[t] = scale * (a[c] (+ b[c] if sum)) * (coef ? coef[cell] : 1); out_b[t] = scale * b[c] (two-component)
+    int n_smp;
+    const int *smp_cell;
+    const float *sa, *sb, *s_coef;
+    float *out_a, *out_b;
+    int smp_sum;
+    float s_scale;
+    // image term of force sources (adjoint): g_img[c] += s_scale * img_amp[t] * sa[c] (chains of smp_link: one owner per cell)
+    float *g_img;
+    const float *img_amp;
+    const int *smp_link;
+    // injection: a[c] += scale * coef * amp_a[t]; b[c] += scale * amp_b[t] (b may be NULL)
+    int n_inj;
+    const int *inj_cell, *inj_link;
+    float *ia, *ib;
+    const float *amp_a, *amp_b, *i_coef;
+    float i_scale;
+};
+
+__global__ void __launch_bounds__(128) elastic_points(const PointArgs q) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= S * n) return;
-    const int s = t / n;
-    const long long c = (long long)s * cells + __ldg(cell + t);
+    const int n_i = q.S * q.n_inj, n_s = q.S * q.n_smp;
     pdl_wait();
-    out_a[t] = scale * a[c];
-    if (out_b) out_b[t] = scale * b[c];
-}
-// sum-sample: out[s][r] = scale * (a + b)[cell]
-__global__ void elastic_sample_sum(const float *a, const float *b, long long cells, int S, int n, const int *cell,
-                                   float *out, float scale) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= S * n) return;
-    const int s = t / n;
-    const long long c = (long long)s * cells + __ldg(cell + t);
-    pdl_wait();
-    out[t] = scale * (a[c] + b[c]);
-}
-// a[cell] += scale * amp_a, b[cell] += scale * amp_b.  One thread per point; points that share a
-// cell are chained by `link` (bits 0..29: index of the next point in the same cell + 1, 0 = none;
-// bit 30 set: not the first of its chain) and added by the first one in list order: deterministic.
-__global__ void elastic_inject2(float *a, float *b, long long cells, int S, int n, const int *cell, const int *link,
-                                const float *amp_a, const float *amp_b, float scale) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= S * n) return;
-    int l = __ldg(link + t);
-    if (l & 0x40000000) return;
-    const int s = t / n;
-    const long long c = (long long)s * cells + __ldg(cell + t);
-    pdl_wait();
-    float va = a[c] + scale * __ldg(amp_a + t), vb = b[c] + scale * __ldg(amp_b + t);
-    while ((l & 0x3fffffff) != 0) {
-        const int k = s * n + (l & 0x3fffffff) - 1;
-        va = va + scale * __ldg(amp_a + k);
-        vb = vb + scale * __ldg(amp_b + k);
-        l = __ldg(link + k);
+    if (t < n_i) {
+        int l = __ldg(q.inj_link + t);
+        if (!(l & 0x40000000)) {
+            const int s = t / q.n_inj;
+            const int cell = __ldg(q.inj_cell + t);
+            const long long c = (long long)s * q.cells + cell;
+            const float k = q.i_scale * (q.i_coef ? __ldg(q.i_coef + cell) : 1.0f);
+            float va = q.ia[c] + k * __ldg(q.amp_a + t), vb = q.ib ? q.ib[c] + k * __ldg(q.amp_b + t) : 0.f;
+            while ((l & 0x3fffffff) != 0) {
+                const int m = s * q.n_inj + (l & 0x3fffffff) - 1;
+                va = va + k * __ldg(q.amp_a + m);
+                if (q.ib) vb = vb + k * __ldg(q.amp_b + m);
+                l = __ldg(q.inj_link + m);
+            }
+            q.ia[c] = va;
+            if (q.ib) q.ib[c] = vb;
+        }
+    } else if (t < n_i + n_s) {
+        const int u = t - n_i;
+        const int s = u / q.n_smp;
+        const int cell = __ldg(q.smp_cell + u);
+        const long long c = (long long)s * q.cells + cell;
+        const float k = q.s_scale * (q.s_coef ? __ldg(q.s_coef + cell) : 1.0f);
+        const float a = q.sa[c];
+        if (q.smp_sum) q.out_a[u] = k * (a + q.sb[c]);
+        else {
+            q.out_a[u] = k * a;
+            if (q.out_b) q.out_b[u] = k * q.sb[c];
+        }
+        // force sources, adjoint: d(dt b s)/db at the source cell; the first point of a chain adds for all of them
+        if (q.g_img) {
+            int l = __ldg(q.smp_link + u);
+            if (!(l & 0x40000000)) {
+                float g = q.g_img[c] + (q.s_scale * __ldg(q.img_amp + u)) * a;
+                while ((l & 0x3fffffff) != 0) {
+                    const int m = s * q.n_smp + (l & 0x3fffffff) - 1;
+                    g = g + (q.s_scale * __ldg(q.img_amp + m)) * a;
+                    l = __ldg(q.smp_link + m);
+                }
+                q.g_img[c] = g;
+            }
+        }
     }
-    a[c] = va;
-    b[c] = vb;
+}
+
+inline void launch_points(const PointArgs &q, cudaStream_t st) {
+    const long long n = (long long)q.S * (q.n_inj + q.n_smp);
+    if (n == 0) return;
+    launch_pdl(elastic_points, dim3((unsigned)((n + 127) / 128)), dim3(128), st, q);
+    fwi::count_launch();
 }
 
 int check(const fwi_elastic_desc *d) {
@@ -638,8 +675,13 @@ template <int H, bool SAVE>
 void launch_f_fused(const EParams &p, dim3 grid, cudaStream_t st) {
     constexpr size_t smem = (3 * (kTX + 4 * H) * (kTZ + 4 * H) + 2 * (kTX + 2 * H) * (kTZ + 2 * H)) * sizeof(float);
     auto kern = elastic_f_fused<H, 512, SAVE>;
-    static bool once = false;
-    if (!once) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); once = true; }
+    static bool done[64] = {};           // function attributes are per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !done[dev]) {
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (dev >= 0 && dev < 64) done[dev] = true;
+    }
     launch_pdl_smem(kern, grid, dim3(512), smem, st, p);
 }
 template <bool SAVE>
@@ -675,17 +717,25 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
     float *setA[9], *setB[9];
     for (int k = 0; k < 5; ++k) { setA[k] = b->wave + k * fld; setB[k] = b->wave + (13 + k) * fld; }
     for (int k = 0; k < 4; ++k) { setA[5 + k] = b->wave + (PSI + k) * fld; setB[5 + k] = b->wave + (18 + k) * fld; }
+    // point work of a step: sample the receivers before it, inject the sources after it.  The injection of step n and
+    // the sampling of step n + 1 touch different fields and share one launch.
+    FWI_CHECK_ARG(d->source_kind >= 0 && d->source_kind <= 2, "source_kind must be 0 (explosive), 1 (vertical force) or 2 (horizontal force)");
+    auto fill_sample = [&](PointArgs &q, int n) {
+        q.n_smp = d->n_rec; q.smp_cell = b->rec_cell; q.sa = p.f[VY]; q.sb = p.f[VZ]; q.s_coef = nullptr;
+        q.out_a = b->rec_out + n * nrec; q.out_b = b->rec_out + ((long long)d->nsteps + n) * nrec;
+        q.smp_sum = 0; q.s_scale = 1.0f; q.g_img = nullptr;
+    };
     for (int n = 0; n < d->nsteps; ++n) {
         if (fused) {
             float **in = (n & 1) ? setB : setA, **out = (n & 1) ? setA : setB;
             for (int k = 0; k < 5; ++k) { p.f[k] = in[k]; p.fo[k] = out[k]; }
             for (int k = 0; k < 4; ++k) { p.psi_in[k] = in[5 + k]; p.psi_out[k] = out[5 + k]; }
         }
-        if (d->n_rec) {
-            launch_pdl(elastic_sample2, dim3((unsigned)((nrec + 127) / 128)), dim3(128), st,
-                p.f[VY], p.f[VZ], p.cells, d->n_shots, d->n_rec, b->rec_cell, b->rec_out + n * nrec,
-                b->rec_out + ((long long)d->nsteps + n) * nrec, 1.0f);
-            fwi::count_launch();
+        if (n == 0 && d->n_rec) {
+            PointArgs q = {};
+            q.cells = p.cells; q.S = d->n_shots;
+            fill_sample(q, 0);
+            launch_points(q, st);
         }
         p.snap = b->snap ? b->snap + (long long)n * 5 * fld : nullptr;
         if (fused) {
@@ -702,12 +752,29 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
             }
             fwi::count_launch(2);
         }
-        if (d->n_src) {
-            float *sxx = fused ? p.fo[SXX] : p.f[SXX], *szz = fused ? p.fo[SZZ] : p.f[SZZ];
-            launch_pdl(elastic_inject2, dim3((unsigned)((nsrc + 127) / 128)), dim3(128), st,
-                sxx, szz, p.cells, d->n_shots, d->n_src, b->src_cell, b->src_link, b->src_amp + n * nsrc,
-                b->src_amp + n * nsrc, p.dt);
-            fwi::count_launch();
+        {
+            float **cur = fused ? p.fo : p.f;       // the fields this step has just written
+            PointArgs q = {};
+            q.cells = p.cells; q.S = d->n_shots;
+            if (d->n_src) {
+                q.n_inj = d->n_src; q.inj_cell = b->src_cell; q.inj_link = b->src_link;
+                q.amp_a = q.amp_b = b->src_amp + n * nsrc; q.i_scale = p.dt; q.i_coef = nullptr;
+                if (d->source_kind == 0) { q.ia = cur[SXX]; q.ib = cur[SZZ]; }
+                else if (d->source_kind == 1) { q.ia = cur[VZ]; q.ib = nullptr; q.i_coef = b->bz; }
+                else { q.ia = cur[VY]; q.ib = nullptr; q.i_coef = b->by; }
+            }
+            if (d->n_rec && n + 1 < d->nsteps) {
+                fill_sample(q, n + 1);
+                q.sa = cur[VY]; q.sb = cur[VZ];
+                // a force source writes the velocity the sampling of the next step reads: keep the two apart then
+                if (d->n_src && d->source_kind != 0) {
+                    PointArgs qi = q;
+                    qi.n_smp = 0;
+                    launch_points(qi, st);
+                    q.n_inj = 0;
+                }
+            }
+            launch_points(q, st);
         }
         FWI_CHECK_CUDA(cudaGetLastError());
     }
@@ -734,16 +801,35 @@ extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic
     static const int fnt = getenv("FWI_B200_EL_NT") ? atoi(getenv("FWI_B200_EL_NT")) : 512;
     const dim3 fblock(fnt == 256 || fnt == 1024 ? fnt : 512);
     const dim3 fgrid((d->nyp - 2 * p.h + kTX - 1) / kTX, (d->nzp - 2 * p.h + kTZ - 1) / kTZ, d->n_shots);
+    FWI_CHECK_ARG(d->source_kind >= 0 && d->source_kind <= 2, "source_kind must be 0, 1 or 2");
+    FWI_CHECK_ARG(d->source_kind == 0 || d->n_src == 0 || (b->src_amp && b->src_link),
+                  "force sources: the adjoint pass needs src_amp and src_link (image term of the buoyancy)");
+    // adjoint of a step, in reverse: sample the adjoint field at the sources (-> grad_src[n]), B2, B1, inject grad_rec[n].
+    // The injection of step n and the sampling of step n - 1 share one launch (different fields, except for force
+    // sources, which are sampled from the velocities the injection writes: two launches then).
+    auto fill_sample = [&](PointArgs &q, int n) {
+        q.n_smp = d->n_src; q.smp_cell = b->src_cell; q.out_a = b->grad_src + n * nsrc; q.out_b = nullptr;
+        q.s_scale = p.dt; q.s_coef = nullptr; q.g_img = nullptr;
+        if (d->source_kind == 0) { q.sa = p.f[SXX]; q.sb = p.f[SZZ]; q.smp_sum = 1; }
+        else {
+            const int comp = d->source_kind == 1 ? VZ : VY;
+            q.sa = p.f[comp]; q.sb = nullptr; q.smp_sum = 0;
+            q.s_coef = d->source_kind == 1 ? b->bz : b->by;
+            q.g_img = b->grad + (d->source_kind == 1 ? 4 : 3) * fld;
+            q.img_amp = b->src_amp + n * nsrc; q.smp_link = b->src_link;
+        }
+    };
     for (int n = d->nsteps - 1; n >= 0; --n) {
-        if (d->n_src) {
-            launch_pdl(elastic_sample_sum, dim3((unsigned)((nsrc + 127) / 128)), dim3(128), st,
-                p.f[SXX], p.f[SZZ], p.cells, d->n_shots, d->n_src, b->src_cell, b->grad_src + n * nsrc, p.dt);
-            fwi::count_launch();
+        if (n == d->nsteps - 1 && d->n_src) {
+            PointArgs q = {};
+            q.cells = p.cells; q.S = d->n_shots;
+            fill_sample(q, n);
+            launch_points(q, st);
         }
         p.snap = const_cast<float *>(b->snap) + (long long)n * 5 * fld;
         if (fused) {
             // memory variables ping-pong between the wave workspace and `scratch` (see elastic_b2_fused)
-            const int par = (d->nsteps - 1 - n) & 1;
+            const int par = ((d->nsteps - 1 - n) + d->adj_parity) & 1;
             for (int k = 0; k < 8; ++k) {
                 float *a = p.f[PSI + k], *c = b->scratch + k * fld;
                 p.psi_in[k] = par ? c : a;
@@ -761,11 +847,24 @@ extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic
             ELASTIC_LAUNCH_H(elastic_b1b);
             fwi::count_launch(4);
         }
-        if (d->n_rec) {
-            launch_pdl(elastic_inject2, dim3((unsigned)((nrec + 127) / 128)), dim3(128), st,
-                p.f[VY], p.f[VZ], p.cells, d->n_shots, d->n_rec, b->rec_cell, b->rec_link, b->grad_rec + n * nrec,
-                b->grad_rec + ((long long)d->nsteps + n) * nrec, 1.0f);
-            fwi::count_launch();
+        {
+            PointArgs q = {};
+            q.cells = p.cells; q.S = d->n_shots;
+            if (d->n_rec) {
+                q.n_inj = d->n_rec; q.inj_cell = b->rec_cell; q.inj_link = b->rec_link; q.ia = p.f[VY]; q.ib = p.f[VZ];
+                q.amp_a = b->grad_rec + n * nrec; q.amp_b = b->grad_rec + ((long long)d->nsteps + n) * nrec;
+                q.i_scale = 1.0f; q.i_coef = nullptr;
+            }
+            if (d->n_src && n > 0) {
+                fill_sample(q, n - 1);
+                if (d->n_rec && d->source_kind != 0) {
+                    PointArgs qi = q;
+                    qi.n_smp = 0; qi.g_img = nullptr;
+                    launch_points(qi, st);
+                    q.n_inj = 0;
+                }
+            }
+            launch_points(q, st);
         }
         FWI_CHECK_CUDA(cudaGetLastError());
     }

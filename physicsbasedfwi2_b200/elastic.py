@@ -74,9 +74,13 @@ def effective_parameters(vp_pad, vs_pad, rho_pad):
     return l2m, lam, mu_yz, by, bz
 
 
+_SOURCE_KINDS = {"explosive": 0, "fz": 1, "fy": 2}
+
+
 class _ElasticFunction(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, vp, vs, rho, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, pml_freq, loc_mode):
+    def forward(ctx, vp, vs, rho, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, pml_freq, loc_mode,
+                source="explosive", checkpoint_every=0):
         for name, t in (("vp", vp), ("vs", vs), ("rho", rho)):
             if t.dim() != 2 or t.shape != vp.shape:
                 raise RuntimeError(f"model['{name}'] must be 2-D with the shape of model['vp']")
@@ -86,6 +90,8 @@ class _ElasticFunction(torch.autograd.Function):
                 raise RuntimeError(f"model['{name}'] must be float32, got {t.dtype}")
         if order not in (2, 4, 6, 8):
             raise RuntimeError(f"accuracy must be 2, 4, 6 or 8, got {order}")
+        if source not in _SOURCE_KINDS:
+            raise RuntimeError(f"source must be one of {sorted(_SOURCE_KINDS)}, got {source!r}")
         if source_amplitudes.dim() != 3:
             raise RuntimeError("source_amplitudes must be [nt, n_shots, n_sources_per_shot]")
         nt, S, Ns = source_amplitudes.shape
@@ -123,31 +129,73 @@ class _ElasticFunction(torch.autograd.Function):
 
         need_model = any(ctx.needs_input_grad[:3])
         need_any = need_model or ctx.needs_input_grad[3]
-        desc = _lib.ElasticDesc(nzp, nyp, order, pw, S, nti, Ns, R, dz, dy, dti)
+        kind = _SOURCE_KINDS[source]
         L = _lib.lib()
-        n_wave = int(L.fwi_elastic_wave_floats(C.byref(desc)))
+        cells_n = nzp * nyp
+        K = int(checkpoint_every)
+        if K % 2:
+            K += 1                              # even segments: the fused kernels ping-pong buffers every step
+        use_ckpt = need_any and 0 < K < nti
+        # the adjoint kernels read five snapshot fields per inner step (also when only the source gradient is wanted:
+        # they accumulate the images unconditionally): say what that needs before asking the allocator for it
+        snap_steps = K if use_ckpt else nti
+        snap_bytes = snap_steps * 5 * S * cells_n * 4 if need_any else 0
+        state_bytes = (13 * S * cells_n * 4) * ((nti + K - 1) // K) if use_ckpt else 0
+        free, _ = torch.cuda.mem_get_info(dev)
+        free += torch.cuda.memory_reserved(dev) - torch.cuda.memory_allocated(dev)     # blocks the caching allocator holds
+        if snap_bytes + state_bytes > 0.97 * free:
+            raise RuntimeError(
+                f"elastic gradient of {S} shots x {nti} inner steps on a {nzp} x {nyp} grid needs {snap_bytes / 2**30:.1f} GiB of "
+                f"snapshots (+ {state_bytes / 2**30:.1f} GiB of checkpoints); {free / 2**30:.1f} GiB are free.  Use fewer shots per "
+                f"call or checkpoint_every=K (K snapshots + one state per K steps; one extra forward pass).")
+
+        def desc_for(n, parity=0):
+            return _lib.ElasticDesc(nzp, nyp, order, pw, S, n, Ns, R, dz, dy, dti, kind, parity)
+
+        n_wave = int(L.fwi_elastic_wave_floats(C.byref(desc_for(nti))))
         wave = torch.zeros(n_wave, dtype=torch.float32, device=dev)
-        rec = torch.empty(2, nti, S, R, dtype=torch.float32, device=dev)
-        snap = torch.empty(nti * 5 * S * nzp * nyp, dtype=torch.float32, device=dev) if need_any else None
-        b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
-                                _ptr(s_link), _ptr(amp), _ptr(r_cell), _ptr(r_link), _ptr(rec), _ptr(snap), None, None,
-                                None, None)
         cur = torch.cuda.current_stream(dev)
-        with torch.cuda.device(dev):
-            ev = _lib.time_loop_begin(cur)
-            _lib.check(L.fwi_elastic_forward(C.byref(desc), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_forward")
-            _lib.time_loop_end(cur, ev, "elastic_fwd", nti, S)
+
+        def run_forward(n, amp_n, wave, snap):
+            rec = torch.empty(2, n, S, R, dtype=torch.float32, device=dev)
+            d = desc_for(n)
+            b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
+                                    _ptr(s_link), _ptr(amp_n), _ptr(r_cell), _ptr(r_link), _ptr(rec), _ptr(snap), None, None,
+                                    None, None)
+            with torch.cuda.device(dev):
+                ev = _lib.time_loop_begin(cur)
+                _lib.check(L.fwi_elastic_forward(C.byref(d), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_forward")
+                _lib.time_loop_end(cur, ev, "elastic_fwd", n, S)
+            return rec
+
+        snap, ckpts = None, None
+        if use_ckpt:
+            # wavefield checkpointing: the 13 live fields every K steps instead of five snapshot fields every step
+            ckpts, parts = [], []
+            for t0 in range(0, nti, K):
+                n = min(K, nti - t0)
+                ckpts.append(wave[:13 * S * cells_n].clone())
+                parts.append(run_forward(n, amp[t0:t0 + n], wave, None))
+            rec = torch.cat(parts, 1)
+        else:
+            if need_any:
+                snap = torch.empty(nti * 5 * S * cells_n, dtype=torch.float32, device=dev)
+            rec = run_forward(nti, amp, wave, snap)
         out = rec[:, ::ratio].contiguous() if ratio > 1 else rec
-        ctx.saved = (vp.detach(), vs.detach(), rho.detach(), params, prof_z, prof_y, s_cell, r_cell, s_link, r_link, snap, desc)
-        ctx.meta = (nt, S, Ns, R, nti, ratio, P, dev)
+        ctx.saved = (vp.detach(), vs.detach(), rho.detach(), params, prof_z, prof_y, s_cell, r_cell, s_link, r_link, snap)
+        ctx.ckpt = (K, ckpts) if use_ckpt else None
+        ctx.amp = amp
+        ctx.run_forward = run_forward
+        ctx.desc_for = desc_for
+        ctx.meta = (nt, S, Ns, R, nti, ratio, P, dev, n_wave, cells_n, nzp, nyp)
         ctx.src_like = source_amplitudes.detach()
         return out
 
     @staticmethod
     @torch.autograd.function.once_differentiable
     def backward(ctx, grad_rec):
-        vp, vs, rho, params, prof_z, prof_y, s_cell, r_cell, s_link, r_link, snap, desc = ctx.saved
-        nt, S, Ns, R, nti, ratio, P, dev = ctx.meta
+        vp, vs, rho, params, prof_z, prof_y, s_cell, r_cell, s_link, r_link, snap = ctx.saved
+        nt, S, Ns, R, nti, ratio, P, dev, n_wave, cells, nzp, nyp = ctx.meta
         need_model = any(ctx.needs_input_grad[:3])
         g = grad_rec.to(dev, torch.float32)
         if ratio > 1:
@@ -156,19 +204,38 @@ class _ElasticFunction(torch.autograd.Function):
         else:
             g_in = g.contiguous()
         L = _lib.lib()
-        cells = desc.nzp * desc.nyp
-        wave = torch.zeros(int(L.fwi_elastic_wave_floats(C.byref(desc))), dtype=torch.float32, device=dev)
+        wave = torch.zeros(n_wave, dtype=torch.float32, device=dev)
         scratch = torch.zeros(8 * S * cells, dtype=torch.float32, device=dev)
-        grad = torch.zeros(5, S, desc.nzp, desc.nyp, dtype=torch.float32, device=dev)
-        gsrc = torch.zeros(nti, S, Ns, dtype=torch.float32, device=dev)
-        b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
-                                _ptr(s_link), None, _ptr(r_cell), _ptr(r_link), None, _ptr(snap), _ptr(scratch), _ptr(grad),
-                                _ptr(g_in), _ptr(gsrc))
+        grad = torch.zeros(5, S, nzp, nyp, dtype=torch.float32, device=dev)
         cur = torch.cuda.current_stream(dev)
-        with torch.cuda.device(dev):
-            ev = _lib.time_loop_begin(cur)
-            _lib.check(L.fwi_elastic_backward(C.byref(desc), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_backward")
-            _lib.time_loop_end(cur, ev, "elastic_adj", nti, S)
+
+        def run_adjoint(n, g_n, amp_n, snap_n, parity):
+            gsrc = torch.zeros(n, S, Ns, dtype=torch.float32, device=dev)
+            d = ctx.desc_for(n, parity)
+            b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
+                                    _ptr(s_link), _ptr(amp_n), _ptr(r_cell), _ptr(r_link), None, _ptr(snap_n), _ptr(scratch),
+                                    _ptr(grad), _ptr(g_n), _ptr(gsrc))
+            with torch.cuda.device(dev):
+                ev = _lib.time_loop_begin(cur)
+                _lib.check(L.fwi_elastic_backward(C.byref(d), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_backward")
+                _lib.time_loop_end(cur, ev, "elastic_adj", n, S)
+            return gsrc
+
+        if ctx.ckpt is not None:
+            K, ckpts = ctx.ckpt
+            snap_seg = torch.empty(K * 5 * S * cells, dtype=torch.float32, device=dev)
+            fwave = torch.zeros(n_wave, dtype=torch.float32, device=dev)
+            parts, parity = [], 0
+            for t0 in reversed(range(0, nti, K)):
+                n = min(K, nti - t0)
+                fwave[:13 * S * cells].copy_(ckpts.pop())
+                ctx.run_forward(n, ctx.amp[t0:t0 + n], fwave, snap_seg)          # recompute this segment's snapshots
+                parts.append(run_adjoint(n, g_in[:, t0:t0 + n].contiguous(), ctx.amp[t0:t0 + n], snap_seg, parity))
+                parity = (parity + n) & 1
+            gsrc = torch.cat(parts[::-1], 0)
+            ctx.ckpt = None
+        else:
+            gsrc = run_adjoint(nti, g_in, ctx.amp, snap, 0)
         gvp = gvs = grho = gs = None
         if need_model:
             gpar = grad.sum(1)                       # fixed-order sum over shots
@@ -180,9 +247,9 @@ class _ElasticFunction(torch.autograd.Function):
         if ctx.needs_input_grad[3]:
             gs = H.resample_up_adjoint(gsrc, ratio, ctx.src_like.to(dev, torch.float32))
             gs = gs.to(ctx.src_like.device, ctx.src_like.dtype)
-        ctx.saved = None
+        ctx.saved = ctx.run_forward = ctx.desc_for = ctx.amp = None
         return (gvp if ctx.needs_input_grad[0] else None, gvs if ctx.needs_input_grad[1] else None,
-                grho if ctx.needs_input_grad[2] else None, gs, None, None, None, None, None, None, None, None, None)
+                grho if ctx.needs_input_grad[2] else None, gs) + (None,) * 11
 
 
 class Propagator(torch.nn.Module):
@@ -193,10 +260,14 @@ class Propagator(torch.nn.Module):
     models/networks.py:9054-9061).  Sources are explosive (equal sxx / szz moment rate).
     ``pml_width`` (default 10), ``accuracy`` 2/4/6/8 (default 4), ``pml_freq`` (Hz, the frequency the
     C-PML is tuned to, default 25), ``vpmax``, ``loc_mode`` as in the scalar propagator.
+    ``source``: 'explosive' (default; DENISE's QUELLTYPB 1), 'fz' vertical or 'fy' horizontal point force
+    (QUELLTYPB 2 / 3; the reference sets 2 at models/networks.py:10452).  ``checkpoint_every`` = K: wavefield
+    checkpointing - the 13 live fields every K inner steps instead of five snapshot fields every step, the backward
+    pass recomputes one K-step segment at a time (BASELINE config 3 at k = 1 is 28 GB of snapshots per shot).
     """
 
     def __init__(self, model: dict, dx, pml_width=None, survey_pad=None, vpmax=None, *, accuracy: int = 4,
-                 pml_freq: float = 25.0, loc_mode: str = "trunc"):
+                 pml_freq: float = 25.0, loc_mode: str = "trunc", source: str = "explosive", checkpoint_every: int = 0):
         super().__init__()
         if not isinstance(model, dict) or not {"vp", "vs", "rho"} <= set(model):
             raise RuntimeError("model must be a dict with keys 'vp', 'vs' and 'rho'")
@@ -214,9 +285,15 @@ class Propagator(torch.nn.Module):
         self.accuracy = accuracy
         self.pml_freq = float(pml_freq)
         self.loc_mode = loc_mode
+        if source not in _SOURCE_KINDS:
+            raise RuntimeError(f"source must be one of {sorted(_SOURCE_KINDS)}, got {source!r}")
+        self.source = source
+        if checkpoint_every < 0:
+            raise RuntimeError("checkpoint_every must be >= 0")
+        self.checkpoint_every = int(checkpoint_every)
 
     def forward(self, source_amplitudes, source_locations, receiver_locations, dt):
         m = self.model
         return _ElasticFunction.apply(m["vp"], m["vs"], m["rho"], source_amplitudes, source_locations,
                                       receiver_locations, float(dt), self.dx, self.accuracy, self.pml_width,
-                                      self.vpmax, self.pml_freq, self.loc_mode)
+                                      self.vpmax, self.pml_freq, self.loc_mode, self.source, self.checkpoint_every)
