@@ -86,6 +86,9 @@ typedef struct fwi_acoustic_buffers {
     const float *q_read;      /* same layout or NULL: snapshots consumed by the imaging sum */
     float *image;             /* [n_images][nzp][pitch] or NULL: image[s] += field * q_read */
     void *unit_table;         /* [unit_table_bytes] scratch: the library writes its work table here */
+    int64_t q_step_stride;    /* floats between the snapshots of consecutive steps in q_write; 0 = n_shots * shot_stride.
+                                 Lets a forward call that advances a SUBSET of the shots of a gradient (forward launches
+                                 are fastest when their wavefields fit L2) write into the snapshot array of all of them */
 } fwi_acoustic_buffers;
 
 /* Fills `out` for `desc`.  Replaces nothing in the reference (layout is private to deepwave

@@ -37,7 +37,7 @@ class AcousticBuffers(C.Structure):
                 ("wave", C.c_void_p), ("inj_row_start", C.c_void_p), ("inj_cell", C.c_void_p),
                 ("inj_col", C.c_void_p), ("inj_amp", C.c_void_p), ("smp_cell", C.c_void_p),
                 ("smp_out", C.c_void_p), ("q_write", C.c_void_p), ("q_read", C.c_void_p),
-                ("image", C.c_void_p), ("unit_table", C.c_void_p)]
+                ("image", C.c_void_p), ("unit_table", C.c_void_p), ("q_step_stride", C.c_int64)]
 
 
 class ModelDesc(C.Structure):

@@ -1208,6 +1208,8 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     FWI_CHECK_ARG(d->n_inj == 0 || (b->inj_row_start && b->inj_cell && b->inj_col && b->inj_amp),
                   "injection lists required when n_inj > 0");
     FWI_CHECK_ARG(!(b->q_write && b->q_read), "q_write and q_read are mutually exclusive");
+    FWI_CHECK_ARG(b->q_step_stride == 0 || (b->q_write && b->q_step_stride >= (int64_t)d->n_shots * d->nzp * make_geom(d).pitch),
+                  "q_step_stride must be 0 or at least one snapshot of this call's shots, and needs q_write");
     FWI_CHECK_ARG(!b->q_read || b->image, "image required with q_read");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (d->nsteps == 0) return FWI_OK;
@@ -1219,7 +1221,7 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     // ---- small grids: the whole time loop as one cluster-resident kernel (acoustic_small.cu) ----
     const int small_on = env_int("FWI_B200_SMALL", 1);      // read per call: tests switch paths in-process
     static const int small_cells = env_int("FWI_B200_SMALL_CELLS", 1500000);
-    if (small_on && !link && !getenv("FWI_B200_TRACE") && d->chunk_rows == 0 && (mode != 2 || d->adjoint) &&
+    if (small_on && !link && !getenv("FWI_B200_TRACE") && d->chunk_rows == 0 && (mode != 2 || d->adjoint) && b->q_step_stride == 0 &&
         (int64_t)d->n_shots * d->nzp * d->nyp <= small_cells) {
         fwi::SmallParams sp = {};
         sp.nzp = d->nzp; sp.nyp = d->nyp; sp.pitch = g.pitch; sp.col0 = g.col0; sp.h = h; sp.pw = d->pml_width;
@@ -1393,7 +1395,7 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
         const Table &T = table_of(m);
         p.segs = T.d_segs; p.unit_start = T.d_units; p.n_units = T.n_units;
         const int blocks = T.blocks;
-        p.qw = b->q_write ? b->q_write + (size_t)n * fld : nullptr;
+        p.qw = b->q_write ? b->q_write + (size_t)n * (b->q_step_stride > 0 ? (size_t)b->q_step_stride : fld) : nullptr;
         p.qr = b->q_read ? b->q_read + (size_t)n * fld : nullptr;
         p.G = b->image;
         p.inj_amp = d->n_inj ? b->inj_amp + (size_t)n * d->n_shots * d->n_inj : nullptr;

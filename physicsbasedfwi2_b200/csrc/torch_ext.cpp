@@ -124,7 +124,7 @@ Tensor scalar_run(const Tensor &w, const Tensor &sigz, const Tensor &sigy, Tenso
                   const Tensor &inj_cell, const Tensor &inj_col, const Tensor &inj_amp, const Tensor &smp_cell,
                   const c10::optional<Tensor> &q_write, const c10::optional<Tensor> &q_read, const c10::optional<Tensor> &image,
                   const Tensor &meta, int64_t n_shots, int64_t nsteps, bool adjoint, int64_t order, int64_t pml, double dz,
-                  double dy, int64_t chunk_rows) {
+                  double dy, int64_t chunk_rows, int64_t q_step_stride) {
     TORCH_CHECK(w.is_cuda() && wave.is_cuda(), "scalar_run needs CUDA tensors: there is no CPU path");
     const double *m = meta.data_ptr<double>();
     c10::cuda::CUDAGuard guard(w.device());
@@ -150,6 +150,7 @@ Tensor scalar_run(const Tensor &w, const Tensor &sigz, const Tensor &sigy, Tenso
     b.q_read = q_read.has_value() ? fptr(*q_read) : nullptr;
     b.image = fptr_mut(im);
     b.unit_table = table.data_ptr();
+    b.q_step_stride = q_step_stride;
     check_rc(adjoint ? fwi_acoustic_backward(&d, &b, stream_of(w)) : fwi_acoustic_forward(&d, &b, stream_of(w)),
              adjoint ? "fwi_acoustic_backward" : "fwi_acoustic_forward");
     return smp_out;
@@ -218,7 +219,7 @@ TORCH_LIBRARY(b200fwi, m) {
           "bool loc_round, int c0, int c1) -> (Tensor, Tensor, Tensor, Tensor)");
     m.def("scalar_run(Tensor w, Tensor sigz, Tensor sigy, Tensor(a!) wave, Tensor inj_start, Tensor inj_cell, Tensor inj_col, "
           "Tensor inj_amp, Tensor smp_cell, Tensor(b!)? q_write, Tensor? q_read, Tensor(c!)? image, Tensor meta, int n_shots, "
-          "int nsteps, bool adjoint, int order, int pml, float dz, float dy, int chunk_rows) -> Tensor");
+          "int nsteps, bool adjoint, int order, int pml, float dz, float dy, int chunk_rows, int q_step_stride=0) -> Tensor");
     m.def("scalar_fold(Tensor image, Tensor? gs, Tensor? amp, Tensor src_cell, Tensor v, Tensor meta, int n_shots, int order, "
           "int pml, float dz, float dy) -> Tensor");
     m.def("flag_begin(Tensor bad) -> Tensor");

@@ -171,3 +171,29 @@ def test_paired_imaging_is_bit_identical_to_one_imaging_per_step(cuda_lib, nt, m
         outs.append((vg.grad.clone(), sg.grad.clone()))
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
     assert float(outs[0][0].abs().max()) > 0
+
+
+def test_forward_shot_groups_do_not_change_results(cuda_lib, monkeypatch):
+    """Large grids run the forward time loop per group of shots (wavefields L2-resident) into the snapshot array of all
+    shots (q_step_stride of the C ABI); the adjoint runs once over all of them.  Same kernels per shot: same bits."""
+    from physicsbasedfwi2_b200.scalar import Propagator
+    monkeypatch.setenv("FWI_B200_SMALL", "0")
+    c = dict(CASES[3], S=5)
+    v = K.layered_model(c["nz"], c["ny"], seed=1)
+    x_s, x_r = K.survey(c["nz"], c["ny"], c["dx"], c["S"], c["R"], c["Ns"], seed=2, scattered=True)
+    x_s[3] = x_s[1]
+    src = K.ricker(c["f"], c["nt"], c["dt"], 1.0 / c["f"]).reshape(-1, 1, 1).repeat(1, c["S"], c["Ns"]).contiguous()
+    src = src * (1.0 + 0.1 * torch.arange(c["S"]).reshape(1, -1, 1))
+    grad_rec = torch.randn(c["nt"], c["S"], c["R"], generator=torch.Generator().manual_seed(3))
+    dev = torch.device("cuda:0")
+    outs = []
+    for fwd_shots in ("0", "2", "1"):
+        monkeypatch.setenv("FWI_B200_FWD_SHOTS", fwd_shots)
+        vg = v.to(dev).requires_grad_(True)
+        sg = src.to(dev).requires_grad_(True)
+        rec = Propagator({"vp": vg}, c["dx"], pml_width=c["pml"], accuracy=c["order"])(sg, x_s.to(dev), x_r.to(dev), c["dt"])
+        (rec * grad_rec.to(dev)).sum().backward()
+        outs.append((rec.detach().clone(), vg.grad.clone(), sg.grad.clone()))
+    for o in outs[1:]:
+        for a, b in zip(outs[0], o):
+            assert torch.equal(a, b)
