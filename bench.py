@@ -746,8 +746,8 @@ def run_gpu(args, w, dev, rank, world, local):
         tot_bytes = sum(t["bytes"] for t in agg.values())
         ach = tot_bytes / (tot_ms * 1e-3) / 1e9
         kname = ("elastic step (f1 + f2 forward, b2 + b1 fused adjoint; one time step = one 'launch')"
-                 if elastic else "acoustic_step_kernel (forward MODE 1 + adjoint MODE 2" +
-                 (" + forward-only MODE 0 of the checkpoint pass)" if "acoustic_fwd0" in agg else " pair)"))
+                 if elastic else "acoustic_step_kernel (forward: MODE 1 per L2-sized shot group; adjoint: MODE 0 advance-only + MODE 3 "
+                 "paired-imaging launches" + (" + forward-only MODE 0 of the checkpoint pass)" if "acoustic_fwd0" in agg else ")"))
         roof = {"bound": "hbm", "kernel": kname, "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(ach / peak, 4), "algorithmic_frac": round(ach / peak, 4), "dram_frac": None,
                 "traffic": None, "peak_source": peak_src,
@@ -770,17 +770,23 @@ def run_gpu(args, w, dev, rank, world, local):
         if tr:
             roof["traffic"] = tr
             fwd_k, adj_k = ("elastic_fwd", "elastic_adj") if elastic else ("acoustic_fwd", "acoustic_adj")
-            s_ref = float(tr.get("shots_per_launch", 6 if not elastic else 5))
             if fwd_k in agg and adj_k in agg and len(agg) == 2:
-                # scale the captured bytes per launch to the launches timed here by their shot counts
-                dram = sum(tr[k2] * agg[k]["cell_updates"] / (cells * s_ref / div)
-                           for k, k2 in ((fwd_k, "forward_bytes_per_launch"), (adj_k, "adjoint_bytes_per_launch")))
+                # measured DRAM bytes per cell-update of each pass (one ncu capture per kernel) x the cell-updates timed here
+                if "forward_bytes_per_cell_update" in tr:
+                    bf_m, ba_m = tr["forward_bytes_per_cell_update"], tr["adjoint_bytes_per_cell_update"]
+                else:
+                    s_ref = float(tr.get("shots_per_launch", 5 if elastic else 6))
+                    bf_m = tr["forward_bytes_per_launch"] / (cells * s_ref)
+                    ba_m = tr["adjoint_bytes_per_launch"] / (cells * s_ref)
+                dram = bf_m * agg[fwd_k]["cell_updates"] + ba_m * agg[adj_k]["cell_updates"]
                 roof["dram_frac"] = round(dram / (tot_ms * 1e-3) / 1e9 / peak, 4)
         cfg = bench_config(w, cap, world, args.workload)
         cfg.update(shots_per_gpu_per_step=n_rank, launches_per_gpu_per_step=[hi - lo for lo, hi in batches],
                    shots_per_step=shots_step, first_shot_of_rank0=first,
-                   survey=("whole 256-shot survey sharded over the ranks, one allreduce" if scaling == "strong" and not slabs
-                           else f"{n_rank} shots per GPU per step (the per-GPU share of the survey on 8 GPUs), one allreduce per step"))
+                   survey=("every rank works on the same shots, one column slab each" if slabs else
+                           "whole survey sharded over the ranks, one allreduce" if scaling == "strong" else
+                           f"{n_rank} shots per GPU per step, one allreduce per step"
+                           + (" (the per-GPU share of the 256-shot survey on 8 GPUs)" if args.workload == "c2" and n_rank == total // 8 else "")))
         line = {"metric": "FWI gradient Gcell-updates/s (fwd+adjoint)", "value": round(value, 3),
                 "unit": "Gcell-updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": scaling,

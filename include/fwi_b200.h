@@ -207,6 +207,9 @@ typedef struct fwi_elastic_desc {
     double dz, dy, dt;
     int32_t source_kind;      /* 0: explosive (sxx, szz += dt s; DENISE QUELLTYPB 1), 1: vertical force (vz += dt bz s;
                                  QUELLTYPB 2, models/networks.py:10452), 2: horizontal force (vy += dt by s) */
+    int32_t free_surface;     /* 1: stress-imaging free surface at the first model row (row pml_width + order/2 of the padded
+                                 grid) instead of a top C-PML (DENISE FREE_SURF = 1, models/networks.py:9811): szz = 0 there,
+                                 szz / syz antisymmetric about it, nothing above it is updated */
     int32_t adj_parity;       /* backward in segments (wavefield checkpointing): number of adjoint steps already taken
                                  on this wave / scratch pair, modulo 2 (the memory variables ping-pong between them) */
 } fwi_elastic_desc;

@@ -120,12 +120,16 @@ def _dm(f, dim, h, c, inv_d):
 
 def elastic_forward(vp, vs, rho, dx, source_amplitudes, x_s, x_r, dt, *, order: int = 4, pml_width: int = 10,
                     vpmax: Optional[float] = None, pml_freq: float = 25.0, loc_mode: str = "trunc",
-                    source: str = "explosive"):
+                    source: str = "explosive", free_surface: bool = False):
     """Differentiable forward model (vp, vs, rho, source_amplitudes) -> [2, nt, S, R] (vy, vz).
     source: 'explosive' (sxx, szz += dt s; DENISE QUELLTYPB 1, the reference's default), 'fz' (vertical force:
     vz += dt bz s; QUELLTYPB 2, models/networks.py:10452) or 'fy' (horizontal force: vy += dt by s)."""
     if source not in ("explosive", "fz", "fy"):
         raise RuntimeError(f"unknown source kind {source!r}")
+    # free_surface: stress-imaging free surface at the first model row (DENISE FREE_SURF = 1, models/networks.py:9811;
+    # Levander 1988): szz = 0 on that row, szz and syz antisymmetric about it (the derivatives of F1 read mirrored values
+    # above it), the sxx update of the surface row uses l2m - lam^2 / l2m (szz = 0 eliminates e2), nothing above the
+    # surface is updated (velocities there stay zero).  Replaces the top C-PML.
     dtype = vp.dtype
     dz, dy = _pair(dx)
     nz, ny = vp.shape
@@ -163,18 +167,39 @@ def elastic_forward(vp, vs, rho, dx, source_amplitudes, x_s, x_r, dt, *, order: 
     pad4 = (h, h, h, h)
     l2m_i, lam_i, mu_i, by_i, bz_i = l2m[I], lam[I], mu_yz[I], by[I], bz[I]
     EI = (Ellipsis,) + I
+    rf = P - h                                    # surface row inside the computational region (free_surface)
+    if free_surface:
+        live = torch.zeros(nzp - 2 * h, 1, dtype=dtype)
+        live[rf:] = 1.0                           # rows at and below the surface
+        surf = torch.zeros(nzp - 2 * h, 1, dtype=dtype)
+        surf[rf] = 1.0
+        below = live - surf
+        c_surf = l2m_i - lam_i * lam_i / l2m_i
+
+    def mirrored(szz_, syz_):
+        """Copies of szz / syz with the h rows above the surface filled antisymmetrically."""
+        a, b = szz_.clone(), syz_.clone()
+        for m in range(1, h + 1):
+            a[:, P - m] = -szz_[:, P + m]
+            b[:, P - m] = -syz_[:, P + m - 1]
+        return a, b
+
     rec_y, rec_z = [], []
     for n in range(nti):
         if n % ratio == 0:
             rec_y.append(vy.reshape(S, -1).gather(1, r_lin))
             rec_z.append(vz.reshape(S, -1).gather(1, r_lin))
         # F1: velocities from stresses
+        szz_e, syz_e = mirrored(szz, syz) if free_surface else (szz, syz)
         d1 = _dp(sxx, 1, h, c, 1.0 / dy); psi[0] = byh * psi[0] + ayh * d1
-        d2 = _dm(syz, 0, h, c, 1.0 / dz); psi[1] = bzp * psi[1] + az * d2
+        d2 = _dm(syz_e, 0, h, c, 1.0 / dz); psi[1] = bzp * psi[1] + az * d2
         fy = (d1 + psi[0]) + (d2 + psi[1])
         d3 = _dm(syz, 1, h, c, 1.0 / dy); psi[2] = byp * psi[2] + ay * d3
-        d4 = _dp(szz, 0, h, c, 1.0 / dz); psi[3] = bzh * psi[3] + azh * d4
+        d4 = _dp(szz_e, 0, h, c, 1.0 / dz); psi[3] = bzh * psi[3] + azh * d4
         fz = (d3 + psi[2]) + (d4 + psi[3])
+        if free_surface:
+            psi[0], psi[1], psi[2], psi[3] = (live * q for q in psi[:4])
+            fy, fz = live * fy, live * fz
         vy = vy + F.pad((dti * by_i) * fy, pad4)
         vz = vz + F.pad((dti * bz_i) * fz, pad4)
         # F2: stresses from the new velocities
@@ -184,9 +209,15 @@ def elastic_forward(vp, vs, rho, dx, source_amplitudes, x_s, x_r, dt, *, order: 
         d7 = _dp(vy, 0, h, c, 1.0 / dz); psi[6] = bzh * psi[6] + azh * d7
         d8 = _dp(vz, 1, h, c, 1.0 / dy); psi[7] = byh * psi[7] + ayh * d8
         e3 = (d7 + psi[6]) + (d8 + psi[7])
-        sxx = sxx + F.pad(dti * (l2m_i * e1 + lam_i * e2), pad4)
-        szz = szz + F.pad(dti * (lam_i * e1 + l2m_i * e2), pad4)
-        syz = syz + F.pad((dti * mu_i) * e3, pad4)
+        if free_surface:
+            psi[4], psi[5], psi[6], psi[7] = (live * q for q in psi[4:])
+            sxx = sxx + F.pad(below * (dti * (l2m_i * e1 + lam_i * e2)) + surf * (dti * (c_surf * e1)), pad4)
+            szz = szz + F.pad(below * (dti * (lam_i * e1 + l2m_i * e2)), pad4)
+            syz = syz + F.pad(live * ((dti * mu_i) * e3), pad4)
+        else:
+            sxx = sxx + F.pad(dti * (l2m_i * e1 + lam_i * e2), pad4)
+            szz = szz + F.pad(dti * (lam_i * e1 + l2m_i * e2), pad4)
+            syz = syz + F.pad((dti * mu_i) * e3, pad4)
         if source == "explosive":
             inj = torch.zeros(S, nzp * nyp, dtype=dtype).scatter_add(1, s_lin, dti * amp[n]).reshape(S, nzp, nyp)
             sxx, szz = sxx + inj, szz + inj

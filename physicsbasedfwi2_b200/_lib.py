@@ -76,7 +76,7 @@ class ElasticDesc(C.Structure):
     _fields_ = [("nzp", C.c_int32), ("nyp", C.c_int32), ("order", C.c_int32), ("pml_width", C.c_int32),
                 ("n_shots", C.c_int32), ("nsteps", C.c_int32), ("n_src", C.c_int32), ("n_rec", C.c_int32),
                 ("dz", C.c_double), ("dy", C.c_double), ("dt", C.c_double), ("source_kind", C.c_int32),
-                ("adj_parity", C.c_int32)]
+                ("free_surface", C.c_int32), ("adj_parity", C.c_int32)]
 
 
 class ElasticBuffers(C.Structure):

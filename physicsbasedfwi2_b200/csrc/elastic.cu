@@ -35,6 +35,7 @@ struct EParams {
     float *grad;                // [5][S][cells]: l2m lam mu by bz images
     float *psi_in[8], *psi_out[8];  // fused kernels: memory variables read / written this step (ping-pong)
     float *fo[5];                   // fused forward: vy vz sxx szz syz written this step (p.f[0..4] are read)
+    int fs_row;                     // free surface: first model row (stress imaging there, nothing above it is updated); 0 = none
 };
 
 // Every kernel of the time loop is launched with programmatic stream serialization: its blocks
@@ -91,11 +92,30 @@ __device__ __forceinline__ float dminus(const float *f, long long i, long long s
     return s;
 }
 
+// z-derivatives of szz / syz next to a free surface at row fs (stress imaging: the values above the surface are minus
+// their mirror images; szz mirrors about the row itself, syz - half a cell lower - about the surface between its rows)
+template <int H>
+__device__ __forceinline__ float dplus_z_szz_fs(const float *f, int i, int j, int nyp, int fs, const float *c) {
+    auto at = [&](int r) { return r >= fs ? __ldg(f + (long long)r * nyp + j) : -__ldg(f + (long long)(2 * fs - r) * nyp + j); };
+    float s = c[0] * (at(i + 1) - at(i));
+#pragma unroll
+    for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (at(i + k) - at(i - (k - 1)));
+    return s;
+}
+template <int H>
+__device__ __forceinline__ float dminus_z_syz_fs(const float *f, int i, int j, int nyp, int fs, const float *c) {
+    auto at = [&](int r) { return r >= fs ? __ldg(f + (long long)r * nyp + j) : -__ldg(f + (long long)(2 * fs - r - 1) * nyp + j); };
+    float s = c[0] * (at(i) - at(i - 1));
+#pragma unroll
+    for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (at(i + (k - 1)) - at(i - k));
+    return s;
+}
+
 #define ELASTIC_CELL()                                                              \
     const int j = blockIdx.x * blockDim.x + threadIdx.x + p.h;                      \
     const int i = blockIdx.y * blockDim.y + threadIdx.y + p.h;                      \
     const int s = blockIdx.z;                                                       \
-    if (i >= p.nzp - p.h || j >= p.nyp - p.h) return;                               \
+    if (i >= p.nzp - p.h || j >= p.nyp - p.h || i < p.fs_row) return;               \
     const long long c0 = (long long)i * p.nyp + j;                                  \
     const long long o = (long long)s * p.cells + c0;                                \
     const long long fs = (long long)p.S * p.cells;                                  \
@@ -120,8 +140,11 @@ __global__ void __launch_bounds__(256) elastic_f1(const EParams p) {
     ELASTIC_CELL();
     const float *sxx = p.f[SXX] + (long long)s * p.cells, *szz = p.f[SZZ] + (long long)s * p.cells,
                 *syz = p.f[SYZ] + (long long)s * p.cells;
-    float d1 = dplus<H>(sxx, c0, 1, p.cy), d2 = dminus<H>(syz, c0, p.nyp, p.cz);
-    float d3 = dminus<H>(syz, c0, 1, p.cy), d4 = dplus<H>(szz, c0, p.nyp, p.cz);
+    const bool near_fs = p.fs_row && i < p.fs_row + H;
+    float d1 = dplus<H>(sxx, c0, 1, p.cy);
+    float d2 = near_fs ? dminus_z_syz_fs<H>(syz, i, j, p.nyp, p.fs_row, p.cz) : dminus<H>(syz, c0, p.nyp, p.cz);
+    float d3 = dminus<H>(syz, c0, 1, p.cy);
+    float d4 = near_fs ? dplus_z_szz_fs<H>(szz, i, j, p.nyp, p.fs_row, p.cz) : dplus<H>(szz, c0, p.nyp, p.cz);
     if (ypml) {
         float q0 = BYH(j) * p.f[PSI + 0][o] + AYH(j) * d1; p.f[PSI + 0][o] = q0; d1 = d1 + q0;
         float q2 = BY(j) * p.f[PSI + 2][o] + AY(j) * d3; p.f[PSI + 2][o] = q2; d3 = d3 + q2;
@@ -155,8 +178,13 @@ __global__ void __launch_bounds__(256) elastic_f2(const EParams p) {
     }
     const float e1 = d5, e2 = d6, e3 = d7 + d8;
     const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
-    p.f[SXX][o] = p.f[SXX][o] + p.dt * (l2m * e1 + lam * e2);
-    p.f[SZZ][o] = p.f[SZZ][o] + p.dt * (lam * e1 + l2m * e2);
+    if (p.fs_row && i == p.fs_row) {
+        // on the free surface szz stays zero, which removes e2 from the sxx update: (l2m - lam^2 / l2m) e1
+        p.f[SXX][o] = p.f[SXX][o] + p.dt * ((l2m - lam * lam / l2m) * e1);
+    } else {
+        p.f[SXX][o] = p.f[SXX][o] + p.dt * (l2m * e1 + lam * e2);
+        p.f[SZZ][o] = p.f[SZZ][o] + p.dt * (lam * e1 + l2m * e2);
+    }
     p.f[SYZ][o] = p.f[SYZ][o] + (p.dt * mu) * e3;
     if (SAVE) {
         __stcs(p.snap + 2 * fs + o, e1);
@@ -266,7 +294,8 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b2_fuse
     static_assert((kTX * kTZ) % NT == 0, "tile must be a multiple of the CTA size");
     __shared__ float Y[4][SZ * SX];
     const int s = blockIdx.z;
-    const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + p.h;     // first own cell
+    const int zs = p.fs_row ? p.fs_row : p.h;                               // first computational row
+    const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + zs;      // first own cell
     const long long fs = (long long)p.S * p.cells, so = (long long)s * p.cells;
     pdl_wait();
     // stage 1: the fields Y the transposed differences act on, for the tile and its halo (loads only,
@@ -278,13 +307,18 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b2_fuse
         const int lz = t / SX, lx = t - lz * SX;
         const int i = i0 - H + lz, j = j0 - H + lx;
         float y1 = 0.f, y2 = 0.f, y3 = 0.f, y4 = 0.f;
-        if (i >= p.h && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h) {
+        if (i >= zs && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h) {
             const long long c0 = (long long)i * p.nyp + j, o = so + c0;
             const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1);
             const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1);
             const float asxx = __ldg(p.f[SXX] + o), aszz = __ldg(p.f[SZZ] + o), asyz = __ldg(p.f[SYZ] + o);
             const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
-            const float ae1 = p.dt * (l2m * asxx + lam * aszz), ae2 = p.dt * (lam * asxx + l2m * aszz), ae3 = (p.dt * mu) * asyz;
+            float ae1 = p.dt * (l2m * asxx + lam * aszz), ae2 = p.dt * (lam * asxx + l2m * aszz);
+            const float ae3 = (p.dt * mu) * asyz;
+            if (p.fs_row && i == p.fs_row) {          // free-surface row: sxx += dt (l2m - lam^2 / l2m) e1, szz is not updated
+                ae1 = p.dt * ((l2m - lam * lam / l2m) * asxx);
+                ae2 = 0.f;
+            }
             y1 = ae1; y2 = ae2; y3 = ae3; y4 = ae3;
             if (ypml || zpml) {
                 const bool own = lz >= H && lz < H + kTZ && lx >= H && lx < H + kTX;
@@ -326,8 +360,17 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b2_fuse
         const int t = threadIdx.x + q * NT;
         const int tz = t / kTX, tx = t - tz * kTX;
         const int l = (tz + H) * SX + tx + H;
-        p.grad[o] = g0[q] + p.dt * (sx[q] * e1[q] + sz[q] * e2[q]);
-        p.grad[fs + o] = g1[q] + p.dt * (sx[q] * e2[q] + sz[q] * e1[q]);
+        if (p.fs_row && i0 + tz == p.fs_row) {
+            // images of the free-surface row: d/d l2m and d/d lam of (l2m - lam^2 / l2m) e1
+            const long long c0 = o - so;
+            const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0);
+            const float r = lam / l2m;
+            p.grad[o] = g0[q] + p.dt * (sx[q] * e1[q]) * (1.0f + r * r);
+            p.grad[fs + o] = g1[q] - p.dt * (sx[q] * e1[q]) * (2.0f * r);
+        } else {
+            p.grad[o] = g0[q] + p.dt * (sx[q] * e1[q] + sz[q] * e2[q]);
+            p.grad[fs + o] = g1[q] + p.dt * (sx[q] * e2[q] + sz[q] * e1[q]);
+        }
         p.grad[2 * fs + o] = g2[q] + p.dt * (sy[q] * e3[q]);
         p.f[VY][o] = vy[q] - (sm_dplus<H>(&Y[0][l], 1, p.cy) + sm_dminus<H>(&Y[2][l], SX, p.cz));
         p.f[VZ][o] = vz[q] - (sm_dplus<H>(&Y[1][l], SX, p.cz) + sm_dminus<H>(&Y[3][l], 1, p.cy));
@@ -340,7 +383,8 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b1_fuse
     constexpr int N1 = (SX * SZ + NT - 1) / NT, N2 = (kTX * kTZ) / NT;
     __shared__ float Y[4][SZ * SX];
     const int s = blockIdx.z;
-    const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + p.h;
+    const int zs = p.fs_row ? p.fs_row : p.h;
+    const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + zs;
     const long long fs = (long long)p.S * p.cells, so = (long long)s * p.cells;
     pdl_wait();
 #pragma unroll
@@ -350,7 +394,7 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b1_fuse
         const int lz = t / SX, lx = t - lz * SX;
         const int i = i0 - H + lz, j = j0 - H + lx;
         float y1 = 0.f, y2 = 0.f, y3 = 0.f, y4 = 0.f;
-        if (i >= p.h && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h) {
+        if (i >= zs && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h) {
             const long long c0 = (long long)i * p.nyp + j, o = so + c0;
             const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1);
             const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1);
@@ -398,9 +442,32 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b1_fuse
         const int l = (tz + H) * SX + tx + H;
         p.grad[3 * fs + o] = g3[q] + p.dt * (vy[q] * fy[q]);
         p.grad[4 * fs + o] = g4[q] + p.dt * (vz[q] * fz[q]);
+        float nsy = sy[q] - (sm_dplus<H>(&Y[1][l], SX, p.cz) + sm_dplus<H>(&Y[2][l], 1, p.cy));
+        float nsz = sz[q] - sm_dminus<H>(&Y[3][l], SX, p.cz);
+        if (p.fs_row && blockIdx.y == 0 && tz <= H) {
+            // free surface: F1 read the stresses above the surface as minus their mirror images, so a row next to the
+            // surface also receives, with the opposite sign, what the transposed differences deliver to its mirror row
+            // (the Y of rows above the surface are zero: those rows are not part of the system)
+            const int col = tx + H;
+            auto y_at = [&](const int f, const int lz) { return lz >= H ? Y[f][lz * SX + col] : 0.f; };   // smem row lz <-> grid row i0 - H + lz
+            const int gz = H - tz - 1;                      // smem row of the ghost row 2 fs - r - 1 of syz (r = fs + tz)
+            if (gz >= 0) {
+                float t = p.cz[0] * (y_at(1, gz + 1) - y_at(1, gz));
+#pragma unroll
+                for (int k = 2; k <= H; ++k) t = t + p.cz[k - 1] * (y_at(1, gz + k) - y_at(1, gz - (k - 1)));
+                nsy = nsy + t;                              // + (D+z Y2)[ghost]
+            }
+            const int hz = H - tz;                          // smem row of the ghost row 2 fs - r of szz
+            if (tz >= 1 && hz >= 0) {
+                float t = p.cz[0] * (y_at(3, hz) - y_at(3, hz - 1));
+#pragma unroll
+                for (int k = 2; k <= H; ++k) t = t + p.cz[k - 1] * (y_at(3, hz + (k - 1)) - y_at(3, hz - k));
+                nsz = nsz + t;                              // + (D-z Y4)[ghost]
+            }
+        }
         p.f[SXX][o] = sx[q] - sm_dminus<H>(&Y[0][l], 1, p.cy);
-        p.f[SYZ][o] = sy[q] - (sm_dplus<H>(&Y[1][l], SX, p.cz) + sm_dplus<H>(&Y[2][l], 1, p.cy));
-        p.f[SZZ][o] = sz[q] - sm_dminus<H>(&Y[3][l], SX, p.cz);
+        p.f[SYZ][o] = nsy;
+        p.f[SZZ][o] = nsz;
     }
 }
 
@@ -646,6 +713,7 @@ void fill(EParams &p, const fwi_elastic_desc *d, const fwi_elastic_buffers *b) {
     const long long fld = (long long)d->n_shots * p.cells;
     for (int k = 0; k < 13; ++k) p.f[k] = b->wave + k * fld;
     p.scratch = b->scratch; p.grad = b->grad; p.snap = nullptr;
+    p.fs_row = d->free_surface ? d->pml_width + d->order / 2 : 0;
 }
 
 // thread-block shape of the stencil kernels (x along y, the fast axis); tuning knobs for scripts/
@@ -713,6 +781,7 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
     // It moves 80 B per cell-update instead of ~100 B, but its three barrier-separated stages measured
     // 57.6 us per step on C3 against 42.4 us for the two kernels, so the two-kernel form stays the default.
     const bool fused = getenv("FWI_B200_EL_FUSED_FWD") && atoi(getenv("FWI_B200_EL_FUSED_FWD")) == 1;
+    FWI_CHECK_ARG(!(fused && d->free_surface), "the opt-in fused forward step (FWI_B200_EL_FUSED_FWD=1) has no free surface");
     const dim3 fgrid((d->nyp - 2 * p.h + kTX - 1) / kTX, (d->nzp - 2 * p.h + kTZ - 1) / kTZ, d->n_shots);
     float *setA[9], *setB[9];
     for (int k = 0; k < 5; ++k) { setA[k] = b->wave + k * fld; setB[k] = b->wave + (13 + k) * fld; }
@@ -800,7 +869,9 @@ extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic
     static const bool fused = !(getenv("FWI_B200_EL_FUSED") && atoi(getenv("FWI_B200_EL_FUSED")) == 0);
     static const int fnt = getenv("FWI_B200_EL_NT") ? atoi(getenv("FWI_B200_EL_NT")) : 512;
     const dim3 fblock(fnt == 256 || fnt == 1024 ? fnt : 512);
-    const dim3 fgrid((d->nyp - 2 * p.h + kTX - 1) / kTX, (d->nzp - 2 * p.h + kTZ - 1) / kTZ, d->n_shots);
+    FWI_CHECK_ARG(fused || !d->free_surface, "the four-kernel adjoint (FWI_B200_EL_FUSED=0) has no free surface");
+    const int zs = p.fs_row ? p.fs_row : p.h;
+    const dim3 fgrid((d->nyp - 2 * p.h + kTX - 1) / kTX, (d->nzp - p.h - zs + kTZ - 1) / kTZ, d->n_shots);
     FWI_CHECK_ARG(d->source_kind >= 0 && d->source_kind <= 2, "source_kind must be 0, 1 or 2");
     FWI_CHECK_ARG(d->source_kind == 0 || d->n_src == 0 || (b->src_amp && b->src_link),
                   "force sources: the adjoint pass needs src_amp and src_link (image term of the buoyancy)");

@@ -80,7 +80,7 @@ _SOURCE_KINDS = {"explosive": 0, "fz": 1, "fy": 2}
 class _ElasticFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, vp, vs, rho, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, pml_freq, loc_mode,
-                source="explosive", checkpoint_every=0):
+                source="explosive", checkpoint_every=0, free_surface=False):
         for name, t in (("vp", vp), ("vs", vs), ("rho", rho)):
             if t.dim() != 2 or t.shape != vp.shape:
                 raise RuntimeError(f"model['{name}'] must be 2-D with the shape of model['vp']")
@@ -149,8 +149,11 @@ class _ElasticFunction(torch.autograd.Function):
                 f"snapshots (+ {state_bytes / 2**30:.1f} GiB of checkpoints); {free / 2**30:.1f} GiB are free.  Use fewer shots per "
                 f"call or checkpoint_every=K (K snapshots + one state per K steps; one extra forward pass).")
 
+        if free_surface and kind == 0 and bool((s_cell // nyp == P).any()):
+            raise RuntimeError("an explosive source on the free surface row would break szz = 0 there: put it at least one cell down")
+
         def desc_for(n, parity=0):
-            return _lib.ElasticDesc(nzp, nyp, order, pw, S, n, Ns, R, dz, dy, dti, kind, parity)
+            return _lib.ElasticDesc(nzp, nyp, order, pw, S, n, Ns, R, dz, dy, dti, kind, 1 if free_surface else 0, parity)
 
         n_wave = int(L.fwi_elastic_wave_floats(C.byref(desc_for(nti))))
         wave = torch.zeros(n_wave, dtype=torch.float32, device=dev)
@@ -249,7 +252,7 @@ class _ElasticFunction(torch.autograd.Function):
             gs = gs.to(ctx.src_like.device, ctx.src_like.dtype)
         ctx.saved = ctx.run_forward = ctx.desc_for = ctx.amp = None
         return (gvp if ctx.needs_input_grad[0] else None, gvs if ctx.needs_input_grad[1] else None,
-                grho if ctx.needs_input_grad[2] else None, gs) + (None,) * 11
+                grho if ctx.needs_input_grad[2] else None, gs) + (None,) * 12
 
 
 class Propagator(torch.nn.Module):
@@ -264,10 +267,13 @@ class Propagator(torch.nn.Module):
     (QUELLTYPB 2 / 3; the reference sets 2 at models/networks.py:10452).  ``checkpoint_every`` = K: wavefield
     checkpointing - the 13 live fields every K inner steps instead of five snapshot fields every step, the backward
     pass recomputes one K-step segment at a time (BASELINE config 3 at k = 1 is 28 GB of snapshots per shot).
+    ``free_surface``: stress-imaging free surface at the first model row instead of a top C-PML (the reference runs
+    DENISE with FREE_SURF = 1, models/networks.py:9811).
     """
 
     def __init__(self, model: dict, dx, pml_width=None, survey_pad=None, vpmax=None, *, accuracy: int = 4,
-                 pml_freq: float = 25.0, loc_mode: str = "trunc", source: str = "explosive", checkpoint_every: int = 0):
+                 pml_freq: float = 25.0, loc_mode: str = "trunc", source: str = "explosive", checkpoint_every: int = 0,
+                 free_surface: bool = False):
         super().__init__()
         if not isinstance(model, dict) or not {"vp", "vs", "rho"} <= set(model):
             raise RuntimeError("model must be a dict with keys 'vp', 'vs' and 'rho'")
@@ -291,9 +297,11 @@ class Propagator(torch.nn.Module):
         if checkpoint_every < 0:
             raise RuntimeError("checkpoint_every must be >= 0")
         self.checkpoint_every = int(checkpoint_every)
+        self.free_surface = bool(free_surface)
 
     def forward(self, source_amplitudes, source_locations, receiver_locations, dt):
         m = self.model
         return _ElasticFunction.apply(m["vp"], m["vs"], m["rho"], source_amplitudes, source_locations,
                                       receiver_locations, float(dt), self.dx, self.accuracy, self.pml_width,
-                                      self.vpmax, self.pml_freq, self.loc_mode, self.source, self.checkpoint_every)
+                                      self.vpmax, self.pml_freq, self.loc_mode, self.source, self.checkpoint_every,
+                                      self.free_surface)

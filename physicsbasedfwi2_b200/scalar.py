@@ -27,25 +27,6 @@ def _ptr(t: Optional[torch.Tensor]):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
-_PROFILE_CACHE = {}
-
-
-def _pml_profiles(nzp, nyp_global, h, pw, dz, dy, vmax, pitch, col0, c0, c1, dev):
-    """Device copies of the PML profiles (sigz [nzp], sigy [pitch] in device columns).  They depend only on
-    the arguments, and the reference rebuilds its Propagator every iteration with the same ones
-    (models/networks.py:5449): computed and uploaded once per distinct key, not once per call."""
-    key = (nzp, nyp_global, h, pw, dz, dy, vmax, pitch, col0, c0, c1, str(dev))
-    hit = _PROFILE_CACHE.get(key)
-    if hit is None:
-        sz = H.sigma_profile(nzp, h, pw, dz, vmax).float()
-        sy = torch.zeros(pitch, dtype=torch.float32)
-        sy[col0:col0 + (c1 - c0)] = H.sigma_profile(nyp_global, h, pw, dy, vmax).float()[c0:c1]
-        if len(_PROFILE_CACHE) >= 64:
-            _PROFILE_CACHE.clear()
-        hit = _PROFILE_CACHE[key] = (sz.to(dev), sy.to(dev))
-    return hit
-
-
 class _Plan:
     """Everything about one call that does not depend on the direction of time."""
 
@@ -83,18 +64,19 @@ class _Plan:
         self.pitch, self.col0 = int(lay.pitch), int(lay.col0)
         self.stride = int(lay.shot_stride)
 
-        vp = F.pad(v.detach()[None, None], (self.P,) * 4, mode="replicate")[0, 0]
-        self.v_pad_global = vp
-        vp = vp[:, self.c0:self.c1]
-        self.v_pad = vp
-        # dt^2 rounded the way an fp32 tensor product would (no host->device scalar copy: that copy is a
-        # synchronisation point and would stop the host from preparing this call under the previous one's kernels)
-        dti32 = np.float32(self.dti)
-        dt2 = float(np.float32(dti32 * dti32))
-        self.w = torch.zeros(self.nzp, self.pitch, dtype=torch.float32, device=self.dev)
-        self.w[:, self.col0:self.col0 + self.nyp] = (vp * vp) * dt2
-        self.sigz, self.sigy = _pml_profiles(self.nzp, self.nyp_global, self.h, self.pw, self.dz, self.dy, self.vmax,
-                                             self.pitch, self.col0, self.c0, self.c1, self.dev)
+        # padded copy of the model: the x-slab driver folds its gradient through the padding itself (slab.py)
+        self.v_pad_global = F.pad(v.detach()[None, None], (self.P,) * 4, mode="replicate")[0, 0]
+        self.v_pad = self.v_pad_global[:, self.c0:self.c1]
+        # w = v^2 dt^2 on the padded window and the PML profiles: one native kernel (csrc/host_kernels.cu), nothing cached
+        self.w = torch.empty(self.nzp, self.pitch, dtype=torch.float32, device=self.dev)
+        self.sigz = torch.empty(self.nzp, dtype=torch.float32, device=self.dev)
+        self.sigy = torch.empty(self.pitch, dtype=torch.float32, device=self.dev)
+        m = _lib.ModelDesc(self.nz, self.ny, self.order, self.pw, self.c0, self.c1, self.dz, self.dy, self.dti, self.vmax)
+        vc = v.detach().contiguous()
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.lib().fwi_acoustic_prepare_model(C.byref(m), _ptr(vc), _ptr(self.w), _ptr(self.sigz), _ptr(self.sigy),
+                                                             C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)),
+                       "fwi_acoustic_prepare_model")
         self.n_fields, self.n_images = int(lay.wave_fields), int(lay.n_images)
 
     def desc(self, nsteps, adjoint, n_inj, n_smp) -> _lib.AcousticDesc:

@@ -214,7 +214,14 @@ class _SlabFunction(torch.autograd.Function):
         dev = plan.dev
         s_cell, _, _, bad_s = plan.points(x_s, "source", loc_mode)
         r_cell, _, _, bad_r = plan.points(x_r, "receiver", loc_mode)
-        if bool((bad_s | bad_r).item()):
+        bad = (bad_s | bad_r).reshape(1)
+        flag = None
+        if bad.is_cuda:
+            # read back through pinned memory AFTER this call's time loop is queued (as scalar._ScalarFunction does):
+            # the host does not wait for the planning kernels before it launches
+            from . import _lib as _L
+            flag = _L.ops().flag_begin(bad.to(torch.int32))
+        elif bool(bad.item()):
             raise RuntimeError("source/receiver location outside the model")
         s_col, r_col = plan.padded_columns(x_s, loc_mode), plan.padded_columns(x_r, loc_mode)
 
@@ -257,6 +264,8 @@ class _SlabFunction(torch.autograd.Function):
         rec = rec * r_own[None]
         if world > 1:
             dist.all_reduce(rec, op=dist.ReduceOp.SUM, group=group)
+        if flag is not None:
+            _L.ops().flag_end(flag)
         out = rec[::plan.ratio].contiguous() if plan.ratio > 1 else rec
         ctx.plan, ctx.geo, ctx.group, ctx.q = plan, geo, group, q
         ctx.comm = comm

@@ -155,16 +155,23 @@ if __name__ == "__main__":
             json.dump(cur, open(tj, "w"), indent=1)
         sys.exit(0)
     launches(tag)
-    t = {n: full(tag, n) for n in ("fwd_full", "adj_full")}
-    print(t)
+    # forward: one launch of a 3-shot group (MODE 1); adjoint: an advance-only launch (MODE 0) and the paired-imaging
+    # launch after it (MODE 3), 6 shots each - scripts/gpu_r02c.sh
+    tf = full(tag, "fwd_full")
+    ta = full_multi(tag, "adj_full", "C2 adjoint: advance-only launch (MODE 0) + paired-imaging launch (MODE 3), 6 shots")
+    print(tf, ta)
     for n in ("bench.log", "pytest_gpu.log", "smoke.log"):
         p = os.path.join(OUT, n)
         if os.path.exists(p):
             open(os.path.join(PROF, f"{tag}_{n}.txt"), "w").write(open(p).read())
-    if t["fwd_full"] and t["adj_full"]:
-        # dram bytes per launch of the forward + adjoint pair (what roofline.achieved is quoted over)
+    if tf and ta:
         tj = os.path.join(PROF, "traffic.json")
         cur = json.load(open(tj)) if os.path.exists(tj) else {}
-        cur["c2"] = {"forward_bytes_per_launch": t["fwd_full"], "adjoint_bytes_per_launch": t["adj_full"],
-                     "pair_bytes_per_launch": t["fwd_full"] + t["adj_full"], "source": f"profiles/{tag}_*_full.txt"}
+        cells = 751 * 2301
+        pair = sum(ta.values())
+        cur["c2"] = {"forward_bytes_per_launch": tf, "forward_shots_per_launch": 3,
+                     "adjoint_bytes_per_two_launches": pair, "adjoint_shots_per_launch": 6,
+                     "forward_bytes_per_cell_update": tf / (3 * cells), "adjoint_bytes_per_cell_update": pair / (2 * 6 * cells),
+                     "per_kernel": ta, "source": f"profiles/{tag}_*_full.txt"}
         json.dump(cur, open(tj, "w"), indent=1)
+    sys.exit(0)

@@ -148,3 +148,29 @@ def test_elastic_oversize_call_raises_a_sized_error(cuda_lib):
     prop = pkg.Propagator({"vp": v, "vs": v.detach() / 2, "rho": v.detach()}, 10.0)
     with pytest.raises(RuntimeError, match="GiB of snapshots.*checkpoint_every"):
         prop(torch.zeros(400000, 4, 1, device="cuda:0"), torch.zeros(4, 1, 2), torch.zeros(4, 3, 2), 1e-3)
+
+
+@pytest.mark.parametrize("order,source", [(4, "explosive"), (8, "fz"), (2, "explosive")])
+def test_free_surface_matches_oracle(cuda_lib, order, source):
+    """Stress-imaging free surface at the first model row (DENISE FREE_SURF = 1, models/networks.py:9811): traces and all
+    four gradients against oracle/elastic_ref.py (autograd), receivers on the surface, a source one cell below it."""
+    from oracle import elastic_ref as E
+    import physicsbasedfwi2_b200 as pkg
+    c = dict(CASES[0], order=order, nt=140)
+    vp, vs, rho, x_s, x_r, src, grad_rec = _inputs(c)
+    vs = vp / 1.732                                      # solid up to the surface
+    x_s[0, 0] = torch.tensor([c["dx"], 12 * c["dx"]])    # one cell below the surface
+    x_r[:, :3, 0] = 0.0                                  # three receivers on the surface
+    dev = torch.device("cuda:0")
+    leaves = [t.to(dev).requires_grad_(True) for t in (vp, vs, rho, src)]
+    prop = pkg.Propagator({"vp": leaves[0], "vs": leaves[1], "rho": leaves[2]}, c["dx"], pml_width=c["pml"],
+                          accuracy=order, source=source, free_surface=True)
+    rec = prop(leaves[3], x_s.to(dev), x_r.to(dev), c["dt"])
+    (rec * grad_rec.to(dev)).sum().backward()
+    o = E.elastic_gradient(vp, vs, rho, c["dx"], src, x_s, x_r, c["dt"], grad_rec, order=order, pml_width=c["pml"],
+                           source=source, free_surface=True)
+    o_pml = E.elastic_forward(vp, vs, rho, c["dx"], src, x_s, x_r, c["dt"], order=order, pml_width=c["pml"], source=source)
+    assert K.rel_l2(o[0], o_pml) > 0.1                   # the surface matters in this set-up
+    assert K.rel_l2(rec, o[0]) <= 1e-5, K.rel_l2(rec, o[0])
+    for name, got, want in zip(("vp", "vs", "rho", "src"), [t.grad for t in leaves], o[1:]):
+        assert K.rel_l2(got, want) <= 1e-4, (name, K.rel_l2(got, want))
