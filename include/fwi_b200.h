@@ -54,7 +54,13 @@ typedef struct fwi_acoustic_desc {
     int32_t n_smp;            /* sampling points per shot (receivers fwd / sources adj) */
     int32_t smp_div_a;        /* 1: sampled value divided by a (adjoint source gradient) */
     double dz, dy, dt;        /* grid spacings (m) and inner time step (s) */
+    int32_t flags;            /* FWI_FLAG_* */
+    int32_t reserved;
 } fwi_acoustic_desc;
+
+#define FWI_FLAG_NO_PDL 1     /* plain launches instead of programmatic dependent launches: for jobs that share the device with
+                                 other jobs (fwi_acoustic_run_multi) - a dependent launch made resident early would sit on SM
+                                 slots the other job's ready CTAs could use */
 
 /* Device memory layout chosen by the library for a descriptor (host POD, output). */
 typedef struct fwi_acoustic_layout {
@@ -107,6 +113,12 @@ int fwi_acoustic_plan_stats(const fwi_acoustic_desc *desc, int n_units, int64_t 
  * adjoint=0 replaces the time loop of deepwave's forward (models/networks.py:5464);
  * adjoint=1 with q_read/image replaces its backward (models/networks.py:5491). */
 int fwi_acoustic_run(const fwi_acoustic_desc *desc, const fwi_acoustic_buffers *buf, void *stream);
+
+/* Several independent time loops at once (e.g. the shot groups of one gradient), job j on streams[j]: their launches
+ * interleave on the device, so the ramp and tail of one job's step are covered by the other job's step.  Each job is what
+ * fwi_acoustic_run takes; the caller orders the streams against its own work. */
+int fwi_acoustic_run_multi(int32_t n_jobs, const fwi_acoustic_desc *const *descs, const fwi_acoustic_buffers *const *bufs,
+                           void *const *streams);
 
 /* ---- x-slab domain decomposition: ghost-zone exchange by peer stores over NVLink ---------- */
 /* One shot spread over the GPUs of a box (BASELINE config 4 variant; no reference

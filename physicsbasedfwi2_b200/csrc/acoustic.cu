@@ -29,6 +29,9 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
+#include <string>
+#include <thread>
 #include <type_traits>
 #include <vector>
 
@@ -1000,6 +1003,8 @@ struct Launcher {
     static constexpr size_t smem_bytes() { return (size_t)kNW * warp_smem_floats(MODE) * sizeof(float); }
     // resident CTAs per SM of this kernel on the current device (cached per device)
     static int resident_ctas(int *sms) {
+        static std::mutex mu;                       // (fwi_acoustic_run_multi calls in from several host threads)
+        std::lock_guard<std::mutex> lock(mu);
         static int cached_dev = -1, cached_occ = 0, cached_sms = 0;
         int dev = 0;
         cudaGetDevice(&dev);
@@ -1015,8 +1020,9 @@ struct Launcher {
         *sms = cached_sms;
         return cached_occ;
     }
-    static cudaError_t launch(const StepParams &p, int blocks, cudaStream_t st) {
-        static const int pdl = env_int("FWI_B200_PDL", 1);
+    static cudaError_t launch(const StepParams &p, int blocks, cudaStream_t st, bool allow_pdl) {
+        static const int pdl_env = env_int("FWI_B200_PDL", 1);
+        const int pdl = pdl_env && allow_pdl;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(blocks);
         cfg.blockDim = dim3(kNW * 32);
@@ -1042,12 +1048,12 @@ int resident_h(int h, int *sms) {
 }
 
 template <int MODE>
-cudaError_t launch_h(int h, const StepParams &p, int blocks, cudaStream_t st) {
+cudaError_t launch_h(int h, const StepParams &p, int blocks, cudaStream_t st, bool pdl) {
     switch (h) {
-    case 1: return Launcher<1, MODE>::launch(p, blocks, st);
-    case 2: return Launcher<2, MODE>::launch(p, blocks, st);
-    case 3: return Launcher<3, MODE>::launch(p, blocks, st);
-    default: return Launcher<4, MODE>::launch(p, blocks, st);
+    case 1: return Launcher<1, MODE>::launch(p, blocks, st, pdl);
+    case 2: return Launcher<2, MODE>::launch(p, blocks, st, pdl);
+    case 3: return Launcher<3, MODE>::launch(p, blocks, st, pdl);
+    default: return Launcher<4, MODE>::launch(p, blocks, st, pdl);
     }
 }
 
@@ -1208,8 +1214,9 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     FWI_CHECK_ARG(d->n_inj == 0 || (b->inj_row_start && b->inj_cell && b->inj_col && b->inj_amp),
                   "injection lists required when n_inj > 0");
     FWI_CHECK_ARG(!(b->q_write && b->q_read), "q_write and q_read are mutually exclusive");
-    FWI_CHECK_ARG(b->q_step_stride == 0 || (b->q_write && b->q_step_stride >= (int64_t)d->n_shots * d->nzp * make_geom(d).pitch),
-                  "q_step_stride must be 0 or at least one snapshot of this call's shots, and needs q_write");
+    FWI_CHECK_ARG(b->q_step_stride == 0 || ((b->q_write || b->q_read) && b->q_step_stride % make_geom(d).pitch == 0 &&
+                                            b->q_step_stride >= (int64_t)d->n_shots * d->nzp * make_geom(d).pitch),
+                  "q_step_stride must be 0 or a whole number of rows, at least one snapshot of this call's shots, with q_write / q_read");
     FWI_CHECK_ARG(!b->q_read || b->image, "image required with q_read");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (d->nsteps == 0) return FWI_OK;
@@ -1323,12 +1330,15 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     const size_t fld = (size_t)d->n_shots * p.stride;
     const int fld_rows = d->n_shots * d->nzp;
     const int n_fields = d->pml_width > 0 ? 6 : 2;
-    FWI_CHECK_ARG((int64_t)d->nsteps * fld_rows < (int64_t)1 << 31, "snapshot tensor has too many rows for one TMA descriptor");
+    // rows between the snapshots of consecutive steps (a call on a subset of the shots of a snapshot array: q_step_stride)
+    const int64_t q_rows = b->q_step_stride > 0 ? b->q_step_stride / g.pitch : fld_rows;
+    const int64_t q_map_rows = (int64_t)(d->nsteps - 1) * q_rows + fld_rows;
+    FWI_CHECK_ARG(q_map_rows < (int64_t)1 << 31, "snapshot tensor has too many rows for one TMA descriptor");
     if ((rc = make_map(&p.tm_wave_u, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kRowU)) != FWI_OK) return rc;
     if ((rc = make_map(&p.tm_wave_o, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kRowO)) != FWI_OK) return rc;
     if ((rc = make_map(&p.tm_w, b->w, d->nzp, g.pitch, kRowO)) != FWI_OK) return rc;
     if (mode >= 2) {
-        if ((rc = make_map(&p.tm_q, b->q_read, (int64_t)d->nsteps * fld_rows, g.pitch, kRowO)) != FWI_OK) return rc;
+        if ((rc = make_map(&p.tm_q, b->q_read, q_map_rows, g.pitch, kRowO)) != FWI_OK) return rc;
         if ((rc = make_map(&p.tm_g, b->image, fld_rows, g.pitch, kRowO)) != FWI_OK) return rc;
     } else {
         p.tm_q = p.tm_w;
@@ -1339,7 +1349,7 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
         if ((rc = make_map(&p.ts_wave_o, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kSideO)) != FWI_OK) return rc;
         if ((rc = make_map(&p.ts_w, b->w, d->nzp, g.pitch, kSideO)) != FWI_OK) return rc;
         if (mode >= 2) {
-            if ((rc = make_map(&p.ts_q, b->q_read, (int64_t)d->nsteps * fld_rows, g.pitch, kSideO)) != FWI_OK) return rc;
+            if ((rc = make_map(&p.ts_q, b->q_read, q_map_rows, g.pitch, kSideO)) != FWI_OK) return rc;
             if ((rc = make_map(&p.ts_g, b->image, fld_rows, g.pitch, kSideO)) != FWI_OK) return rc;
         } else {
             p.ts_q = p.ts_w;
@@ -1387,8 +1397,8 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
         p.row_um = (int)((um - b->wave) / g.pitch);
         p.row_pz = pz ? (int)((pz - b->wave) / g.pitch) : 0;
         p.row_py = py ? (int)((py - b->wave) / g.pitch) : 0;
-        p.row_q = n * fld_rows;
-        p.row_q2 = (n + 1) * fld_rows;
+        p.row_q = (int)(n * q_rows);
+        p.row_q2 = (int)((n + 1) * q_rows);
         // which launch this iteration is: see the comment on `pair` above
         int m = mode;
         if (pair) m = (it & 1) ? 3 : (it + 1 < d->nsteps ? 0 : 2);
@@ -1396,15 +1406,16 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
         p.segs = T.d_segs; p.unit_start = T.d_units; p.n_units = T.n_units;
         const int blocks = T.blocks;
         p.qw = b->q_write ? b->q_write + (size_t)n * (b->q_step_stride > 0 ? (size_t)b->q_step_stride : fld) : nullptr;
-        p.qr = b->q_read ? b->q_read + (size_t)n * fld : nullptr;
+        p.qr = b->q_read ? b->q_read + (size_t)n * (b->q_step_stride > 0 ? (size_t)b->q_step_stride : fld) : nullptr;
         p.G = b->image;
         p.inj_amp = d->n_inj ? b->inj_amp + (size_t)n * d->n_shots * d->n_inj : nullptr;
         p.smp_out = d->n_smp ? b->smp_out + (size_t)n * d->n_shots * d->n_smp : nullptr;
         cudaError_t e;
-        if (m == 3) e = launch_h<3>(h, p, blocks, st);
-        else if (m == 2) e = launch_h<2>(h, p, blocks, st);
-        else if (m == 1) e = launch_h<1>(h, p, blocks, st);
-        else e = launch_h<0>(h, p, blocks, st);
+        const bool pdl = !(d->flags & FWI_FLAG_NO_PDL);
+        if (m == 3) e = launch_h<3>(h, p, blocks, st, pdl);
+        else if (m == 2) e = launch_h<2>(h, p, blocks, st, pdl);
+        else if (m == 1) e = launch_h<1>(h, p, blocks, st, pdl);
+        else e = launch_h<0>(h, p, blocks, st, pdl);
         if (e != cudaSuccess) {
             fwi::set_error("acoustic step launch failed at step %d: %s", n, cudaGetErrorString(e));
             return FWI_ERR_CUDA;
@@ -1480,6 +1491,31 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
 
 extern "C" int fwi_acoustic_run(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, void *stream) {
     return run_impl(d, b, nullptr, stream);
+}
+
+extern "C" int fwi_acoustic_run_multi(int32_t n_jobs, const fwi_acoustic_desc *const *descs,
+                                      const fwi_acoustic_buffers *const *bufs, void *const *streams) {
+    FWI_CHECK_ARG(n_jobs >= 1 && n_jobs <= 16 && descs && bufs && streams, "bad job list");
+    if (n_jobs == 1) return fwi_acoustic_run(descs[0], bufs[0], streams[0]);
+    // one host thread per job: their launches interleave on the device, each job on its own stream
+    int dev = 0;
+    FWI_CHECK_CUDA(cudaGetDevice(&dev));
+    std::vector<int> rc(n_jobs, FWI_OK);
+    std::vector<std::string> err(n_jobs);
+    std::vector<std::thread> th;
+    for (int j = 0; j < n_jobs; ++j)
+        th.emplace_back([&, j]() {
+            cudaSetDevice(dev);
+            rc[j] = fwi_acoustic_run(descs[j], bufs[j], streams[j]);
+            if (rc[j] != FWI_OK) err[j] = fwi_last_error();
+        });
+    for (auto &t : th) t.join();
+    for (int j = 0; j < n_jobs; ++j)
+        if (rc[j] != FWI_OK) {
+            fwi::set_error("job %d: %s", j, err[j].c_str());
+            return rc[j];
+        }
+    return FWI_OK;
 }
 
 extern "C" int32_t fwi_slab_exchanges(int32_t nsteps, int32_t halo_steps) {

@@ -12,6 +12,7 @@
 #include <torch/torch.h>
 
 #include <cmath>
+#include <cstdlib>
 #include <tuple>
 #include <vector>
 
@@ -156,6 +157,82 @@ Tensor scalar_run(const Tensor &w, const Tensor &sigz, const Tensor &sigy, Tenso
     return smp_out;
 }
 
+// ---- several shot groups of one gradient at once, one stream per group ---------------------------------------
+// Group j advances the shots [shot0[j], shot0[j] + n_j) of a gradient whose snapshot array q (and image) holds all
+// n_total shots; the groups' launches interleave on the device (fwi_acoustic_run_multi), so one group's step covers the
+// ramp and tail of the other's.  Group 0 runs on the current stream, the others on pool streams that wait for it and
+// that it waits for: to the caller this is one asynchronous call on the current stream.
+std::vector<Tensor> scalar_run_multi(const Tensor &w, const Tensor &sigz, const Tensor &sigy, at::TensorList wave,
+                                     at::TensorList inj_start, at::TensorList inj_cell, at::TensorList inj_col,
+                                     at::TensorList inj_amp, at::TensorList smp_cell, const c10::optional<Tensor> &q_write,
+                                     const c10::optional<Tensor> &q_read, const c10::optional<Tensor> &image,
+                                     at::IntArrayRef shot0, const Tensor &meta, int64_t n_total, int64_t nsteps, bool adjoint,
+                                     int64_t order, int64_t pml, double dz, double dy, int64_t chunk_rows) {
+    const size_t J = wave.size();
+    TORCH_CHECK(J >= 1 && J <= 16 && inj_start.size() == J && inj_cell.size() == J && inj_col.size() == J &&
+                inj_amp.size() == J && smp_cell.size() == J && shot0.size() == J, "one entry per shot group expected");
+    TORCH_CHECK(w.is_cuda(), "scalar_run_multi needs CUDA tensors: there is no CPU path");
+    const double *m = meta.data_ptr<double>();
+    const int64_t stride = (int64_t)m[8];
+    c10::cuda::CUDAGuard guard(w.device());
+    auto main = c10::cuda::getCurrentCUDAStream(w.device().index());
+    std::vector<c10::cuda::CUDAStream> streams;
+    streams.push_back(main);
+    for (size_t j = 1; j < J; ++j) streams.push_back(c10::cuda::getStreamFromPool(false, w.device().index()));
+    cudaEvent_t ready;
+    C10_CUDA_CHECK(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+    C10_CUDA_CHECK(cudaEventRecord(ready, main.stream()));
+    std::vector<fwi_acoustic_desc> descs(J);
+    std::vector<fwi_acoustic_buffers> bufs(J);
+    std::vector<Tensor> out(J), tables(J);
+    std::vector<const fwi_acoustic_desc *> dp(J);
+    std::vector<const fwi_acoustic_buffers *> bp(J);
+    std::vector<void *> sp(J);
+    Tensor qw = q_write.has_value() ? *q_write : Tensor(), im = image.has_value() ? *image : Tensor();
+    for (size_t j = 0; j < J; ++j) {
+        const int64_t n_j = wave[j].numel() / ((int64_t)m[7] * stride);
+        TORCH_CHECK(n_j >= 1 && wave[j].numel() == (int64_t)m[7] * n_j * stride, "wave workspace of group ", j, " has the wrong size");
+        TORCH_CHECK(shot0[j] >= 0 && shot0[j] + n_j <= n_total, "shot range of group ", j, " outside the gradient's shots");
+        fwi_acoustic_desc &d = descs[j];
+        d = fwi_acoustic_desc{};
+        d.nzp = (int32_t)m[5]; d.nyp = (int32_t)m[6]; d.order = (int32_t)order; d.pml_width = (int32_t)pml;
+        d.n_shots = (int32_t)n_j; d.chunk_rows = (int32_t)chunk_rows; d.nsteps = (int32_t)nsteps; d.adjoint = adjoint ? 1 : 0;
+        d.n_inj = inj_amp[j].numel() ? (int32_t)inj_amp[j].size(2) : 0;
+        d.inj_scale_a = d.smp_div_a = adjoint ? 1 : 0;
+        d.n_smp = smp_cell[j].numel() ? (int32_t)smp_cell[j].size(1) : 0;
+        d.dz = dz; d.dy = dy; d.dt = m[2];
+        // programmatic dependent launches stay on (measured on C2, two adjoint groups: 46.9 us per step with, 48.6 without;
+        // FWI_B200_MULTI_PDL=0 switches them off for the groups)
+        static const bool multi_pdl = !(getenv("FWI_B200_MULTI_PDL") && atoi(getenv("FWI_B200_MULTI_PDL")) == 0);
+        d.flags = multi_pdl ? 0 : FWI_FLAG_NO_PDL;
+        TORCH_CHECK(d.n_inj == 0 || (inj_amp[j].is_contiguous() && inj_amp[j].size(0) == nsteps && inj_amp[j].size(1) == n_j),
+                    "injection amplitudes of group ", j, " must be contiguous [nsteps, n_shots, n]");
+        out[j] = at::empty({nsteps, n_j, (int64_t)d.n_smp}, w.options());
+        tables[j] = at::empty({(int64_t)m[9]}, w.options().dtype(at::kByte));
+        fwi_acoustic_buffers &b = bufs[j];
+        b = fwi_acoustic_buffers{};
+        b.w = w.data_ptr<float>(); b.sigz = fptr(sigz); b.sigy = fptr(sigy); b.wave = wave[j].data_ptr<float>();
+        b.inj_row_start = iptr(inj_start[j]); b.inj_cell = iptr(inj_cell[j]); b.inj_col = iptr(inj_col[j]);
+        b.inj_amp = fptr(inj_amp[j]); b.smp_cell = iptr(smp_cell[j]);
+        b.smp_out = out[j].numel() ? out[j].data_ptr<float>() : nullptr;
+        b.q_write = qw.defined() && qw.numel() ? qw.data_ptr<float>() + shot0[j] * stride : nullptr;
+        b.q_read = q_read.has_value() && q_read->numel() ? q_read->data_ptr<float>() + shot0[j] * stride : nullptr;
+        b.image = im.defined() && im.numel() ? im.data_ptr<float>() + shot0[j] * stride : nullptr;
+        b.q_step_stride = (b.q_write || b.q_read) ? n_total * stride : 0;
+        b.unit_table = tables[j].data_ptr();
+        dp[j] = &d; bp[j] = &b; sp[j] = static_cast<void *>(streams[j].stream());
+        if (j > 0) C10_CUDA_CHECK(cudaStreamWaitEvent(streams[j].stream(), ready, 0));
+    }
+    const int rc = fwi_acoustic_run_multi((int32_t)J, dp.data(), bp.data(), sp.data());
+    for (size_t j = 1; j < J; ++j) {                 // the current stream continues when every group is done
+        C10_CUDA_CHECK(cudaEventRecord(ready, streams[j].stream()));
+        C10_CUDA_CHECK(cudaStreamWaitEvent(main.stream(), ready, 0));
+    }
+    C10_CUDA_CHECK(cudaEventDestroy(ready));
+    check_rc(rc, "fwi_acoustic_run_multi");
+    return out;
+}
+
 // ---- image -> dJ/dv -----------------------------------------------------------------------------------------------
 Tensor scalar_fold(const Tensor &image, const c10::optional<Tensor> &gs, const c10::optional<Tensor> &amp, const Tensor &src_cell,
                    const Tensor &v, const Tensor &meta, int64_t n_shots, int64_t order, int64_t pml, double dz, double dy) {
@@ -220,6 +297,10 @@ TORCH_LIBRARY(b200fwi, m) {
     m.def("scalar_run(Tensor w, Tensor sigz, Tensor sigy, Tensor(a!) wave, Tensor inj_start, Tensor inj_cell, Tensor inj_col, "
           "Tensor inj_amp, Tensor smp_cell, Tensor(b!)? q_write, Tensor? q_read, Tensor(c!)? image, Tensor meta, int n_shots, "
           "int nsteps, bool adjoint, int order, int pml, float dz, float dy, int chunk_rows, int q_step_stride=0) -> Tensor");
+    m.def("scalar_run_multi(Tensor w, Tensor sigz, Tensor sigy, Tensor(a!)[] wave, Tensor[] inj_start, Tensor[] inj_cell, "
+          "Tensor[] inj_col, Tensor[] inj_amp, Tensor[] smp_cell, Tensor(b!)? q_write, Tensor? q_read, Tensor(c!)? image, "
+          "int[] shot0, Tensor meta, int n_total, int nsteps, bool adjoint, int order, int pml, float dz, float dy, "
+          "int chunk_rows) -> Tensor[]");
     m.def("scalar_fold(Tensor image, Tensor? gs, Tensor? amp, Tensor src_cell, Tensor v, Tensor meta, int n_shots, int order, "
           "int pml, float dz, float dy) -> Tensor");
     m.def("flag_begin(Tensor bad) -> Tensor");
@@ -233,6 +314,7 @@ TORCH_LIBRARY_IMPL(b200fwi, CompositeExplicitAutograd, m) {
     m.impl("scalar_prepare", scalar_prepare);
     m.impl("scalar_plan_points", scalar_plan_points);
     m.impl("scalar_run", scalar_run);
+    m.impl("scalar_run_multi", scalar_run_multi);
     m.impl("scalar_fold", scalar_fold);
     m.impl("flag_begin", flag_begin);
     m.impl("flag_end", flag_end);

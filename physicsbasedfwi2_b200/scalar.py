@@ -13,6 +13,7 @@ path: tensors must live on a CUDA device and the library must be built.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import numpy as np
@@ -153,13 +154,13 @@ def _settle(wave: torch.Tensor, nsteps: int, n_fields: int) -> torch.Tensor:
     return wave.view(n_fields, -1)[perm].contiguous().view(-1)
 
 
-def _forward_groups(n_shots: int, shot_stride: int):
+def _forward_groups(n_shots: int, shot_stride: int, env=None):
     """Shot groups [s0, s1) of the forward time loop: one group unless at least two more shots than fit L2 with their
     two wavefields (64 MB budget of the 126 MB L2; FWI_B200_FWD_SHOTS overrides the group size, 0 = never split)."""
     import os
     per_shot = 2 * shot_stride * 4
     nmax = max(1, int(64e6 // per_shot))
-    env = os.environ.get("FWI_B200_FWD_SHOTS")
+    env = env if env is not None else os.environ.get("FWI_B200_FWD_SHOTS")
     if env is not None:
         nmax = int(env)
         if nmax <= 0 or n_shots <= nmax:
@@ -235,6 +236,26 @@ class _ScalarFunction(torch.autograd.Function):
             _lib.time_loop_end(cur, ev, "acoustic_fwd" if q_write is not None else "acoustic_fwd0", nsteps, n_s)
             return out
 
+        def run_groups(groups, nsteps, q_write):
+            """The forward time loops of the shot groups, one after the other: a group's wavefields then stay in L2 from
+            step to step (measured on C2: 2 x 18.2 us per step against 41.2 for all six shots in one launch, and 38.2 with
+            the groups running concurrently on two streams, FWI_B200_MULTI=1 - they evict each other)."""
+            plans = [O.scalar_plan_points(x_s[s0:s1], vd, meta, bad, *geo, rnd, 0, 0)[1:] for s0, s1 in groups]
+            amps = [amp[:, s0:s1].contiguous() for s0, s1 in groups]
+            if os.environ.get("FWI_B200_MULTI", "0") != "1":
+                parts = []
+                for (s0, s1), amp_g in zip(groups, amps):
+                    wave_g = torch.zeros(n_fields * (s1 - s0) * stride, dtype=torch.float32, device=dev)
+                    parts.append(run(nsteps, amp_g, wave_g, q_write, shots=(s0, s1)))
+                return torch.cat(parts, 1)
+            waves = [torch.zeros(n_fields * (s1 - s0) * stride, dtype=torch.float32, device=dev) for s0, s1 in groups]
+            ev = _lib.time_loop_begin(cur)
+            parts = O.scalar_run_multi(w, sigz, sigy, waves, [p[0] for p in plans], [p[1] for p in plans], [p[2] for p in plans],
+                                       amps, [r_cell[s0:s1] for s0, s1 in groups], q_write, None, None,
+                                       [s0 for s0, _ in groups], meta, S, nsteps, False, *geo, int(chunk_rows))
+            _lib.time_loop_end(cur, ev, "acoustic_fwd" if q_write is not None else "acoustic_fwd0", nsteps, S)
+            return torch.cat(list(parts), 1)
+
         q, K = None, int(checkpoint_every)
         ctx.ckpt = None
         wave = torch.zeros(n_fields * S * stride, dtype=torch.float32, device=dev)
@@ -261,11 +282,7 @@ class _ScalarFunction(torch.autograd.Function):
                     # (B200: 126 MB; measured on C2: 3 shots 18.5 us, 6 shots 41.4 us per step), the adjoint when it
                     # carries all shots: the forward time loop runs per group of shots, the adjoint once
                     del wave
-                    parts = []
-                    for s0, s1 in groups:
-                        wave_g = torch.zeros(n_fields * (s1 - s0) * stride, dtype=torch.float32, device=dev)
-                        parts.append(run(nti, amp[:, s0:s1].contiguous(), wave_g, q, shots=(s0, s1)))
-                    rec = torch.cat(parts, 1)
+                    rec = run_groups(groups, nti, q)
         O.flag_end(flag)
         out = rec[::ratio].contiguous() if ratio > 1 else rec
         ctx.saved = (vd, meta, w, sigz, sigy, s_cell, r_cell, r_start, r_sc, r_so, s_start, s_sc, s_so)
@@ -274,6 +291,7 @@ class _ScalarFunction(torch.autograd.Function):
         ctx.dims = (nt, S, Ns, R, nti, ratio, n_fields, stride, geo, int(chunk_rows))
         ctx.need = (need_v, need_s)
         ctx.src_like = source_amplitudes.detach()
+        ctx.x_r, ctx.rnd = x_r, rnd
         return out
 
     @staticmethod
@@ -319,6 +337,25 @@ class _ScalarFunction(torch.autograd.Function):
                     awave = _settle(awave, n, n_fields)
                 gs = torch.cat(parts[::-1], 0)
                 ctx.ckpt = None
+            elif (os.environ.get("FWI_B200_ADJ_GROUPS", "1") == "1" and need_v
+                  and len(_forward_groups(S, stride, os.environ.get("FWI_B200_ADJ_SHOTS"))) > 1):
+                # The adjoint does not fit L2 (wavefields + image + two snapshots per shot), so it gains nothing from small
+                # groups as such - but every launch has a ramp (CTAs start over ~3 us, every warp waits for its first TMA
+                # tile) and a tail (the slowest warp), ~13 % of a 6-shot launch.  Two groups on two streams interleave
+                # their launches, each covering the other's ramp and tail: measured on C2 48.1 us per step against 55.4.
+                groups = _forward_groups(S, stride, os.environ.get("FWI_B200_ADJ_SHOTS"))
+                del awave
+                x_r_all = ctx.x_r
+                plans = [O.scalar_plan_points(x_r_all[s0:s1], vd, meta, torch.zeros(1, dtype=torch.int32, device=dev), *geo,
+                                              ctx.rnd, 0, 0)[1:] for s0, s1 in groups]
+                waves = [torch.zeros(n_fields * (s1 - s0) * stride, dtype=torch.float32, device=dev) for s0, s1 in groups]
+                ev = _lib.time_loop_begin(cur)
+                parts = O.scalar_run_multi(w, sigz, sigy, waves, [p[0] for p in plans], [p[1] for p in plans],
+                                           [p[2] for p in plans], [g_in[:, s0:s1].contiguous() for s0, s1 in groups],
+                                           [s_cell[s0:s1] for s0, s1 in groups], None, ctx.q, image, [s0 for s0, _ in groups],
+                                           meta, S, nti, True, *geo, chunk_rows)
+                _lib.time_loop_end(cur, ev, "acoustic_adj", nti, S)
+                gs = torch.cat(list(parts), 1)
             else:
                 gs = run(nti, True, awave, g_in, q_read=ctx.q if need_v else None)
             grad_v = grad_s = None

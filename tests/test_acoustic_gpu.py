@@ -187,8 +187,10 @@ def test_forward_shot_groups_do_not_change_results(cuda_lib, monkeypatch):
     grad_rec = torch.randn(c["nt"], c["S"], c["R"], generator=torch.Generator().manual_seed(3))
     dev = torch.device("cuda:0")
     outs = []
-    for fwd_shots in ("0", "2", "1"):
+    for fwd_shots, multi, adj in (("0", "1", "0"), ("2", "1", "0"), ("2", "0", "0"), ("1", "1", "0"), ("2", "1", "1")):
         monkeypatch.setenv("FWI_B200_FWD_SHOTS", fwd_shots)
+        monkeypatch.setenv("FWI_B200_MULTI", multi)          # groups concurrently on their own streams / one after the other
+        monkeypatch.setenv("FWI_B200_ADJ_GROUPS", adj)       # (tuning switch: the adjoint per group too)
         vg = v.to(dev).requires_grad_(True)
         sg = src.to(dev).requires_grad_(True)
         rec = Propagator({"vp": vg}, c["dx"], pml_width=c["pml"], accuracy=c["order"])(sg, x_s.to(dev), x_r.to(dev), c["dt"])
