@@ -157,7 +157,6 @@ def _settle(wave: torch.Tensor, nsteps: int, n_fields: int) -> torch.Tensor:
 def _forward_groups(n_shots: int, shot_stride: int, env=None):
     """Shot groups [s0, s1) of the forward time loop: one group unless at least two more shots than fit L2 with their
     two wavefields (64 MB budget of the 126 MB L2; FWI_B200_FWD_SHOTS overrides the group size, 0 = never split)."""
-    import os
     per_shot = 2 * shot_stride * 4
     nmax = max(1, int(64e6 // per_shot))
     env = env if env is not None else os.environ.get("FWI_B200_FWD_SHOTS")
@@ -168,6 +167,23 @@ def _forward_groups(n_shots: int, shot_stride: int, env=None):
     elif n_shots < nmax + 2 or per_shot < (1 << 20):
         return [(0, n_shots)]
     k = -(-n_shots // nmax)
+    base, extra = divmod(n_shots, k)
+    out, lo = [], 0
+    for g in range(k):
+        hi = lo + base + (1 if g < extra else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+def _adjoint_groups(n_shots: int, shot_stride: int):
+    """Shot groups of the adjoint time loop, run concurrently on their own streams: two groups when there are at least four
+    shots on a grid large enough for the step kernel to be bandwidth-bound (FWI_B200_ADJ_GROUPS overrides the number of
+    groups; 1 = one launch over all shots)."""
+    k = 2 if (n_shots >= 4 and shot_stride * 4 >= (4 << 20)) else 1
+    env = os.environ.get("FWI_B200_ADJ_GROUPS")
+    if env is not None:
+        k = max(1, min(int(env), n_shots))
     base, extra = divmod(n_shots, k)
     out, lo = [], 0
     for g in range(k):
@@ -218,71 +234,60 @@ class _ScalarFunction(torch.autograd.Function):
         need_v, need_s = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         cur = torch.cuda.current_stream(dev)
 
-        def run(nsteps, amp_n, wave, q_write, shots=None):
-            """One forward time loop: all shots, or the shots [s0, s1) of this call writing into the snapshot array of
-            all of them (their injection lists are planned again for the subset: the lists index per call)."""
-            if shots is None:
-                n_s, lists, smp, q_arg, qss = S, (s_start, s_sc, s_so), r_cell, q_write, 0
-            else:
-                s0, s1 = shots
-                n_s = s1 - s0
-                _, a, b_, c = O.scalar_plan_points(x_s[s0:s1], vd, meta, bad, *geo, rnd, 0, 0)
-                lists, smp = (a, b_, c), r_cell[s0:s1]
-                q_arg = None if q_write is None else q_write[s0 * stride:]
-                qss = S * stride
+        # Forward time loops run per GROUP of shots whose two wavefields fit L2 (one group on small problems): a forward
+        # launch is fastest when its wavefields stay in L2 from one step to the next (B200: 126 MB; measured on C2: 3 shots
+        # 18.2 us per step, 6 shots 41.2).  Groups run one after the other - concurrently on two streams they evict each
+        # other (38.2 us; FWI_B200_MULTI=1 to try) - and write into the snapshot array of all shots (q_step_stride).
+        fgroups = _forward_groups(S, stride)
+        one = len(fgroups) == 1
+        fplans = [(s_start, s_sc, s_so)] if one else [O.scalar_plan_points(x_s[s0:s1], vd, meta, bad, *geo, rnd, 0, 0)[1:]
+                                                      for s0, s1 in fgroups]
+        famps = [amp] if one else [amp[:, s0:s1].contiguous() for s0, s1 in fgroups]
+
+        def run(gi, t0, nsteps, wave, q_write):
+            """Steps [t0, t0 + nsteps) of the forward time loop of group gi; q_write: snapshot array of ALL shots for these steps."""
+            s0, s1 = fgroups[gi]
             ev = _lib.time_loop_begin(cur)
-            out = O.scalar_run(w, sigz, sigy, wave, *lists, amp_n, smp, q_arg, None, None, meta, n_s,
-                               nsteps, False, *geo, int(chunk_rows), qss)
-            _lib.time_loop_end(cur, ev, "acoustic_fwd" if q_write is not None else "acoustic_fwd0", nsteps, n_s)
+            out = O.scalar_run(w, sigz, sigy, wave, *fplans[gi], famps[gi][t0:t0 + nsteps], r_cell[s0:s1],
+                               None if q_write is None else q_write[s0 * stride:], None, None, meta, s1 - s0, nsteps, False,
+                               *geo, int(chunk_rows), 0 if (one or q_write is None) else S * stride)
+            _lib.time_loop_end(cur, ev, "acoustic_fwd" if q_write is not None else "acoustic_fwd0", nsteps, s1 - s0)
             return out
 
-        def run_groups(groups, nsteps, q_write):
-            """The forward time loops of the shot groups, one after the other: a group's wavefields then stay in L2 from
-            step to step (measured on C2: 2 x 18.2 us per step against 41.2 for all six shots in one launch, and 38.2 with
-            the groups running concurrently on two streams, FWI_B200_MULTI=1 - they evict each other)."""
-            plans = [O.scalar_plan_points(x_s[s0:s1], vd, meta, bad, *geo, rnd, 0, 0)[1:] for s0, s1 in groups]
-            amps = [amp[:, s0:s1].contiguous() for s0, s1 in groups]
-            if os.environ.get("FWI_B200_MULTI", "0") != "1":
-                parts = []
-                for (s0, s1), amp_g in zip(groups, amps):
-                    wave_g = torch.zeros(n_fields * (s1 - s0) * stride, dtype=torch.float32, device=dev)
-                    parts.append(run(nsteps, amp_g, wave_g, q_write, shots=(s0, s1)))
-                return torch.cat(parts, 1)
-            waves = [torch.zeros(n_fields * (s1 - s0) * stride, dtype=torch.float32, device=dev) for s0, s1 in groups]
-            ev = _lib.time_loop_begin(cur)
-            parts = O.scalar_run_multi(w, sigz, sigy, waves, [p[0] for p in plans], [p[1] for p in plans], [p[2] for p in plans],
-                                       amps, [r_cell[s0:s1] for s0, s1 in groups], q_write, None, None,
-                                       [s0 for s0, _ in groups], meta, S, nsteps, False, *geo, int(chunk_rows))
-            _lib.time_loop_end(cur, ev, "acoustic_fwd" if q_write is not None else "acoustic_fwd0", nsteps, S)
-            return torch.cat(list(parts), 1)
+        def new_wave(gi):
+            return torch.zeros(n_fields * (fgroups[gi][1] - fgroups[gi][0]) * stride, dtype=torch.float32, device=dev)
 
         q, K = None, int(checkpoint_every)
         ctx.ckpt = None
-        wave = torch.zeros(n_fields * S * stride, dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             if need_v and 0 < K < nti:
                 # wavefield checkpointing: keep the state every K steps instead of a snapshot per step;
                 # backward() recomputes the snapshots of one segment at a time
-                ckpts, parts = [], []
-                for t0 in range(0, nti, K):
-                    n = min(K, nti - t0)
-                    ckpts.append(wave.clone())
-                    parts.append(run(n, amp[t0:t0 + n], wave, None))
-                    wave = _settle(wave, n, n_fields)
-                rec = torch.cat(parts, 0)
+                ckpts, recs = [], []
+                for gi in range(len(fgroups)):
+                    wave, parts, cg = new_wave(gi), [], []
+                    for t0 in range(0, nti, K):
+                        n = min(K, nti - t0)
+                        cg.append(wave.clone())
+                        parts.append(run(gi, t0, n, wave, None))
+                        wave = _settle(wave, n, n_fields)
+                    ckpts.append(cg)
+                    recs.append(torch.cat(parts, 0))
+                rec = recs[0] if one else torch.cat(recs, 1)
                 ctx.ckpt = (K, ckpts)
             else:
                 if need_v:
                     q = torch.empty(nti * S * stride, dtype=torch.float32, device=dev)
-                groups = _forward_groups(S, stride)
-                if len(groups) == 1:
-                    rec = run(nti, amp, wave, q)
+                if one or os.environ.get("FWI_B200_MULTI", "0") != "1":
+                    recs = [run(gi, 0, nti, new_wave(gi), q) for gi in range(len(fgroups))]
                 else:
-                    # a forward launch is fastest when the wavefields of its shots stay in L2 from one step to the next
-                    # (B200: 126 MB; measured on C2: 3 shots 18.5 us, 6 shots 41.4 us per step), the adjoint when it
-                    # carries all shots: the forward time loop runs per group of shots, the adjoint once
-                    del wave
-                    rec = run_groups(groups, nti, q)
+                    ev = _lib.time_loop_begin(cur)
+                    recs = list(O.scalar_run_multi(w, sigz, sigy, [new_wave(gi) for gi in range(len(fgroups))],
+                                                   [p[0] for p in fplans], [p[1] for p in fplans], [p[2] for p in fplans], famps,
+                                                   [r_cell[s0:s1] for s0, s1 in fgroups], q, None, None,
+                                                   [s0 for s0, _ in fgroups], meta, S, nti, False, *geo, int(chunk_rows)))
+                    _lib.time_loop_end(cur, ev, "acoustic_fwd" if q is not None else "acoustic_fwd0", nti, S)
+                rec = recs[0] if one else torch.cat(recs, 1)
         O.flag_end(flag)
         out = rec[::ratio].contiguous() if ratio > 1 else rec
         ctx.saved = (vd, meta, w, sigz, sigy, s_cell, r_cell, r_start, r_sc, r_so, s_start, s_sc, s_so)
@@ -292,6 +297,7 @@ class _ScalarFunction(torch.autograd.Function):
         ctx.need = (need_v, need_s)
         ctx.src_like = source_amplitudes.detach()
         ctx.x_r, ctx.rnd = x_r, rnd
+        ctx.fwd = (fgroups, fplans, famps)
         return out
 
     @staticmethod
@@ -311,53 +317,55 @@ class _ScalarFunction(torch.autograd.Function):
         image = torch.zeros(S * stride, dtype=torch.float32, device=dev) if need_v else None
         cur = torch.cuda.current_stream(dev)
 
-        def run(nsteps, adjoint, wave, amp_n, q_write=None, q_read=None):
+        fgroups, fplans, famps = ctx.fwd
+        # The adjoint does not fit L2 (wavefields + image + two snapshots per shot), so small groups gain it nothing as such -
+        # but every launch has a ramp (CTAs start over ~3 us, every warp waits for its first TMA tile) and a tail (the
+        # slowest warp), ~13 % of a 6-shot launch.  Two groups on two streams interleave their launches, each covering the
+        # other's ramp and tail (fwi_acoustic_run_multi): measured on C2 46.9 us per step against 55.4 in one launch.
+        agroups = _adjoint_groups(S, stride) if need_v else [(0, S)]
+        a_one = len(agroups) == 1
+        if a_one:
+            aplans = [(r_start, r_sc, r_so)]
+        else:
+            nobad = torch.zeros(1, dtype=torch.int32, device=dev)
+            aplans = [O.scalar_plan_points(ctx.x_r[s0:s1], vd, meta, nobad, *geo, ctx.rnd, 0, 0)[1:] for s0, s1 in agroups]
+        awaves = [torch.zeros(n_fields * (s1 - s0) * stride, dtype=torch.float32, device=dev) for s0, s1 in agroups]
+
+        def run_adjoint(t0, nsteps, q_read):
+            """Adjoint steps [t0, t0 + nsteps) (in reverse) of every group; q_read: snapshots of ALL shots for these steps."""
+            amps = [g_in[t0:t0 + nsteps] if a_one else g_in[t0:t0 + nsteps, s0:s1].contiguous() for s0, s1 in agroups]
             ev = _lib.time_loop_begin(cur)
-            if adjoint:
-                out = O.scalar_run(w, sigz, sigy, wave, r_start, r_sc, r_so, amp_n, s_cell, None, q_read,
+            if a_one:
+                out = O.scalar_run(w, sigz, sigy, awaves[0], *aplans[0], amps[0].contiguous(), s_cell, None, q_read,
                                    image if q_read is not None else None, meta, S, nsteps, True, *geo, chunk_rows)
-                tag = "acoustic_adj"
             else:
-                out = O.scalar_run(w, sigz, sigy, wave, s_start, s_sc, s_so, amp_n, r_cell[:, :0], q_write, None, None, meta,
-                                   S, nsteps, False, *geo, chunk_rows)
-                tag = "acoustic_fwd"
-            _lib.time_loop_end(cur, ev, tag, nsteps, S)
+                parts = O.scalar_run_multi(w, sigz, sigy, awaves, [p[0] for p in aplans], [p[1] for p in aplans],
+                                           [p[2] for p in aplans], amps, [s_cell[s0:s1] for s0, s1 in agroups], None, q_read,
+                                           image, [s0 for s0, _ in agroups], meta, S, nsteps, True, *geo, chunk_rows)
+                out = torch.cat(list(parts), 1)
+            _lib.time_loop_end(cur, ev, "acoustic_adj", nsteps, S)
             return out
 
         with torch.cuda.device(dev):
-            awave = torch.zeros(n_fields * S * stride, dtype=torch.float32, device=dev)
             if ctx.ckpt is not None:
                 K, ckpts = ctx.ckpt
                 qseg = torch.empty(K * S * stride, dtype=torch.float32, device=dev)
+                f_one = len(fgroups) == 1
                 parts = []
                 for t0 in reversed(range(0, nti, K)):
                     n = min(K, nti - t0)
-                    run(n, False, ckpts.pop(), ctx.amp[t0:t0 + n], q_write=qseg)
-                    parts.append(run(n, True, awave, g_in[t0:t0 + n].contiguous(), q_read=qseg))
-                    awave = _settle(awave, n, n_fields)
+                    for gi, (s0, s1) in enumerate(fgroups):           # recompute this segment's snapshots, group by group
+                        ev = _lib.time_loop_begin(cur)
+                        O.scalar_run(w, sigz, sigy, ckpts[gi].pop(), *fplans[gi], famps[gi][t0:t0 + n], r_cell[s0:s1, :0],
+                                     qseg[s0 * stride:], None, None, meta, s1 - s0, n, False, *geo, chunk_rows,
+                                     0 if f_one else S * stride)
+                        _lib.time_loop_end(cur, ev, "acoustic_fwd", n, s1 - s0)
+                    parts.append(run_adjoint(t0, n, qseg))
+                    awaves = [_settle(a, n, n_fields) for a in awaves]
                 gs = torch.cat(parts[::-1], 0)
                 ctx.ckpt = None
-            elif (os.environ.get("FWI_B200_ADJ_GROUPS", "1") == "1" and need_v
-                  and len(_forward_groups(S, stride, os.environ.get("FWI_B200_ADJ_SHOTS"))) > 1):
-                # The adjoint does not fit L2 (wavefields + image + two snapshots per shot), so it gains nothing from small
-                # groups as such - but every launch has a ramp (CTAs start over ~3 us, every warp waits for its first TMA
-                # tile) and a tail (the slowest warp), ~13 % of a 6-shot launch.  Two groups on two streams interleave
-                # their launches, each covering the other's ramp and tail: measured on C2 48.1 us per step against 55.4.
-                groups = _forward_groups(S, stride, os.environ.get("FWI_B200_ADJ_SHOTS"))
-                del awave
-                x_r_all = ctx.x_r
-                plans = [O.scalar_plan_points(x_r_all[s0:s1], vd, meta, torch.zeros(1, dtype=torch.int32, device=dev), *geo,
-                                              ctx.rnd, 0, 0)[1:] for s0, s1 in groups]
-                waves = [torch.zeros(n_fields * (s1 - s0) * stride, dtype=torch.float32, device=dev) for s0, s1 in groups]
-                ev = _lib.time_loop_begin(cur)
-                parts = O.scalar_run_multi(w, sigz, sigy, waves, [p[0] for p in plans], [p[1] for p in plans],
-                                           [p[2] for p in plans], [g_in[:, s0:s1].contiguous() for s0, s1 in groups],
-                                           [s_cell[s0:s1] for s0, s1 in groups], None, ctx.q, image, [s0 for s0, _ in groups],
-                                           meta, S, nti, True, *geo, chunk_rows)
-                _lib.time_loop_end(cur, ev, "acoustic_adj", nti, S)
-                gs = torch.cat(list(parts), 1)
             else:
-                gs = run(nti, True, awave, g_in, q_read=ctx.q if need_v else None)
+                gs = run_adjoint(0, nti, ctx.q if need_v else None)
             grad_v = grad_s = None
             if need_v:
                 # dJ/dv = fold((2 / v_pad) (sum_s image_s + source term)): one native call (csrc/host_kernels.cu)

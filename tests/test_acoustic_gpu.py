@@ -122,12 +122,16 @@ def test_cuda_matches_committed_golden_vectors(cuda_lib, path, small, monkeypatc
     assert K.rel_l2(sg.grad, torch.from_numpy(z["grad_src"])) <= GRAD_TOL
 
 
-@pytest.mark.parametrize("small", ["1", "0"], ids=["cluster-resident", "step-kernel"])
+@pytest.mark.parametrize("small", ["1", "0", "groups"], ids=["cluster-resident", "step-kernel", "step-kernel-shot-groups"])
 @pytest.mark.parametrize("K", [14, 7, 33])
 def test_wavefield_checkpointing_reproduces_the_stored_snapshot_gradient(cuda_lib, K, small, monkeypatch):
     """checkpoint_every=K recomputes the snapshots segment by segment (BASELINE config 4): same
     kernels, same arithmetic, so traces and gradients must be identical to the k=1 snapshot mode."""
     from physicsbasedfwi2_b200.scalar import Propagator
+    if small == "groups":      # forward groups of one shot, two concurrent adjoint groups (what SEAM-sized grids run)
+        small = "0"
+        monkeypatch.setenv("FWI_B200_FWD_SHOTS", "1")
+        monkeypatch.setenv("FWI_B200_ADJ_GROUPS", "2")
     monkeypatch.setenv("FWI_B200_SMALL", small)
     c = CASES[1]       # 8th order, sub-stepped (ratio 2), two sources per shot
     from tests import _cases as KK
@@ -175,7 +179,8 @@ def test_paired_imaging_is_bit_identical_to_one_imaging_per_step(cuda_lib, nt, m
 
 def test_forward_shot_groups_do_not_change_results(cuda_lib, monkeypatch):
     """Large grids run the forward time loop per group of shots (wavefields L2-resident) into the snapshot array of all
-    shots (q_step_stride of the C ABI); the adjoint runs once over all of them.  Same kernels per shot: same bits."""
+    shots (q_step_stride of the C ABI) and the adjoint as concurrent groups on their own streams (fwi_acoustic_run_multi).
+    Same kernels per shot: same bits, however the shots are grouped."""
     from physicsbasedfwi2_b200.scalar import Propagator
     monkeypatch.setenv("FWI_B200_SMALL", "0")
     c = dict(CASES[3], S=5)
@@ -187,10 +192,10 @@ def test_forward_shot_groups_do_not_change_results(cuda_lib, monkeypatch):
     grad_rec = torch.randn(c["nt"], c["S"], c["R"], generator=torch.Generator().manual_seed(3))
     dev = torch.device("cuda:0")
     outs = []
-    for fwd_shots, multi, adj in (("0", "1", "0"), ("2", "1", "0"), ("2", "0", "0"), ("1", "1", "0"), ("2", "1", "1")):
-        monkeypatch.setenv("FWI_B200_FWD_SHOTS", fwd_shots)
-        monkeypatch.setenv("FWI_B200_MULTI", multi)          # groups concurrently on their own streams / one after the other
-        monkeypatch.setenv("FWI_B200_ADJ_GROUPS", adj)       # (tuning switch: the adjoint per group too)
+    for fwd_shots, multi, adj in (("0", "0", "1"), ("2", "1", "1"), ("2", "0", "2"), ("1", "1", "3"), ("0", "0", "5")):
+        monkeypatch.setenv("FWI_B200_FWD_SHOTS", fwd_shots)  # shots per forward group (0: one group)
+        monkeypatch.setenv("FWI_B200_MULTI", multi)          # forward groups concurrently on their own streams / one after the other
+        monkeypatch.setenv("FWI_B200_ADJ_GROUPS", adj)       # concurrent groups of the adjoint time loop
         vg = v.to(dev).requires_grad_(True)
         sg = src.to(dev).requires_grad_(True)
         rec = Propagator({"vp": vg}, c["dx"], pml_width=c["pml"], accuracy=c["order"])(sg, x_s.to(dev), x_r.to(dev), c["dt"])
