@@ -108,7 +108,10 @@ struct StepParams {
 struct F4 { float a[4]; };
 __device__ __forceinline__ F4 f4(const float4 t) { F4 r; r.a[0] = t.x; r.a[1] = t.y; r.a[2] = t.z; r.a[3] = t.w; return r; }
 __device__ __forceinline__ float4 t4(const F4 &r) { return make_float4(r.a[0], r.a[1], r.a[2], r.a[3]); }
-__device__ __forceinline__ F4 ld_nc(const float *p) { return f4(__ldg(reinterpret_cast<const float4 *>(p))); }
+// plain (coherent) 128-bit load: wavefields are written by the previous grid, which may still be running when this one
+// becomes resident under programmatic dependent launch - ld.global.nc is only for data that is read-only for the whole
+// lifetime of the grid (w, sigma, the index lists)
+__device__ __forceinline__ F4 ld_field(const float *p) { return f4(*reinterpret_cast<const float4 *>(p)); }
 __device__ __forceinline__ F4 lds4(const float *p) { return f4(*reinterpret_cast<const float4 *>(p)); }
 // masked store of 4 values starting at device column `col` of row pointer `row`
 template <bool STREAM>
@@ -280,7 +283,7 @@ __device__ __forceinline__ void march_ring(const StepParams &p, const Seg &sg, f
     // sliding window: inside iteration block b (first centre row z0), W[i] = u row z0 - H + i
     F4 W[2 * H + RB];
 #pragma unroll
-    for (int k = 0; k < 2 * H - RB; ++k) W[RB + k] = ld_nc(u + (size_t)(zb - H + k) * p.pitch + colL);
+    for (int k = 0; k < 2 * H - RB; ++k) W[RB + k] = ld_field(u + (size_t)(zb - H + k) * p.pitch + colL);
     F4 sy;
 #pragma unroll
     for (int j = 0; j < 4; ++j) sy.a[j] = PML ? __ldg(p.sigy + colL + j) : 0.f;
@@ -692,7 +695,7 @@ __global__ void __launch_bounds__(warps_per_cta(MODE) * 32, ctas_per_sm(MODE)) a
     for (int item = item0; item < total_smp; item += gridDim.x * blockDim.x) {
         const int s = item / p.n_smp;
         const int cell = item == item0 ? cell0 : __ldg(p.smp_cell + item);
-        float val = __ldg(p.u + (size_t)s * p.stride + cell);
+        float val = p.u[(size_t)s * p.stride + cell];      // (plain load: written by the previous grid)
         if (p.smp_div_a) {
             const int z = cell / p.pitch, y = cell - z * p.pitch;
             const float hs = p.hdt * (__ldg(p.sigz + z) + __ldg(p.sigy + y));

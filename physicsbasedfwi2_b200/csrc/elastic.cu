@@ -135,12 +135,12 @@ __device__ __forceinline__ float dminus_z_syz_fs(const float *f, int i, int j, i
 #define BYH(j) __ldg(p.py + 3 * p.nyp + (j))
 
 // ---- forward ------------------------------------------------------------------------------
-template <int H, bool SAVE>
+template <int H, bool SAVE, bool FS>
 __global__ void __launch_bounds__(256) elastic_f1(const EParams p) {
     ELASTIC_CELL();
     const float *sxx = p.f[SXX] + (long long)s * p.cells, *szz = p.f[SZZ] + (long long)s * p.cells,
                 *syz = p.f[SYZ] + (long long)s * p.cells;
-    const bool near_fs = p.fs_row && i < p.fs_row + H;
+    const bool near_fs = FS && i < p.fs_row + H;      // (FS is a template flag: the grids without a free surface keep their code)
     float d1 = dplus<H>(sxx, c0, 1, p.cy);
     float d2 = near_fs ? dminus_z_syz_fs<H>(syz, i, j, p.nyp, p.fs_row, p.cz) : dminus<H>(syz, c0, p.nyp, p.cz);
     float d3 = dminus<H>(syz, c0, 1, p.cy);
@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(256) elastic_f1(const EParams p) {
     }
 }
 
-template <int H, bool SAVE>
+template <int H, bool SAVE, bool FS>
 __global__ void __launch_bounds__(256) elastic_f2(const EParams p) {
     ELASTIC_CELL();
     const float *vy = p.f[VY] + (long long)s * p.cells, *vz = p.f[VZ] + (long long)s * p.cells;
@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(256) elastic_f2(const EParams p) {
     }
     const float e1 = d5, e2 = d6, e3 = d7 + d8;
     const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
-    if (p.fs_row && i == p.fs_row) {
+    if (FS && i == p.fs_row) {
         // on the free surface szz stays zero, which removes e2 from the sxx update: (l2m - lam^2 / l2m) e1
         p.f[SXX][o] = p.f[SXX][o] + p.dt * ((l2m - lam * lam / l2m) * e1);
     } else {
@@ -287,14 +287,14 @@ __device__ __forceinline__ float sm_dminus(const float *y, int st, const float *
     return s;
 }
 
-template <int H, int NT>
+template <int H, int NT, bool FS>
 __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b2_fused(const EParams p) {
     constexpr int SX = kTX + 2 * H, SZ = kTZ + 2 * H;
     constexpr int N1 = (SX * SZ + NT - 1) / NT, N2 = (kTX * kTZ) / NT;
     static_assert((kTX * kTZ) % NT == 0, "tile must be a multiple of the CTA size");
     __shared__ float Y[4][SZ * SX];
     const int s = blockIdx.z;
-    const int zs = p.fs_row ? p.fs_row : p.h;                               // first computational row
+    const int zs = FS ? p.fs_row : p.h;                                     // first computational row
     const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + zs;      // first own cell
     const long long fs = (long long)p.S * p.cells, so = (long long)s * p.cells;
     pdl_wait();
@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b2_fuse
             const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
             float ae1 = p.dt * (l2m * asxx + lam * aszz), ae2 = p.dt * (lam * asxx + l2m * aszz);
             const float ae3 = (p.dt * mu) * asyz;
-            if (p.fs_row && i == p.fs_row) {          // free-surface row: sxx += dt (l2m - lam^2 / l2m) e1, szz is not updated
+            if (FS && i == p.fs_row) {                // free-surface row: sxx += dt (l2m - lam^2 / l2m) e1, szz is not updated
                 ae1 = p.dt * ((l2m - lam * lam / l2m) * asxx);
                 ae2 = 0.f;
             }
@@ -360,7 +360,7 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b2_fuse
         const int t = threadIdx.x + q * NT;
         const int tz = t / kTX, tx = t - tz * kTX;
         const int l = (tz + H) * SX + tx + H;
-        if (p.fs_row && i0 + tz == p.fs_row) {
+        if (FS && i0 + tz == p.fs_row) {
             // images of the free-surface row: d/d l2m and d/d lam of (l2m - lam^2 / l2m) e1
             const long long c0 = o - so;
             const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0);
@@ -377,13 +377,13 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b2_fuse
     }
 }
 
-template <int H, int NT>
+template <int H, int NT, bool FS>
 __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b1_fused(const EParams p) {
     constexpr int SX = kTX + 2 * H, SZ = kTZ + 2 * H;
     constexpr int N1 = (SX * SZ + NT - 1) / NT, N2 = (kTX * kTZ) / NT;
     __shared__ float Y[4][SZ * SX];
     const int s = blockIdx.z;
-    const int zs = p.fs_row ? p.fs_row : p.h;
+    const int zs = FS ? p.fs_row : p.h;
     const int j0 = blockIdx.x * kTX + p.h, i0 = blockIdx.y * kTZ + zs;
     const long long fs = (long long)p.S * p.cells, so = (long long)s * p.cells;
     pdl_wait();
@@ -444,7 +444,7 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b1_fuse
         p.grad[4 * fs + o] = g4[q] + p.dt * (vz[q] * fz[q]);
         float nsy = sy[q] - (sm_dplus<H>(&Y[1][l], SX, p.cz) + sm_dplus<H>(&Y[2][l], 1, p.cy));
         float nsz = sz[q] - sm_dminus<H>(&Y[3][l], SX, p.cz);
-        if (p.fs_row && blockIdx.y == 0 && tz <= H) {
+        if (FS && blockIdx.y == 0 && tz <= H) {
             // free surface: F1 read the stresses above the surface as minus their mirror images, so a row next to the
             // surface also receives, with the opposite sign, what the transposed differences deliver to its mirror row
             // (the Y of rows above the surface are zero: those rows are not part of the system)
@@ -812,12 +812,12 @@ extern "C" int fwi_elastic_forward(const fwi_elastic_desc *d, const fwi_elastic_
             else launch_f_fused_h<false>(p, fgrid, st);
             fwi::count_launch();
         } else {
-            if (p.snap) {
-                ELASTIC_LAUNCH_H(elastic_f1, true);
-                ELASTIC_LAUNCH_H(elastic_f2, true);
+            if (p.fs_row) {
+                if (p.snap) { ELASTIC_LAUNCH_H(elastic_f1, true, true); ELASTIC_LAUNCH_H(elastic_f2, true, true); }
+                else { ELASTIC_LAUNCH_H(elastic_f1, false, true); ELASTIC_LAUNCH_H(elastic_f2, false, true); }
             } else {
-                ELASTIC_LAUNCH_H(elastic_f1, false);
-                ELASTIC_LAUNCH_H(elastic_f2, false);
+                if (p.snap) { ELASTIC_LAUNCH_H(elastic_f1, true, false); ELASTIC_LAUNCH_H(elastic_f2, true, false); }
+                else { ELASTIC_LAUNCH_H(elastic_f1, false, false); ELASTIC_LAUNCH_H(elastic_f2, false, false); }
             }
             fwi::count_launch(2);
         }
@@ -907,9 +907,10 @@ extern "C" int fwi_elastic_backward(const fwi_elastic_desc *d, const fwi_elastic
                 p.psi_out[k] = par ? a : c;
             }
             const dim3 block = fblock, grid = fgrid;
-            if (fnt == 256) { ELASTIC_LAUNCH_H(elastic_b2_fused, 256); ELASTIC_LAUNCH_H(elastic_b1_fused, 256); }
-            else if (fnt == 1024) { ELASTIC_LAUNCH_H(elastic_b2_fused, 1024); ELASTIC_LAUNCH_H(elastic_b1_fused, 1024); }
-            else { ELASTIC_LAUNCH_H(elastic_b2_fused, 512); ELASTIC_LAUNCH_H(elastic_b1_fused, 512); }
+            if (p.fs_row) { ELASTIC_LAUNCH_H(elastic_b2_fused, 512, true); ELASTIC_LAUNCH_H(elastic_b1_fused, 512, true); }
+            else if (fnt == 256) { ELASTIC_LAUNCH_H(elastic_b2_fused, 256, false); ELASTIC_LAUNCH_H(elastic_b1_fused, 256, false); }
+            else if (fnt == 1024) { ELASTIC_LAUNCH_H(elastic_b2_fused, 1024, false); ELASTIC_LAUNCH_H(elastic_b1_fused, 1024, false); }
+            else { ELASTIC_LAUNCH_H(elastic_b2_fused, 512, false); ELASTIC_LAUNCH_H(elastic_b1_fused, 512, false); }
             fwi::count_launch(2);
         } else {
             launch_pdl(elastic_b2a, grid, block, st, p);

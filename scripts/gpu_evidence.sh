@@ -21,6 +21,6 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --c
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:acoustic_step \
     --launch-skip 20 --launch-count 1 -o gpurun_out/fwd_full -f $CMD > gpurun_out/ncu_fwd.log 2>&1; echo "ncu fwd rc=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:acoustic_step \
-    --launch-skip 90 --launch-count 2 -o gpurun_out/adj_full -f $CMD > gpurun_out/ncu_adj.log 2>&1; echo "ncu adj rc=$?"
+    --launch-skip 90 --launch-count 4 -o gpurun_out/adj_full -f $CMD > gpurun_out/ncu_adj.log 2>&1; echo "ncu adj rc=$?"
 fi
 ls gpurun_out | head -50
