@@ -1,9 +1,10 @@
 #!/bin/bash
-# 8-GPU pass: shot-parallel C2, x-slab C4, end-to-end C5.  gpurun --gpus 8 --timeout 900 -- 'bash scripts/gpu_scale8.sh'
+# 8-GPU lines: shot-parallel default (= the 256-shot survey on 8 GPUs) and the x-slab variant; written to gpurun_out/
 set -u
 mkdir -p gpurun_out
-N=${N:-8}
-T="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-timeout 300 $T --master-port 29521 bench.py --gpus $N --steps 3 --warmup 3 --no-e2e > gpurun_out/bench_c2_$N.log 2>&1; echo "c2 rc=$?"; tail -1 gpurun_out/bench_c2_$N.log | cut -c1-160
-timeout 300 $T --master-port 29522 bench.py --gpus $N --workload c4dd --steps 2 --warmup 3 --no-e2e > gpurun_out/bench_c4dd_$N.log 2>&1; echo "c4dd rc=$?"; tail -1 gpurun_out/bench_c4dd_$N.log | cut -c1-160
-timeout 300 $T --master-port 29523 bench.py --gpus $N --workload c5 --steps 3 --warmup 3 > gpurun_out/bench_c5_$N.log 2>&1; echo "c5 rc=$?"; tail -1 gpurun_out/bench_c5_$N.log | cut -c1-160
+N=${1:-8}
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
+$TR --master-port 29521 bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/bench_c2_${N}gpu.log 2>&1; echo "c2 rc=$?"; grep '^{' gpurun_out/bench_c2_${N}gpu.log | tail -1 | cut -c1-260
+$TR --master-port 29522 bench.py --gpus $N --steps 2 --warmup 3 --workload c4dd > gpurun_out/bench_c4dd_${N}gpu.log 2>&1; echo "c4dd rc=$?"; grep '^{' gpurun_out/bench_c4dd_${N}gpu.log | tail -1 | cut -c1-260
+$TR --master-port 29523 bench.py --gpus $N --steps 2 --warmup 3 --workload c5 > gpurun_out/bench_c5_${N}gpu.log 2>&1; echo "c5 rc=$?"; grep '^{' gpurun_out/bench_c5_${N}gpu.log | tail -1 | cut -c1-260
+$TR --master-port 29524 bench.py --impl reference --gpus $N --steps 1 --warmup 1 > gpurun_out/bench_reference_${N}gpu.log 2>&1; grep '^{' gpurun_out/bench_reference_${N}gpu.log | tail -1 | cut -c1-200
