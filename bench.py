@@ -290,7 +290,8 @@ def bench_config(w, batch, world, name):
     return {"workload": f"{name}: 2-D {'elastic P-SV' if w.get('elastic') else 'acoustic'} {w['nz']}x{w['ny']} dx={w['dx']}m order {w['order']} "
                         f"pml {w['pml']} nt {w['nt']} dt {w['dt']} {w['freq']}Hz Ricker, "
                         f"{w['n_rec']} receivers/shot, fwd+adjoint gradient (MSE), "
-                        + (f"wavefield checkpoint every {w['ckpt']} steps + recompute" if w.get("ckpt") else "snapshot every step"),
+                        + (f"wavefield checkpoint every {w['ckpt']} steps + recompute" if w.get("ckpt") else
+                           "snapshot every step" if w.get("save_every", 1) == 1 else f"snapshot every {w['save_every']} steps (decimated imaging)"),
             "shots_per_gpu_per_step": batch, "shots_per_step": batch * (1 if w.get("slabs") else world),
             "survey_shots": w["survey_shots"],
             "parallelism": (f"x-slab domain decomposition x{world}, ghost exchange every {w['slabs']} steps"
@@ -588,7 +589,8 @@ def run_gpu(args, w, dev, rank, world, local):
     P = w["pml"] + w["order"] // 2
     nti = nt * (1 if elastic else _host.inner_step(w["dt"], w["dx"], w["dx"], w["vmax"])[0])
     # shots per launch: one q snapshot per inner step per shot must fit HBM next to the wavefields
-    per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nti + 8) * (5 if elastic else 1)
+    kq = w.get("save_every", 1)
+    per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (nti // kq + 8) * (5 if elastic else 1)
     if w.get("ckpt"):
         per_shot = (nz + 2 * P) * (ny + 2 * P + 64) * 4 * (6 * (nti // w["ckpt"] + 2) + w["ckpt"] + 24)
     if slabs:
@@ -597,7 +599,7 @@ def run_gpu(args, w, dev, rank, world, local):
     free, _ = torch.cuda.mem_get_info(dev)
     # 6 shots per launch is where the C2 kernel pair was tuned (7 fit, but leave the allocator no slack)
     full_nt = WORKLOADS[args.workload]["nt"]              # the cap must not change with a --nt override (ncu runs)
-    cap = 16 if (w.get("ckpt") or per_shot * (full_nt / nt) < (2 << 30)) else 6
+    cap = 16 if (w.get("ckpt") or per_shot * (full_nt / nt) < (2 << 30)) else (6 if kq == 1 else 12)
     cap = args.shots or max(1, min(cap, w["survey_shots"], int((0.6 if w.get("ckpt") else 0.88) * free // per_shot)))
 
     # shots of one step on this rank.  Default for the shot-parallel acoustic survey (C2): the 1/8 slice of the
@@ -637,7 +639,7 @@ def run_gpu(args, w, dev, rank, world, local):
                                   accuracy=w["order"], vpmax=w["vmax"], checkpoint_every=w.get("ckpt", 0))
         else:
             prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"],
-                              checkpoint_every=w.get("ckpt", 0), slabs=slabs and world > 1,
+                              checkpoint_every=w.get("ckpt", 0), save_every=kq, slabs=slabs and world > 1,
                               halo_steps=w.get("slabs") or 8)
         rec = prop(src_d, xs_d, xr_d, w["dt"])
         loss = 0.5 * ((rec - obs_d) ** 2).sum()
@@ -729,7 +731,7 @@ def run_gpu(args, w, dev, rank, world, local):
     # ---- roofline from the native time loops of the timed region (CUDA events on the launching stream) ----
     # per pass: algorithmic bytes per cell-update: forward + snapshot 20 B, adjoint + imaging 28 B,
     # forward only (checkpoint pass, MODE 0) 16 B; elastic 80 / 120 B
-    bytes_of = {"acoustic_fwd": B_FWD, "acoustic_fwd0": 16.0, "acoustic_adj": B_ADJ,
+    bytes_of = {"acoustic_fwd": 16.0 + 4.0 / kq, "acoustic_fwd0": 16.0, "acoustic_adj": 16.0 + 12.0 / kq,
                 "elastic_fwd": B_FWD_EL, "elastic_adj": B_ADJ_EL}
     div = world if slabs else 1                          # a slab launch advances 1/world of each shot
     agg = {}
@@ -847,6 +849,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg")
     ap.add_argument("--pml", type=int, default=-1, help="override the PML width (tuning only: 0 = PML-free grid)")
+    ap.add_argument("--save-every", type=int, default=1, help="snapshot decimation k (performance mode; k = 1 is the parity-graded default)")
     ap.add_argument("--survey", action="store_true", help="one step = the WHOLE survey sharded over the ranks (strong scaling)")
     ap.add_argument("--one-batch", action="store_true", help="c2: one launch of shots per step instead of the 32-shot slice")
     ap.add_argument("--no-check", action="store_true", help="skip the multi-GPU correctness check ahead of the timed region")
@@ -860,6 +863,7 @@ def main():
         w["nt"] = args.nt
     if args.pml >= 0:
         w["pml"] = args.pml
+    w["save_every"] = max(1, args.save_every)
 
     if args.impl == "reference":
         run_reference(args, w)

@@ -55,7 +55,9 @@ typedef struct fwi_acoustic_desc {
     int32_t smp_div_a;        /* 1: sampled value divided by a (adjoint source gradient) */
     double dz, dy, dt;        /* grid spacings (m) and inner time step (s) */
     int32_t flags;            /* FWI_FLAG_* */
-    int32_t reserved;
+    int32_t save_every;       /* k > 1: snapshot decimation - q_write / q_read hold ceil(nsteps / k) snapshots, those
+                                 of the steps n with n % k == 0, and only those steps are imaged (the caller weighs the image by k);
+                                 0 or 1: every step (the parity-graded mode) */
 } fwi_acoustic_desc;
 
 #define FWI_FLAG_NO_PDL 1     /* plain launches instead of programmatic dependent launches: for jobs that share the device with

@@ -53,10 +53,12 @@ def _ptr(a: Optional[np.ndarray]):
 
 def run(np_dtype, nzp, nyp, order, pml_width, S, dz, dy, dt, w, sigz, sigy, nsteps, adjoint,
         inj_cell, inj_amp, inj_scale_a, smp_cell, smp_div_a, q_write=None, q_read=None, G=None,
-        u_final=None, state=None):
+        u_final=None, state=None, save_every=1):
     """Thin call of fwi_oracle_acoustic_run[_state]_{f32,f64}; returns smp_out [nsteps, S, n_smp].
     `state` [6, S, nzp*nyp] (u, u-, pz, -, py, -) is read and left updated when given."""
-    f = getattr(lib(), "fwi_oracle_acoustic_run_" + ("state_" if state is not None else "")
+    if save_every > 1:
+        assert state is None and u_final is None
+    f = getattr(lib(), "fwi_oracle_acoustic_run_" + ("state_" if state is not None else "k_" if save_every > 1 else "")
                 + ("f32" if np_dtype == np.float32 else "f64"))
     f.restype = ctypes.c_int
     n_inj = 0 if inj_cell is None else inj_cell.shape[1]
@@ -71,7 +73,8 @@ def run(np_dtype, nzp, nyp, order, pml_width, S, dz, dy, dt, w, sigz, sigy, nste
            _ptr(w), _ptr(sigz), _ptr(sigy), ctypes.c_int(nsteps), ctypes.c_int(adjoint),
            ctypes.c_int(n_inj), _ptr(inj_cell), _ptr(inj_amp), ctypes.c_int(inj_scale_a),
            ctypes.c_int(n_smp), _ptr(smp_cell), _ptr(smp_out), ctypes.c_int(smp_div_a),
-           _ptr(q_write), _ptr(q_read), _ptr(G), _ptr(state if state is not None else u_final))
+           _ptr(q_write), _ptr(q_read), _ptr(G),
+           ctypes.c_int(save_every) if save_every > 1 else _ptr(state if state is not None else u_final))
     if rc != 0:
         raise RuntimeError(f"fwi_oracle_acoustic_run failed rc={rc}")
     return smp_out
@@ -116,15 +119,17 @@ def _buffer(workspace, name, shape, dtype):
 
 
 def acoustic_forward(v, dx, source_amplitudes, x_s, x_r, dt, *, order=4, pml_width=10,
-                     vpmax=None, loc_mode="trunc", dtype=torch.float64, save=False, workspace=None):
+                     vpmax=None, loc_mode="trunc", dtype=torch.float64, save=False, workspace=None, save_every=1):
     su = AcousticSetup(v, dx, dt, order, pml_width, vpmax, dtype)
+    su.save_every = max(1, int(save_every))
     nt, S, _ = source_amplitudes.shape
     amp = T.upsample(source_amplitudes.detach().to(dtype), su.ratio).contiguous().numpy()
     nti = nt * su.ratio
     sc, rc = su.cells(x_s, loc_mode), su.cells(x_r, loc_mode)
-    q = _buffer(workspace, "q", (nti, S, su.nzp * su.nyp), su.npdtype) if save else None
+    nq = -(-nti // su.save_every)
+    q = _buffer(workspace, "q", (nq, S, su.nzp * su.nyp), su.npdtype) if save else None
     rec = run(su.npdtype, su.nzp, su.nyp, order, pml_width, S, su.dz, su.dy, su.dti, su.w,
-              su.sigz, su.sigy, nti, 0, sc, amp, 0, rc, 0, q_write=q)
+              su.sigz, su.sigy, nti, 0, sc, amp, 0, rc, 0, q_write=q, save_every=su.save_every)
     rec = torch.from_numpy(rec[::su.ratio].copy())
     if save:
         return rec, (su, q, sc, rc, amp)
@@ -142,9 +147,10 @@ def acoustic_adjoint(state, grad_rec, source_amplitudes, dtype=torch.float64):
     g_in[::su.ratio] = g.numpy()
     G = np.zeros((S, su.nzp * su.nyp), dtype=su.npdtype)
     gs = run(su.npdtype, su.nzp, su.nyp, su.order, su.pw, S, su.dz, su.dy, su.dti, su.w,
-             su.sigz, su.sigy, nti, 1, rc, g_in, 1, sc, 1, q_read=q, G=G)
+             su.sigz, su.sigy, nti, 1, rc, g_in, 1, sc, 1, q_read=q, G=G, save_every=getattr(su, "save_every", 1))
     # dJ/dv_pad = (2 / v_pad) * (G + scatter_src(sum_n gs_n * s_n)), then fold the replicate pad
-    Gt = torch.from_numpy(G).sum(0)
+    # (save_every = k: the image holds every k-th product; rectangle rule, weight k)
+    Gt = torch.from_numpy(G).sum(0) * getattr(su, "save_every", 1)
     gs_t = torch.from_numpy(gs)                                     # [nti, S, Ns]
     src_term = (gs_t * torch.from_numpy(amp)).sum(0).reshape(-1)    # [S*Ns]
     Gt = Gt.index_add(0, torch.from_numpy(sc.reshape(-1).astype(np.int64)), src_term)
@@ -158,11 +164,13 @@ def acoustic_adjoint(state, grad_rec, source_amplitudes, dtype=torch.float64):
 
 
 def acoustic_gradient(v, dx, source_amplitudes, x_s, x_r, dt, grad_rec=None, observed=None, *,
-                      order=4, pml_width=10, vpmax=None, loc_mode="trunc", dtype=torch.float64, workspace=None):
-    """Returns (rec, grad_v [nz, ny], grad_src [nt, S, Ns]) with the hand-written adjoint."""
+                      order=4, pml_width=10, vpmax=None, loc_mode="trunc", dtype=torch.float64, workspace=None,
+                      save_every=1):
+    """Returns (rec, grad_v [nz, ny], grad_src [nt, S, Ns]) with the hand-written adjoint.  save_every = k > 1: the
+    decimated imaging condition of SURVEY.md 7.0 (snapshots and products every k-th inner step, weight k)."""
     rec, state = acoustic_forward(
         v, dx, source_amplitudes, x_s, x_r, dt, order=order, pml_width=pml_width, vpmax=vpmax,
-        loc_mode=loc_mode, dtype=dtype, save=True, workspace=workspace)
+        loc_mode=loc_mode, dtype=dtype, save=True, workspace=workspace, save_every=save_every)
     g = grad_rec.to(dtype) if grad_rec is not None else (rec - observed.to(dtype))
     grad_v, grad_s = acoustic_adjoint(state, g, source_amplitudes, dtype)
     return rec, grad_v, grad_s

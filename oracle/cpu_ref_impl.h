@@ -84,7 +84,10 @@ static int NAME(acoustic_run_core)(int nzp, int nyp, int order, int pml_width, i
                                   const int *inj_cell, const REAL *inj_amp, int inj_scale_a,
                                   int n_smp, const int *smp_cell, REAL *smp_out, int smp_div_a,
                                   REAL *q_write, const REAL *q_read, REAL *G, REAL *u_final,
-                                  REAL *state) {
+                                  REAL *state, int save_every) {
+    /* save_every = k > 1 (snapshot decimation): q is written / read and the image accumulated only at
+     * steps n with n % k == 0, snapshot index n / k; the caller scales the image by k (rectangle rule) */
+    const int k_img = save_every > 1 ? save_every : 1;
     if (order != 2 && order != 4 && order != 6 && order != 8) return 1;
     const int h = order / 2;
     if (nzp <= 2 * h || nyp <= 2 * h || S < 1 || nsteps < 0) return 1;
@@ -136,8 +139,9 @@ static int NAME(acoustic_run_core)(int nzp, int nyp, int order, int pml_width, i
             for (int z = h; z < nzp - h; ++z) {
                 const REAL *us = u + s * cells;
                 REAL *ums = um + s * cells;
-                REAL *qw = q_write ? q_write + ((size_t)n * S + s) * cells : NULL;
-                const REAL *qr = q_read ? q_read + ((size_t)n * S + s) * cells : NULL;
+                const int img = (n % k_img) == 0;
+                REAL *qw = (q_write && img) ? q_write + ((size_t)(n / k_img) * S + s) * cells : NULL;
+                const REAL *qr = (q_read && img) ? q_read + ((size_t)(n / k_img) * S + s) * cells : NULL;
                 REAL *Gs = G ? G + s * cells : NULL;
                 if (!Gs) qr = NULL;
                 const int pml_row = (pml_width > 0) && (z < zlo || z >= zhi);
@@ -194,7 +198,19 @@ int NAME(fwi_oracle_acoustic_run)(int nzp, int nyp, int order, int pml_width, in
                                   REAL *q_write, const REAL *q_read, REAL *G, REAL *u_final) {
     return NAME(acoustic_run_core)(nzp, nyp, order, pml_width, S, dz, dy, dt, w, sigz, sigy, nsteps,
                                    adjoint, n_inj, inj_cell, inj_amp, inj_scale_a, n_smp, smp_cell,
-                                   smp_out, smp_div_a, q_write, q_read, G, u_final, NULL);
+                                   smp_out, smp_div_a, q_write, q_read, G, u_final, NULL, 1);
+}
+
+/* Same with snapshot decimation: q_write / q_read hold ceil(nsteps / save_every) snapshots. */
+int NAME(fwi_oracle_acoustic_run_k)(int nzp, int nyp, int order, int pml_width, int S, double dz,
+                                  double dy, double dt, const REAL *w, const REAL *sigz,
+                                  const REAL *sigy, int nsteps, int adjoint, int n_inj,
+                                  const int *inj_cell, const REAL *inj_amp, int inj_scale_a,
+                                  int n_smp, const int *smp_cell, REAL *smp_out, int smp_div_a,
+                                  REAL *q_write, const REAL *q_read, REAL *G, int save_every) {
+    return NAME(acoustic_run_core)(nzp, nyp, order, pml_width, S, dz, dy, dt, w, sigz, sigy, nsteps,
+                                   adjoint, n_inj, inj_cell, inj_amp, inj_scale_a, n_smp, smp_cell,
+                                   smp_out, smp_div_a, q_write, q_read, G, NULL, NULL, save_every);
 }
 
 /* Same, continuing from (and leaving) the state [6][S][nzp*nyp] = u, u-, pz, -, py, - : lets a
@@ -208,5 +224,5 @@ int NAME(fwi_oracle_acoustic_run_state)(int nzp, int nyp, int order, int pml_wid
     if (!state) return 1;
     return NAME(acoustic_run_core)(nzp, nyp, order, pml_width, S, dz, dy, dt, w, sigz, sigy, nsteps,
                                    adjoint, n_inj, inj_cell, inj_amp, inj_scale_a, n_smp, smp_cell,
-                                   smp_out, smp_div_a, q_write, q_read, G, NULL, state);
+                                   smp_out, smp_div_a, q_write, q_read, G, NULL, state, 1);
 }

@@ -23,7 +23,7 @@ class AcousticDesc(C.Structure):
                 ("pml_width", C.c_int32), ("n_shots", C.c_int32), ("chunk_rows", C.c_int32),
                 ("nsteps", C.c_int32), ("adjoint", C.c_int32), ("n_inj", C.c_int32),
                 ("inj_scale_a", C.c_int32), ("n_smp", C.c_int32), ("smp_div_a", C.c_int32),
-                ("dz", C.c_double), ("dy", C.c_double), ("dt", C.c_double), ("flags", C.c_int32), ("reserved", C.c_int32)]
+                ("dz", C.c_double), ("dy", C.c_double), ("dt", C.c_double), ("flags", C.c_int32), ("save_every", C.c_int32)]
 
 
 class AcousticLayout(C.Structure):

@@ -766,6 +766,7 @@ int check_desc(const fwi_acoustic_desc *d) {
     FWI_CHECK_ARG(d->n_inj >= 0 && d->n_smp >= 0, "negative point counts");
     FWI_CHECK_ARG(d->dz > 0 && d->dy > 0 && d->dt != 0, "dz, dy must be > 0 and dt != 0");
     FWI_CHECK_ARG(d->chunk_rows >= 0, "chunk_rows must be >= 0");
+    FWI_CHECK_ARG(d->save_every >= 0, "save_every must be >= 0");
     return FWI_OK;
 }
 
@@ -1231,7 +1232,7 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     // ---- small grids: the whole time loop as one cluster-resident kernel (acoustic_small.cu) ----
     const int small_on = env_int("FWI_B200_SMALL", 1);      // read per call: tests switch paths in-process
     static const int small_cells = env_int("FWI_B200_SMALL_CELLS", 1500000);
-    if (small_on && !link && !getenv("FWI_B200_TRACE") && d->chunk_rows == 0 && (mode != 2 || d->adjoint) && b->q_step_stride == 0 &&
+    if (small_on && !link && !getenv("FWI_B200_TRACE") && d->chunk_rows == 0 && (mode != 2 || d->adjoint) && b->q_step_stride == 0 && d->save_every <= 1 &&
         (int64_t)d->n_shots * d->nzp * d->nyp <= small_cells) {
         fwi::SmallParams sp = {};
         sp.nzp = d->nzp; sp.nyp = d->nyp; sp.pitch = g.pitch; sp.col0 = g.col0; sp.h = h; sp.pw = d->pml_width;
@@ -1263,12 +1264,13 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     // alternate between an advance-only launch (MODE 0, 16 B per cell) and a launch that images both steps (MODE 3),
     // the additions to G staying in the order one imaging per step makes them - results are bit-identical.  An odd
     // last iteration images alone (MODE 2).  FWI_B200_PAIR=0 keeps one imaging per step.
-    const bool pair = mode == 2 && env_int("FWI_B200_PAIR", 1) != 0 && d->nsteps >= 2;
+    const int kimg = d->save_every > 1 ? d->save_every : 1;          // snapshot decimation: image / snapshot every kimg-th step
+    const bool pair = mode == 2 && kimg == 1 && env_int("FWI_B200_PAIR", 1) != 0 && d->nsteps >= 2;
     int sms = 0;
     struct Table { int mode, n_units, blocks; Seg *d_segs; int *d_units; };
     Table tables[3];
     int n_tables = 0;
-    const int want[3] = {pair ? 0 : mode, pair ? 3 : -1, pair && (d->nsteps & 1) ? 2 : -1};
+    const int want[3] = {pair ? 0 : mode, pair ? 3 : (kimg > 1 && mode != 0 ? 0 : -1), pair && (d->nsteps & 1) ? 2 : -1};
     thread_local std::vector<Col> cols;
     thread_local std::vector<Seg> segs;
     thread_local std::vector<int> unit_start;
@@ -1335,7 +1337,7 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
     const int n_fields = d->pml_width > 0 ? 6 : 2;
     // rows between the snapshots of consecutive steps (a call on a subset of the shots of a snapshot array: q_step_stride)
     const int64_t q_rows = b->q_step_stride > 0 ? b->q_step_stride / g.pitch : fld_rows;
-    const int64_t q_map_rows = (int64_t)(d->nsteps - 1) * q_rows + fld_rows;
+    const int64_t q_map_rows = (int64_t)((d->nsteps - 1) / kimg) * q_rows + fld_rows;
     FWI_CHECK_ARG(q_map_rows < (int64_t)1 << 31, "snapshot tensor has too many rows for one TMA descriptor");
     if ((rc = make_map(&p.tm_wave_u, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kRowU)) != FWI_OK) return rc;
     if ((rc = make_map(&p.tm_wave_o, b->wave, (int64_t)n_fields * fld_rows, g.pitch, kRowO)) != FWI_OK) return rc;
@@ -1400,16 +1402,19 @@ static int run_impl(const fwi_acoustic_desc *d, const fwi_acoustic_buffers *b, c
         p.row_um = (int)((um - b->wave) / g.pitch);
         p.row_pz = pz ? (int)((pz - b->wave) / g.pitch) : 0;
         p.row_py = py ? (int)((py - b->wave) / g.pitch) : 0;
-        p.row_q = (int)(n * q_rows);
-        p.row_q2 = (int)((n + 1) * q_rows);
-        // which launch this iteration is: see the comment on `pair` above
+        const int nq = n / kimg;                          // snapshot index of this step
+        p.row_q = (int)(nq * q_rows);
+        p.row_q2 = (int)((nq + 1) * q_rows);
+        // which launch this iteration is: see the comment on `pair` above; with decimation only every kimg-th step
+        // writes / images a snapshot, the others advance only
         int m = mode;
         if (pair) m = (it & 1) ? 3 : (it + 1 < d->nsteps ? 0 : 2);
+        else if (kimg > 1 && n % kimg != 0) m = 0;
         const Table &T = table_of(m);
         p.segs = T.d_segs; p.unit_start = T.d_units; p.n_units = T.n_units;
         const int blocks = T.blocks;
-        p.qw = b->q_write ? b->q_write + (size_t)n * (b->q_step_stride > 0 ? (size_t)b->q_step_stride : fld) : nullptr;
-        p.qr = b->q_read ? b->q_read + (size_t)n * (b->q_step_stride > 0 ? (size_t)b->q_step_stride : fld) : nullptr;
+        p.qw = b->q_write ? b->q_write + (size_t)nq * (b->q_step_stride > 0 ? (size_t)b->q_step_stride : fld) : nullptr;
+        p.qr = b->q_read ? b->q_read + (size_t)nq * (b->q_step_stride > 0 ? (size_t)b->q_step_stride : fld) : nullptr;
         p.G = b->image;
         p.inj_amp = d->n_inj ? b->inj_amp + (size_t)n * d->n_shots * d->n_inj : nullptr;
         p.smp_out = d->n_smp ? b->smp_out + (size_t)n * d->n_shots * d->n_smp : nullptr;

@@ -125,7 +125,7 @@ Tensor scalar_run(const Tensor &w, const Tensor &sigz, const Tensor &sigy, Tenso
                   const Tensor &inj_cell, const Tensor &inj_col, const Tensor &inj_amp, const Tensor &smp_cell,
                   const c10::optional<Tensor> &q_write, const c10::optional<Tensor> &q_read, const c10::optional<Tensor> &image,
                   const Tensor &meta, int64_t n_shots, int64_t nsteps, bool adjoint, int64_t order, int64_t pml, double dz,
-                  double dy, int64_t chunk_rows, int64_t q_step_stride) {
+                  double dy, int64_t chunk_rows, int64_t q_step_stride, int64_t save_every) {
     TORCH_CHECK(w.is_cuda() && wave.is_cuda(), "scalar_run needs CUDA tensors: there is no CPU path");
     const double *m = meta.data_ptr<double>();
     c10::cuda::CUDAGuard guard(w.device());
@@ -137,6 +137,7 @@ Tensor scalar_run(const Tensor &w, const Tensor &sigz, const Tensor &sigy, Tenso
     d.n_smp = smp_cell.defined() && smp_cell.numel() ? (int32_t)smp_cell.size(1) : 0;
     d.smp_div_a = adjoint ? 1 : 0;
     d.dz = dz; d.dy = dy; d.dt = m[2];
+    d.save_every = (int32_t)save_every;
     TORCH_CHECK(wave.numel() == (int64_t)m[7] * n_shots * (int64_t)m[8], "wave workspace has the wrong size");
     TORCH_CHECK(d.n_inj == 0 || (inj_amp.is_contiguous() && inj_amp.size(0) == nsteps && inj_amp.size(1) == n_shots),
                 "injection amplitudes must be contiguous [nsteps, n_shots, n]");
@@ -167,7 +168,7 @@ std::vector<Tensor> scalar_run_multi(const Tensor &w, const Tensor &sigz, const 
                                      at::TensorList inj_amp, at::TensorList smp_cell, const c10::optional<Tensor> &q_write,
                                      const c10::optional<Tensor> &q_read, const c10::optional<Tensor> &image,
                                      at::IntArrayRef shot0, const Tensor &meta, int64_t n_total, int64_t nsteps, bool adjoint,
-                                     int64_t order, int64_t pml, double dz, double dy, int64_t chunk_rows) {
+                                     int64_t order, int64_t pml, double dz, double dy, int64_t chunk_rows, int64_t save_every) {
     const size_t J = wave.size();
     TORCH_CHECK(J >= 1 && J <= 16 && inj_start.size() == J && inj_cell.size() == J && inj_col.size() == J &&
                 inj_amp.size() == J && smp_cell.size() == J && shot0.size() == J, "one entry per shot group expected");
@@ -201,6 +202,7 @@ std::vector<Tensor> scalar_run_multi(const Tensor &w, const Tensor &sigz, const 
         d.inj_scale_a = d.smp_div_a = adjoint ? 1 : 0;
         d.n_smp = smp_cell[j].numel() ? (int32_t)smp_cell[j].size(1) : 0;
         d.dz = dz; d.dy = dy; d.dt = m[2];
+        d.save_every = (int32_t)save_every;
         // programmatic dependent launches stay on (measured on C2, two adjoint groups: 46.9 us per step with, 48.6 without;
         // FWI_B200_MULTI_PDL=0 switches them off for the groups)
         static const bool multi_pdl = !(getenv("FWI_B200_MULTI_PDL") && atoi(getenv("FWI_B200_MULTI_PDL")) == 0);
@@ -296,11 +298,11 @@ TORCH_LIBRARY(b200fwi, m) {
           "bool loc_round, int c0, int c1) -> (Tensor, Tensor, Tensor, Tensor)");
     m.def("scalar_run(Tensor w, Tensor sigz, Tensor sigy, Tensor(a!) wave, Tensor inj_start, Tensor inj_cell, Tensor inj_col, "
           "Tensor inj_amp, Tensor smp_cell, Tensor(b!)? q_write, Tensor? q_read, Tensor(c!)? image, Tensor meta, int n_shots, "
-          "int nsteps, bool adjoint, int order, int pml, float dz, float dy, int chunk_rows, int q_step_stride=0) -> Tensor");
+          "int nsteps, bool adjoint, int order, int pml, float dz, float dy, int chunk_rows, int q_step_stride=0, int save_every=1) -> Tensor");
     m.def("scalar_run_multi(Tensor w, Tensor sigz, Tensor sigy, Tensor(a!)[] wave, Tensor[] inj_start, Tensor[] inj_cell, "
           "Tensor[] inj_col, Tensor[] inj_amp, Tensor[] smp_cell, Tensor(b!)? q_write, Tensor? q_read, Tensor(c!)? image, "
           "int[] shot0, Tensor meta, int n_total, int nsteps, bool adjoint, int order, int pml, float dz, float dy, "
-          "int chunk_rows) -> Tensor[]");
+          "int chunk_rows, int save_every=1) -> Tensor[]");
     m.def("scalar_fold(Tensor image, Tensor? gs, Tensor? amp, Tensor src_cell, Tensor v, Tensor meta, int n_shots, int order, "
           "int pml, float dz, float dy) -> Tensor");
     m.def("flag_begin(Tensor bad) -> Tensor");

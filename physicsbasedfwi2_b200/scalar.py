@@ -200,7 +200,7 @@ class _ScalarFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, v, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, loc_mode,
-                chunk_rows, checkpoint_every=0):
+                chunk_rows, checkpoint_every=0, save_every=1):
         if source_amplitudes.dim() != 3:
             raise RuntimeError("source_amplitudes must be [nt, n_shots, n_sources_per_shot]")
         nt, S, Ns = source_amplitudes.shape
@@ -250,7 +250,7 @@ class _ScalarFunction(torch.autograd.Function):
             ev = _lib.time_loop_begin(cur)
             out = O.scalar_run(w, sigz, sigy, wave, *fplans[gi], famps[gi][t0:t0 + nsteps], r_cell[s0:s1],
                                None if q_write is None else q_write[s0 * stride:], None, None, meta, s1 - s0, nsteps, False,
-                               *geo, int(chunk_rows), 0 if (one or q_write is None) else S * stride)
+                               *geo, int(chunk_rows), 0 if (one or q_write is None) else S * stride, kq)
             _lib.time_loop_end(cur, ev, "acoustic_fwd" if q_write is not None else "acoustic_fwd0", nsteps, s1 - s0)
             return out
 
@@ -258,9 +258,12 @@ class _ScalarFunction(torch.autograd.Function):
             return torch.zeros(n_fields * (fgroups[gi][1] - fgroups[gi][0]) * stride, dtype=torch.float32, device=dev)
 
         q, K = None, int(checkpoint_every)
+        kq = max(1, int(save_every))            # snapshot decimation: every kq-th inner step is stored and imaged
         ctx.ckpt = None
         with torch.cuda.device(dev):
             if need_v and 0 < K < nti:
+                if kq > 1:
+                    raise RuntimeError("save_every and checkpoint_every cannot be combined")
                 # wavefield checkpointing: keep the state every K steps instead of a snapshot per step;
                 # backward() recomputes the snapshots of one segment at a time
                 ckpts, recs = [], []
@@ -277,7 +280,7 @@ class _ScalarFunction(torch.autograd.Function):
                 ctx.ckpt = (K, ckpts)
             else:
                 if need_v:
-                    q = torch.empty(nti * S * stride, dtype=torch.float32, device=dev)
+                    q = torch.empty(-(-nti // kq) * S * stride, dtype=torch.float32, device=dev)
                 if one or os.environ.get("FWI_B200_MULTI", "0") != "1":
                     recs = [run(gi, 0, nti, new_wave(gi), q) for gi in range(len(fgroups))]
                 else:
@@ -285,7 +288,7 @@ class _ScalarFunction(torch.autograd.Function):
                     recs = list(O.scalar_run_multi(w, sigz, sigy, [new_wave(gi) for gi in range(len(fgroups))],
                                                    [p[0] for p in fplans], [p[1] for p in fplans], [p[2] for p in fplans], famps,
                                                    [r_cell[s0:s1] for s0, s1 in fgroups], q, None, None,
-                                                   [s0 for s0, _ in fgroups], meta, S, nti, False, *geo, int(chunk_rows)))
+                                                   [s0 for s0, _ in fgroups], meta, S, nti, False, *geo, int(chunk_rows), kq))
                     _lib.time_loop_end(cur, ev, "acoustic_fwd" if q is not None else "acoustic_fwd0", nti, S)
                 rec = recs[0] if one else torch.cat(recs, 1)
         O.flag_end(flag)
@@ -293,7 +296,7 @@ class _ScalarFunction(torch.autograd.Function):
         ctx.saved = (vd, meta, w, sigz, sigy, s_cell, r_cell, r_start, r_sc, r_so, s_start, s_sc, s_so)
         ctx.q = q
         ctx.amp = amp if need_v else None
-        ctx.dims = (nt, S, Ns, R, nti, ratio, n_fields, stride, geo, int(chunk_rows))
+        ctx.dims = (nt, S, Ns, R, nti, ratio, n_fields, stride, geo, int(chunk_rows), kq)
         ctx.need = (need_v, need_s)
         ctx.src_like = source_amplitudes.detach()
         ctx.x_r, ctx.rnd = x_r, rnd
@@ -305,7 +308,7 @@ class _ScalarFunction(torch.autograd.Function):
     def backward(ctx, grad_rec):
         O = _lib.ops()
         vd, meta, w, sigz, sigy, s_cell, r_cell, r_start, r_sc, r_so, s_start, s_sc, s_so = ctx.saved
-        nt, S, Ns, R, nti, ratio, n_fields, stride, geo, chunk_rows = ctx.dims
+        nt, S, Ns, R, nti, ratio, n_fields, stride, geo, chunk_rows, kq = ctx.dims
         need_v, need_s = ctx.need
         dev = vd.device
         g = grad_rec.to(dev, torch.float32)
@@ -337,11 +340,11 @@ class _ScalarFunction(torch.autograd.Function):
             ev = _lib.time_loop_begin(cur)
             if a_one:
                 out = O.scalar_run(w, sigz, sigy, awaves[0], *aplans[0], amps[0].contiguous(), s_cell, None, q_read,
-                                   image if q_read is not None else None, meta, S, nsteps, True, *geo, chunk_rows)
+                                   image if q_read is not None else None, meta, S, nsteps, True, *geo, chunk_rows, 0, kq)
             else:
                 parts = O.scalar_run_multi(w, sigz, sigy, awaves, [p[0] for p in aplans], [p[1] for p in aplans],
                                            [p[2] for p in aplans], amps, [s_cell[s0:s1] for s0, s1 in agroups], None, q_read,
-                                           image, [s0 for s0, _ in agroups], meta, S, nsteps, True, *geo, chunk_rows)
+                                           image, [s0 for s0, _ in agroups], meta, S, nsteps, True, *geo, chunk_rows, kq)
                 out = torch.cat(list(parts), 1)
             _lib.time_loop_end(cur, ev, "acoustic_adj", nsteps, S)
             return out
@@ -368,13 +371,15 @@ class _ScalarFunction(torch.autograd.Function):
                 gs = run_adjoint(0, nti, ctx.q if need_v else None)
             grad_v = grad_s = None
             if need_v:
+                if kq > 1:
+                    image.mul_(float(kq))       # rectangle rule over the decimated products
                 # dJ/dv = fold((2 / v_pad) (sum_s image_s + source term)): one native call (csrc/host_kernels.cu)
                 grad_v = O.scalar_fold(image, gs, ctx.amp, s_cell, vd, meta, S, *geo)
         if need_s:
             grad_s = H.resample_up_adjoint(gs, ratio, ctx.src_like.to(dev, torch.float32))
             grad_s = grad_s.to(ctx.src_like.device, ctx.src_like.dtype)
         ctx.q = None
-        return grad_v, grad_s, None, None, None, None, None, None, None, None, None, None
+        return grad_v, grad_s, None, None, None, None, None, None, None, None, None, None, None
 
 
 class Propagator(torch.nn.Module):
@@ -388,6 +393,8 @@ class Propagator(torch.nn.Module):
     ``checkpoint_every`` (K > 0: wavefield checkpointing - the forward pass keeps the state every K
     inner steps instead of one snapshot per step, and the backward pass recomputes the snapshots
     of one K-step segment at a time: memory O(nt/K + K) fields instead of O(nt), one extra forward),
+    ``save_every`` (k > 1: snapshot decimation - only every k-th inner step is stored and imaged, with weight k; a
+    performance mode, k = 1 is the exact discrete gradient),
     ``slabs`` (True or a process group: x-slab domain decomposition of every shot over the ranks of
     the group with ghost-zone exchange every ``halo_steps`` inner steps - 'auto' picks the interval
     from the slab width, slab.auto_halo_steps - see slab.py; every rank
@@ -398,7 +405,7 @@ class Propagator(torch.nn.Module):
 
     def __init__(self, model: dict, dx, pml_width=None, survey_pad=None, vpmax=None, *,
                  accuracy: int = 4, loc_mode: str = "trunc", chunk_rows: int = 0, checkpoint_every: int = 0,
-                 slabs=False, halo_steps=8, exchange: str = "peer"):
+                 save_every: int = 1, slabs=False, halo_steps=8, exchange: str = "peer"):
         super().__init__()
         if not isinstance(model, dict) or "vp" not in model:
             raise RuntimeError("model must be a dict with key 'vp'")
@@ -428,6 +435,11 @@ class Propagator(torch.nn.Module):
         if checkpoint_every < 0:
             raise RuntimeError("checkpoint_every must be >= 0")
         self.checkpoint_every = int(checkpoint_every)
+        if save_every < 1:
+            raise RuntimeError("save_every must be >= 1")
+        self.save_every = int(save_every)
+        if self.save_every > 1 and (checkpoint_every or (slabs is not False and slabs is not None)):
+            raise RuntimeError("save_every cannot be combined with checkpoint_every or slabs")
         if slabs is not False and slabs is not None and checkpoint_every:
             raise RuntimeError("slabs and checkpoint_every cannot be combined")
         self.slabs = None if slabs is False else slabs
@@ -450,7 +462,8 @@ class Propagator(torch.nn.Module):
                                        self.pml_width, self.vpmax, self.loc_mode, self.halo_steps,
                                        None if self.slabs is True else self.slabs, _Plan, self.exchange)
         return _ScalarFunction.apply(v, source_amplitudes, x_s, x_r, float(dt), self.dx, self.accuracy,
-                                     self.pml_width, self.vpmax, self.loc_mode, self.chunk_rows, self.checkpoint_every)
+                                     self.pml_width, self.vpmax, self.loc_mode, self.chunk_rows, self.checkpoint_every,
+                                     self.save_every)
 
 
 def _crop_to_survey(v, dx, x_s, x_r, survey_pad):
