@@ -77,6 +77,61 @@ def effective_parameters(vp_pad, vs_pad, rho_pad):
 _SOURCE_KINDS = {"explosive": 0, "fz": 1, "fy": 2}
 
 
+def _shot_groups(n_shots: int, cells: int):
+    """[s0, s1) shot groups that advance concurrently: two when there are at least four shots on a grid large enough to be
+    bandwidth-bound (FWI_B200_EL_GROUPS overrides the number of groups; 1 = all shots in one call)."""
+    import os
+    k = 2 if (n_shots >= 4 and cells >= (1 << 18)) else 1
+    env = os.environ.get("FWI_B200_EL_GROUPS")
+    if env is not None:
+        k = max(1, min(int(env), n_shots))
+    base, extra = divmod(n_shots, k)
+    out, lo = [], 0
+    for g in range(k):
+        hi = lo + base + (1 if g < extra else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+def _run_jobs(jobs, dev, cur):
+    """jobs: (C function, desc, buffers, name).  One job runs on the current stream; several run concurrently, job 0 on the
+    current stream and the others on pool streams that wait for it and that it waits for, each called from its own host
+    thread so that their launches interleave (ctypes releases the GIL during the call)."""
+    if len(jobs) == 1:
+        fn, d, b, name = jobs[0]
+        with torch.cuda.device(dev):
+            _lib.check(fn(C.byref(d), C.byref(b), C.c_void_p(cur.cuda_stream)), name)
+        return
+    import threading
+    start = torch.cuda.Event()
+    start.record(cur)
+    streams = [cur] + [torch.cuda.Stream(device=dev) for _ in jobs[1:]]
+    for st in streams[1:]:
+        st.wait_event(start)
+    errors = [None] * len(jobs)
+
+    def work(i):
+        fn, d, b, name = jobs[i]
+        try:
+            with torch.cuda.device(dev):
+                _lib.check(fn(C.byref(d), C.byref(b), C.c_void_p(streams[i].cuda_stream)), name)
+        except Exception as e:      # noqa: BLE001 - re-raised on the calling thread
+            errors[i] = e
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(len(jobs))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for st in streams[1:]:
+        done = torch.cuda.Event()
+        done.record(st)
+        cur.wait_event(done)
+    for e in errors:
+        if e is not None:
+            raise e
+
+
 class _ElasticFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, vp, vs, rho, source_amplitudes, x_s, x_r, dt, dx, order, pml_width, vpmax, pml_freq, loc_mode,
@@ -152,53 +207,67 @@ class _ElasticFunction(torch.autograd.Function):
         if free_surface and kind == 0 and bool((s_cell // nyp == P).any()):
             raise RuntimeError("an explosive source on the free surface row would break szz = 0 there: put it at least one cell down")
 
-        def desc_for(n, parity=0):
-            return _lib.ElasticDesc(nzp, nyp, order, pw, S, n, Ns, R, dz, dy, dti, kind, 1 if free_surface else 0, parity)
-
-        n_wave = int(L.fwi_elastic_wave_floats(C.byref(desc_for(nti))))
-        wave = torch.zeros(n_wave, dtype=torch.float32, device=dev)
+        # Shot groups: every elastic time step is three launches (F1, F2, points) whose hand-over costs ~7.5 us per step
+        # whatever the number of shots (measured on C3: 14.6 + 6.8 us per extra shot).  Two groups of shots advance
+        # concurrently, each on its own stream from its own host thread (the C calls release the GIL), so one group's
+        # kernels run in the other's gaps.  A group is an independent problem with its own wavefields, snapshots and images.
+        groups = _shot_groups(S, cells_n)
         cur = torch.cuda.current_stream(dev)
 
-        def run_forward(n, amp_n, wave, snap):
-            rec = torch.empty(2, n, S, R, dtype=torch.float32, device=dev)
-            d = desc_for(n)
-            b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
-                                    _ptr(s_link), _ptr(amp_n), _ptr(r_cell), _ptr(r_link), _ptr(rec), _ptr(snap), None, None,
-                                    None, None)
-            with torch.cuda.device(dev):
-                ev = _lib.time_loop_begin(cur)
-                _lib.check(L.fwi_elastic_forward(C.byref(d), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_forward")
-                _lib.time_loop_end(cur, ev, "elastic_fwd", n, S)
-            return rec
+        def desc_for(g, n, parity=0):
+            return _lib.ElasticDesc(nzp, nyp, order, pw, g[1] - g[0], n, Ns, R, dz, dy, dti, kind, 1 if free_surface else 0, parity)
 
-        snap, ckpts = None, None
+        n_wave = [int(L.fwi_elastic_wave_floats(C.byref(desc_for(g, nti)))) for g in groups]
+        sl = [dict(s_cell=s_cell[g[0]:g[1]].contiguous(), s_link=s_link[g[0]:g[1]].contiguous(),
+                   r_cell=r_cell[g[0]:g[1]].contiguous(), r_link=r_link[g[0]:g[1]].contiguous(),
+                   amp=amp if len(groups) == 1 else amp[:, g[0]:g[1]].contiguous()) for g in groups]
+
+        def run_forward(t0, n, waves, snaps):
+            """Steps [t0, t0 + n) of every group; returns the traces [2, n, S, R]."""
+            recs = [torch.empty(2, n, g[1] - g[0], R, dtype=torch.float32, device=dev) for g in groups]
+            jobs = []
+            for gi, g in enumerate(groups):
+                d = desc_for(g, n)
+                b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(waves[gi]),
+                                        _ptr(sl[gi]["s_cell"]), _ptr(sl[gi]["s_link"]), _ptr(sl[gi]["amp"][t0:t0 + n]),
+                                        _ptr(sl[gi]["r_cell"]), _ptr(sl[gi]["r_link"]), _ptr(recs[gi]),
+                                        _ptr(None if snaps is None else snaps[gi]), None, None, None, None)
+                jobs.append((L.fwi_elastic_forward, d, b, "fwi_elastic_forward"))
+            ev = _lib.time_loop_begin(cur)
+            _run_jobs(jobs, dev, cur)
+            _lib.time_loop_end(cur, ev, "elastic_fwd", n, S)
+            return recs[0] if len(groups) == 1 else torch.cat(recs, 2)
+
+        waves = [torch.zeros(nw, dtype=torch.float32, device=dev) for nw in n_wave]
+        snaps, ckpts = None, None
         if use_ckpt:
             # wavefield checkpointing: the 13 live fields every K steps instead of five snapshot fields every step
             ckpts, parts = [], []
             for t0 in range(0, nti, K):
                 n = min(K, nti - t0)
-                ckpts.append(wave[:13 * S * cells_n].clone())
-                parts.append(run_forward(n, amp[t0:t0 + n], wave, None))
+                ckpts.append([wv[:13 * (g[1] - g[0]) * cells_n].clone() for wv, g in zip(waves, groups)])
+                parts.append(run_forward(t0, n, waves, None))
             rec = torch.cat(parts, 1)
         else:
             if need_any:
-                snap = torch.empty(nti * 5 * S * cells_n, dtype=torch.float32, device=dev)
-            rec = run_forward(nti, amp, wave, snap)
+                snaps = [torch.empty(nti * 5 * (g[1] - g[0]) * cells_n, dtype=torch.float32, device=dev) for g in groups]
+            rec = run_forward(0, nti, waves, snaps)
         out = rec[:, ::ratio].contiguous() if ratio > 1 else rec
-        ctx.saved = (vp.detach(), vs.detach(), rho.detach(), params, prof_z, prof_y, s_cell, r_cell, s_link, r_link, snap)
+        ctx.saved = (vp.detach(), vs.detach(), rho.detach(), params, prof_z, prof_y, snaps)
         ctx.ckpt = (K, ckpts) if use_ckpt else None
-        ctx.amp = amp
+        ctx.groups, ctx.sl, ctx.n_wave = groups, sl, n_wave
         ctx.run_forward = run_forward
         ctx.desc_for = desc_for
-        ctx.meta = (nt, S, Ns, R, nti, ratio, P, dev, n_wave, cells_n, nzp, nyp)
+        ctx.meta = (nt, S, Ns, R, nti, ratio, P, dev, cells_n, nzp, nyp)
         ctx.src_like = source_amplitudes.detach()
         return out
 
     @staticmethod
     @torch.autograd.function.once_differentiable
     def backward(ctx, grad_rec):
-        vp, vs, rho, params, prof_z, prof_y, s_cell, r_cell, s_link, r_link, snap = ctx.saved
-        nt, S, Ns, R, nti, ratio, P, dev, n_wave, cells, nzp, nyp = ctx.meta
+        vp, vs, rho, params, prof_z, prof_y, snaps = ctx.saved
+        nt, S, Ns, R, nti, ratio, P, dev, cells, nzp, nyp = ctx.meta
+        groups, sl, n_wave = ctx.groups, ctx.sl, ctx.n_wave
         need_model = any(ctx.needs_input_grad[:3])
         g = grad_rec.to(dev, torch.float32)
         if ratio > 1:
@@ -207,38 +276,45 @@ class _ElasticFunction(torch.autograd.Function):
         else:
             g_in = g.contiguous()
         L = _lib.lib()
-        wave = torch.zeros(n_wave, dtype=torch.float32, device=dev)
-        scratch = torch.zeros(8 * S * cells, dtype=torch.float32, device=dev)
-        grad = torch.zeros(5, S, nzp, nyp, dtype=torch.float32, device=dev)
+        waves = [torch.zeros(nw, dtype=torch.float32, device=dev) for nw in n_wave]
+        scratch = [torch.zeros(8 * (gr[1] - gr[0]) * cells, dtype=torch.float32, device=dev) for gr in groups]
+        grads = [torch.zeros(5, gr[1] - gr[0], nzp, nyp, dtype=torch.float32, device=dev) for gr in groups]
         cur = torch.cuda.current_stream(dev)
 
-        def run_adjoint(n, g_n, amp_n, snap_n, parity):
-            gsrc = torch.zeros(n, S, Ns, dtype=torch.float32, device=dev)
-            d = ctx.desc_for(n, parity)
-            b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(wave), _ptr(s_cell),
-                                    _ptr(s_link), _ptr(amp_n), _ptr(r_cell), _ptr(r_link), None, _ptr(snap_n), _ptr(scratch),
-                                    _ptr(grad), _ptr(g_n), _ptr(gsrc))
-            with torch.cuda.device(dev):
-                ev = _lib.time_loop_begin(cur)
-                _lib.check(L.fwi_elastic_backward(C.byref(d), C.byref(b), C.c_void_p(cur.cuda_stream)), "fwi_elastic_backward")
-                _lib.time_loop_end(cur, ev, "elastic_adj", n, S)
-            return gsrc
+        def run_adjoint(t0, n, snaps_n, parity):
+            gsrc = [torch.zeros(n, gr[1] - gr[0], Ns, dtype=torch.float32, device=dev) for gr in groups]
+            gn = [g_in[:, t0:t0 + n] if len(groups) == 1 else g_in[:, t0:t0 + n, gr[0]:gr[1]] for gr in groups]
+            gn = [t.contiguous() for t in gn]
+            jobs = []
+            for gi, gr in enumerate(groups):
+                d = ctx.desc_for(gr, n, parity)
+                b = _lib.ElasticBuffers(*[_ptr(t) for t in params], _ptr(prof_z), _ptr(prof_y), _ptr(waves[gi]),
+                                        _ptr(sl[gi]["s_cell"]), _ptr(sl[gi]["s_link"]), _ptr(sl[gi]["amp"][t0:t0 + n]),
+                                        _ptr(sl[gi]["r_cell"]), _ptr(sl[gi]["r_link"]), None, _ptr(snaps_n[gi]),
+                                        _ptr(scratch[gi]), _ptr(grads[gi]), _ptr(gn[gi]), _ptr(gsrc[gi]))
+                jobs.append((L.fwi_elastic_backward, d, b, "fwi_elastic_backward"))
+            ev = _lib.time_loop_begin(cur)
+            _run_jobs(jobs, dev, cur)
+            _lib.time_loop_end(cur, ev, "elastic_adj", n, S)
+            return gsrc[0] if len(groups) == 1 else torch.cat(gsrc, 1)
 
         if ctx.ckpt is not None:
             K, ckpts = ctx.ckpt
-            snap_seg = torch.empty(K * 5 * S * cells, dtype=torch.float32, device=dev)
-            fwave = torch.zeros(n_wave, dtype=torch.float32, device=dev)
+            snap_seg = [torch.empty(K * 5 * (gr[1] - gr[0]) * cells, dtype=torch.float32, device=dev) for gr in groups]
+            fwaves = [torch.zeros(nw, dtype=torch.float32, device=dev) for nw in n_wave]
             parts, parity = [], 0
             for t0 in reversed(range(0, nti, K)):
                 n = min(K, nti - t0)
-                fwave[:13 * S * cells].copy_(ckpts.pop())
-                ctx.run_forward(n, ctx.amp[t0:t0 + n], fwave, snap_seg)          # recompute this segment's snapshots
-                parts.append(run_adjoint(n, g_in[:, t0:t0 + n].contiguous(), ctx.amp[t0:t0 + n], snap_seg, parity))
+                for fw, ck, gr in zip(fwaves, ckpts.pop(), groups):
+                    fw[:13 * (gr[1] - gr[0]) * cells].copy_(ck)
+                ctx.run_forward(t0, n, fwaves, snap_seg)                         # recompute this segment's snapshots
+                parts.append(run_adjoint(t0, n, snap_seg, parity))
                 parity = (parity + n) & 1
             gsrc = torch.cat(parts[::-1], 0)
             ctx.ckpt = None
         else:
-            gsrc = run_adjoint(nti, g_in, ctx.amp, snap, 0)
+            gsrc = run_adjoint(0, nti, snaps, 0)
+        grad = grads[0] if len(groups) == 1 else torch.cat(grads, 1)
         gvp = gvs = grho = gs = None
         if need_model:
             gpar = grad.sum(1)                       # fixed-order sum over shots
@@ -250,7 +326,7 @@ class _ElasticFunction(torch.autograd.Function):
         if ctx.needs_input_grad[3]:
             gs = H.resample_up_adjoint(gsrc, ratio, ctx.src_like.to(dev, torch.float32))
             gs = gs.to(ctx.src_like.device, ctx.src_like.dtype)
-        ctx.saved = ctx.run_forward = ctx.desc_for = ctx.amp = None
+        ctx.saved = ctx.run_forward = ctx.desc_for = ctx.sl = None
         return (gvp if ctx.needs_input_grad[0] else None, gvs if ctx.needs_input_grad[1] else None,
                 grho if ctx.needs_input_grad[2] else None, gs) + (None,) * 12
 

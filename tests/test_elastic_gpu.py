@@ -119,16 +119,22 @@ def test_force_sources_match_oracle(cuda_lib, source):
         assert K.rel_l2(got, want) <= 1e-4, (name, K.rel_l2(got, want))
 
 
+@pytest.mark.parametrize("groups", ["1", "2"])
 @pytest.mark.parametrize("K_", [16, 31, 50])
-def test_elastic_checkpointing_reproduces_the_stored_snapshot_gradient(cuda_lib, K_):
+def test_elastic_checkpointing_reproduces_the_stored_snapshot_gradient(cuda_lib, K_, groups, monkeypatch):
     """checkpoint_every=K keeps the 13 live fields every K steps and recomputes the five snapshot fields of one segment
     at a time in the backward pass: the same kernels on the same values."""
     import physicsbasedfwi2_b200 as pkg
+    monkeypatch.setenv("FWI_B200_EL_GROUPS", groups)     # "2": the two shots as concurrent groups on their own streams
     c = CASES[1]                                         # sub-stepped (ratio 2), two sources per shot
     vp, vs, rho, x_s, x_r, src, grad_rec = _inputs(c)
     dev = torch.device("cuda:0")
     outs = []
     for ck in (0, K_):
+        if ck == 0:
+            monkeypatch.setenv("FWI_B200_EL_GROUPS", "1")   # reference: one call over all shots, stored snapshots
+        else:
+            monkeypatch.setenv("FWI_B200_EL_GROUPS", groups)
         leaves = [t.to(dev).requires_grad_(True) for t in (vp, vs, rho, src)]
         prop = pkg.Propagator({"vp": leaves[0], "vs": leaves[1], "rho": leaves[2]}, c["dx"], pml_width=c["pml"],
                               accuracy=c["order"], checkpoint_every=ck)
