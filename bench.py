@@ -363,7 +363,9 @@ def run_c5(args, w, dev, rank, world, local):
     x_r[:, :, 1] = (torch.arange(R).float() * w["dx"])[None]
     src = ricker(w["freq"], nt, w["dt"], 1.0 / w["freq"]).reshape(-1, 1, 1).repeat(1, hi - lo, 1).contiguous().to(dev)
     xs_d, xr_d = x_s[lo:hi].to(dev), x_r[lo:hi].to(dev)
-    kw = dict(pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"])
+    # --no-vpmax: the reference's own call, Propagator({'vp': v}, dx) without vpmax: the inner step and the PML then follow
+    # the model's maximum, read back from the device once per call (as deepwave does)
+    kw = dict(pml_width=w["pml"], accuracy=w["order"], vpmax=None if args.no_vpmax else w["vmax"])
     v_true = synth_model(w).to(dev)
     with torch.no_grad():
         observed_all = torch.zeros(nt, S, R, device=dev)      # the data set: all shots, on every rank (network input)
@@ -441,6 +443,7 @@ def run_c5(args, w, dev, rank, world, local):
         cfg["workload"] += "; one step = generator forward + propagator gradient (fused L1 trace misfit, cached direct wave) + generator backward + Adam"
         cfg["shots_per_step"] = S
         cfg["l2"] = "wavefields of a launch fit L2 (latency-bound regime of the reference's own grids)"
+        cfg["vpmax"] = "from the model, read back every call (the reference's call)" if args.no_vpmax else "passed by the caller"
         line = {"metric": "FWI gradient Gcell-updates/s (fwd+adjoint)", "value": round(work * args.steps / (ms * 1e-3) / 1e9, 3),
                 "unit": "Gcell-updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "strong",
@@ -638,8 +641,8 @@ def run_gpu(args, w, dev, rank, world, local):
             prop = pkg.Propagator({"vp": v_d, "vs": vs_d, "rho": rho_d}, w["dx"], pml_width=w["pml"],
                                   accuracy=w["order"], vpmax=w["vmax"], checkpoint_every=w.get("ckpt", 0))
         else:
-            prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"], vpmax=w["vmax"],
-                              checkpoint_every=w.get("ckpt", 0), save_every=kq, slabs=slabs and world > 1,
+            prop = Propagator({"vp": v_d}, w["dx"], pml_width=w["pml"], accuracy=w["order"],
+                              vpmax=None if args.no_vpmax else w["vmax"], checkpoint_every=w.get("ckpt", 0), save_every=kq, slabs=slabs and world > 1,
                               halo_steps=w.get("slabs") or 8)
         rec = prop(src_d, xs_d, xr_d, w["dt"])
         loss = 0.5 * ((rec - obs_d) ** 2).sum()
@@ -849,6 +852,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg")
     ap.add_argument("--pml", type=int, default=-1, help="override the PML width (tuning only: 0 = PML-free grid)")
+    ap.add_argument("--no-vpmax", action="store_true", help="call the propagator as the reference does, without vpmax (one device-to-host read per call)")
     ap.add_argument("--save-every", type=int, default=1, help="snapshot decimation k (performance mode; k = 1 is the parity-graded default)")
     ap.add_argument("--survey", action="store_true", help="one step = the WHOLE survey sharded over the ranks (strong scaling)")
     ap.add_argument("--one-batch", action="store_true", help="c2: one launch of shots per step instead of the 32-shot slice")
