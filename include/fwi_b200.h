@@ -280,6 +280,19 @@ int fwi_trace_misfit_backward(const fwi_misfit_desc *desc, const float *pred, co
                               const float *obs, const float *grad_loss, float *grad_pred, void *workspace,
                               void *stream);
 
+/* Allocation-free variant of fwi_trace_misfit.  It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  Same arguments and result as fwi_trace_misfit without `workspace`: the
+ * partials live in a file-scope `static __device__` array of FWI_TRACE_MISFIT_STATIC_MAX_BYTES that every GPU loading
+ * the library holds until exit.  Returns FWI_ERR_ARG (with a message naming both sizes) when
+ * fwi_trace_misfit_workspace_bytes(desc) exceeds that maximum.  Calls no cudaMalloc / cudaFree / allocating routine.
+ * All calls share the array (it keeps the previous call's contents; nothing needs to start at zero): calls that overlap
+ * on one GPU - two streams, two threads - race.  fwi_trace_misfit_backward needs the partials of a forward call in a
+ * workspace of the caller's, so it pairs with fwi_trace_misfit, not with this entry point. */
+#define FWI_TRACE_MISFIT_STATIC_MAX_BYTES (4 * 1024 * 1024)
+int fwi_trace_misfit_noalloc(const fwi_misfit_desc *desc, const float *pred, const float *direct, const float *obs,
+                             float *loss, void *stream);
+
 /* ---- the steps either side of the elastic gradient (DENISE glue of the reference's elastic `prop`) ----------- */
 /* Frequency stage of d.add_fwi_stage(fc_low=0.0, fc_high=10.0, ...) (models/networks.py:9147): Butterworth low-pass of
  * even `order` on every trace of in [nt][n_traces] (traces fast), zero initial state; zero_phase: a second pass

@@ -215,6 +215,8 @@ def lib() -> C.CDLL:
     L.fwi_trace_misfit.restype = C.c_int
     L.fwi_trace_misfit_backward.argtypes = [C.POINTER(MisfitDesc)] + [C.c_void_p] * 7
     L.fwi_trace_misfit_backward.restype = C.c_int
+    L.fwi_trace_misfit_noalloc.argtypes = [C.POINTER(MisfitDesc)] + [C.c_void_p] * 5
+    L.fwi_trace_misfit_noalloc.restype = C.c_int
     L.fwi_butterworth_lowpass.argtypes = [C.POINTER(ButterDesc), C.c_void_p, C.c_void_p, C.c_void_p]
     L.fwi_butterworth_lowpass.restype = C.c_int
     L.fwi_elastic_gradient_post.argtypes = [C.POINTER(GradPostDesc)] + [C.c_void_p] * 8

@@ -16,6 +16,7 @@
 // Layout: [nt][M] with M = S*R traces contiguous; a thread owns one trace inside one time chunk,
 // so a warp reads 32 adjacent traces per time sample (coalesced).
 #include <algorithm>
+#include <mutex>
 
 #include "common.h"
 
@@ -179,4 +180,53 @@ extern "C" int fwi_trace_misfit_backward(const fwi_misfit_desc *d, const float *
     fwi::count_launch();
     FWI_CHECK_CUDA(cudaGetLastError());
     return FWI_OK;
+}
+
+// ---- allocation-free variant of fwi_trace_misfit --------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot allocate device
+// memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The [4][C][M] partials
+// that fwi_trace_misfit keeps in a caller-provided workspace live in a file-scope device array of
+// FWI_TRACE_MISFIT_STATIC_MAX_BYTES (4 MiB; every GPU that loads the library holds it until exit).  All calls share the
+// array: it keeps the previous call's contents (every element the kernels read is written first by the same call, so
+// nothing has to start at zero and nothing is cleared), and two calls that overlap on one GPU race.
+namespace {
+
+static __device__ __align__(256) unsigned char g_misfit_scratch[FWI_TRACE_MISFIT_STATIC_MAX_BYTES];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mutex;
+void *g_scratch_addr[kMaxDevices];      // device address of g_misfit_scratch on device i (0 = not looked up yet)
+
+// In host code `g_misfit_scratch` is a host-side stand-in, not a device address: the address a kernel can use comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+int misfit_scratch(void **ptr) {
+    int dev = -1;
+    FWI_CHECK_CUDA(cudaGetDevice(&dev));
+    FWI_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "device ordinal %d out of range (max %d)", dev, kMaxDevices);
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (!g_scratch_addr[dev]) {
+        void *p = nullptr;
+        FWI_CHECK_CUDA(cudaGetSymbolAddress(&p, g_misfit_scratch));
+        FWI_CHECK_ARG(p != nullptr, "cudaGetSymbolAddress returned NULL for the static misfit scratch");
+        g_scratch_addr[dev] = p;
+    }
+    *ptr = g_scratch_addr[dev];
+    return FWI_OK;
+}
+
+}  // namespace
+
+extern "C" int fwi_trace_misfit_noalloc(const fwi_misfit_desc *d, const float *pred, const float *direct, const float *obs,
+                                        float *loss, void *stream) {
+    FWI_CHECK_ARG(d != nullptr, "descriptor is NULL");
+    const int64_t need = fwi_trace_misfit_workspace_bytes(d);
+    FWI_CHECK_ARG(need > 0, "nt and n_traces must be >= 1");
+    FWI_CHECK_ARG(need <= (int64_t)FWI_TRACE_MISFIT_STATIC_MAX_BYTES,
+                  "fwi_trace_misfit_noalloc: nt = %d, n_traces = %d need %lld bytes of scratch, the static array holds %lld "
+                  "(use fwi_trace_misfit with a caller-provided workspace)",
+                  d->nt, d->n_traces, (long long)need, (long long)FWI_TRACE_MISFIT_STATIC_MAX_BYTES);
+    void *scratch = nullptr;
+    int rc = misfit_scratch(&scratch);
+    if (rc != FWI_OK) return rc;
+    return fwi_trace_misfit(d, pred, direct, obs, loss, scratch, stream);
 }

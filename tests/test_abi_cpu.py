@@ -131,6 +131,9 @@ def test_misfit_and_slab_entry_points_check_arguments_on_the_host():
     bad = _lib.MisfitDesc(10, 5, 2, 1, 1e-10)
     assert L.fwi_trace_misfit(ctypes.byref(bad), 1, None, 1, 1, 1, None) == -1
     assert b"kind" in L.fwi_last_error()
+    big = _lib.MisfitDesc(4000, 400000, 0, 1, 1e-10)          # 6.4 MB of partials: beyond the static array of the no-alloc variant
+    assert L.fwi_trace_misfit_noalloc(ctypes.byref(big), 256, None, 256, 256, None) == -1
+    assert b"4194304" in L.fwi_last_error()
     assert L.fwi_slab_exchanges(8000, 8) == 999 and L.fwi_slab_exchanges(8, 8) == 0 and L.fwi_slab_exchanges(9, 8) == 1
     assert L.fwi_slab_exchanges(0, 8) == 0
     ad = _lib.AcousticDesc(124, 324, 4, 10, 1, 0, 10, 0, 0, 0, 0, 0, 10.0, 10.0, 1e-3)
