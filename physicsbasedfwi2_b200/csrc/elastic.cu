@@ -77,18 +77,25 @@ inline void launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream
 
 constexpr int VY = 0, VZ = 1, SXX = 2, SZZ = 3, SYZ = 4, PSI = 5;
 
+// Wavefields are read with plain (coherent) loads everywhere in this file, never with __ldg.  ld.global.nc declares the
+// data read-only for the lifetime of the grid, and both nvcc and ptxas move such loads above griddepcontrol.wait, asm
+// "memory" clobber or not (an address made to depend on an opaque zero produced after the wait does not help: ptxas
+// folds the zero) - but under programmatic dependent launch the previous kernel of the time loop may still be writing
+// the field then.  Seen in the SASS of one build of the free-surface F2 (six LDG.E.CONSTANT of vy / vz ahead of ACQBULK)
+// and as traces that depended on timing.  __ldg stays on what no kernel of the time loop writes: material grids,
+// profiles, index lists, amplitudes.
 template <int H>
 __device__ __forceinline__ float dplus(const float *f, long long i, long long st, const float *c) {
-    float s = c[0] * (__ldg(f + i + st) - __ldg(f + i));
+    float s = c[0] * (f[i + st] - f[i]);
 #pragma unroll
-    for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (__ldg(f + i + k * st) - __ldg(f + i - (k - 1) * st));
+    for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (f[i + k * st] - f[i - (k - 1) * st]);
     return s;
 }
 template <int H>
 __device__ __forceinline__ float dminus(const float *f, long long i, long long st, const float *c) {
-    float s = c[0] * (__ldg(f + i) - __ldg(f + i - st));
+    float s = c[0] * (f[i] - f[i - st]);
 #pragma unroll
-    for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (__ldg(f + i + (k - 1) * st) - __ldg(f + i - k * st));
+    for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (f[i + (k - 1) * st] - f[i - k * st]);
     return s;
 }
 
@@ -96,7 +103,7 @@ __device__ __forceinline__ float dminus(const float *f, long long i, long long s
 // their mirror images; szz mirrors about the row itself, syz - half a cell lower - about the surface between its rows)
 template <int H>
 __device__ __forceinline__ float dplus_z_szz_fs(const float *f, int i, int j, int nyp, int fs, const float *c) {
-    auto at = [&](int r) { return r >= fs ? __ldg(f + (long long)r * nyp + j) : -__ldg(f + (long long)(2 * fs - r) * nyp + j); };
+    auto at = [&](int r) { return r >= fs ? f[(long long)r * nyp + j] : -f[(long long)(2 * fs - r) * nyp + j]; };
     float s = c[0] * (at(i + 1) - at(i));
 #pragma unroll
     for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (at(i + k) - at(i - (k - 1)));
@@ -104,7 +111,7 @@ __device__ __forceinline__ float dplus_z_szz_fs(const float *f, int i, int j, in
 }
 template <int H>
 __device__ __forceinline__ float dminus_z_syz_fs(const float *f, int i, int j, int nyp, int fs, const float *c) {
-    auto at = [&](int r) { return r >= fs ? __ldg(f + (long long)r * nyp + j) : -__ldg(f + (long long)(2 * fs - r - 1) * nyp + j); };
+    auto at = [&](int r) { return r >= fs ? f[(long long)r * nyp + j] : -f[(long long)(2 * fs - r - 1) * nyp + j]; };
     float s = c[0] * (at(i) - at(i - 1));
 #pragma unroll
     for (int k = 2; k <= H; ++k) s = s + c[k - 1] * (at(i + (k - 1)) - at(i - k));
@@ -135,27 +142,41 @@ __device__ __forceinline__ float dminus_z_syz_fs(const float *f, int i, int j, i
 #define BYH(j) __ldg(p.py + 3 * p.nyp + (j))
 
 // ---- forward ------------------------------------------------------------------------------
+#ifdef FWI_EL_MINBLK         // minimum blocks per SM of F1 / F2 (a register budget): a tuning knob of scripts/dev_variants.sh
+#define FWI_EL_FB 256, FWI_EL_MINBLK
+#else
+#define FWI_EL_FB 256
+#endif
+// Every operand of a cell is requested before the first one is used: the memory-variable stores of the PML branches
+// (which may alias anything, as far as the compiler knows) would otherwise keep the loads of the updated fields and of the
+// material grids behind them, and a thread would pay two or three memory round trips in a row instead of one
+// (profiles/r02e_el_fwd_full.txt: 60 % of the stall samples sat on those late loads).
 template <int H, bool SAVE, bool FS>
-__global__ void __launch_bounds__(256) elastic_f1(const EParams p) {
+__global__ void __launch_bounds__(FWI_EL_FB) elastic_f1(const EParams p) {
     ELASTIC_CELL();
     const float *sxx = p.f[SXX] + (long long)s * p.cells, *szz = p.f[SZZ] + (long long)s * p.cells,
                 *syz = p.f[SYZ] + (long long)s * p.cells;
+    const float vy0 = p.f[VY][o], vz0 = p.f[VZ][o];
+    const float by = __ldg(p.by + c0), bz = __ldg(p.bz + c0);
+    float ps0 = 0.f, ps1 = 0.f, ps2 = 0.f, ps3 = 0.f;
+    if (ypml) { ps0 = p.f[PSI + 0][o]; ps2 = p.f[PSI + 2][o]; }
+    if (zpml) { ps1 = p.f[PSI + 1][o]; ps3 = p.f[PSI + 3][o]; }
     const bool near_fs = FS && i < p.fs_row + H;      // (FS is a template flag: the grids without a free surface keep their code)
     float d1 = dplus<H>(sxx, c0, 1, p.cy);
     float d2 = near_fs ? dminus_z_syz_fs<H>(syz, i, j, p.nyp, p.fs_row, p.cz) : dminus<H>(syz, c0, p.nyp, p.cz);
     float d3 = dminus<H>(syz, c0, 1, p.cy);
     float d4 = near_fs ? dplus_z_szz_fs<H>(szz, i, j, p.nyp, p.fs_row, p.cz) : dplus<H>(szz, c0, p.nyp, p.cz);
     if (ypml) {
-        float q0 = BYH(j) * p.f[PSI + 0][o] + AYH(j) * d1; p.f[PSI + 0][o] = q0; d1 = d1 + q0;
-        float q2 = BY(j) * p.f[PSI + 2][o] + AY(j) * d3; p.f[PSI + 2][o] = q2; d3 = d3 + q2;
+        float q0 = BYH(j) * ps0 + AYH(j) * d1; p.f[PSI + 0][o] = q0; d1 = d1 + q0;
+        float q2 = BY(j) * ps2 + AY(j) * d3; p.f[PSI + 2][o] = q2; d3 = d3 + q2;
     }
     if (zpml) {
-        float q1 = BZ(i) * p.f[PSI + 1][o] + AZ(i) * d2; p.f[PSI + 1][o] = q1; d2 = d2 + q1;
-        float q3 = BZH(i) * p.f[PSI + 3][o] + AZH(i) * d4; p.f[PSI + 3][o] = q3; d4 = d4 + q3;
+        float q1 = BZ(i) * ps1 + AZ(i) * d2; p.f[PSI + 1][o] = q1; d2 = d2 + q1;
+        float q3 = BZH(i) * ps3 + AZH(i) * d4; p.f[PSI + 3][o] = q3; d4 = d4 + q3;
     }
     const float fy = d1 + d2, fz = d3 + d4;
-    p.f[VY][o] = p.f[VY][o] + (p.dt * __ldg(p.by + c0)) * fy;
-    p.f[VZ][o] = p.f[VZ][o] + (p.dt * __ldg(p.bz + c0)) * fz;
+    p.f[VY][o] = vy0 + (p.dt * by) * fy;
+    p.f[VZ][o] = vz0 + (p.dt * bz) * fz;
     if (SAVE) {
         __stcs(p.snap + o, fy);
         __stcs(p.snap + fs + o, fz);
@@ -163,29 +184,33 @@ __global__ void __launch_bounds__(256) elastic_f1(const EParams p) {
 }
 
 template <int H, bool SAVE, bool FS>
-__global__ void __launch_bounds__(256) elastic_f2(const EParams p) {
+__global__ void __launch_bounds__(FWI_EL_FB) elastic_f2(const EParams p) {
     ELASTIC_CELL();
     const float *vy = p.f[VY] + (long long)s * p.cells, *vz = p.f[VZ] + (long long)s * p.cells;
+    const float sxx0 = p.f[SXX][o], szz0 = p.f[SZZ][o], syz0 = p.f[SYZ][o];       // (all loads first: see elastic_f1)
+    const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
+    float ps4 = 0.f, ps5 = 0.f, ps6 = 0.f, ps7 = 0.f;
+    if (ypml) { ps4 = p.f[PSI + 4][o]; ps7 = p.f[PSI + 7][o]; }
+    if (zpml) { ps5 = p.f[PSI + 5][o]; ps6 = p.f[PSI + 6][o]; }
     float d5 = dminus<H>(vy, c0, 1, p.cy), d6 = dminus<H>(vz, c0, p.nyp, p.cz);
     float d7 = dplus<H>(vy, c0, p.nyp, p.cz), d8 = dplus<H>(vz, c0, 1, p.cy);
     if (ypml) {
-        float q4 = BY(j) * p.f[PSI + 4][o] + AY(j) * d5; p.f[PSI + 4][o] = q4; d5 = d5 + q4;
-        float q7 = BYH(j) * p.f[PSI + 7][o] + AYH(j) * d8; p.f[PSI + 7][o] = q7; d8 = d8 + q7;
+        float q4 = BY(j) * ps4 + AY(j) * d5; p.f[PSI + 4][o] = q4; d5 = d5 + q4;
+        float q7 = BYH(j) * ps7 + AYH(j) * d8; p.f[PSI + 7][o] = q7; d8 = d8 + q7;
     }
     if (zpml) {
-        float q5 = BZ(i) * p.f[PSI + 5][o] + AZ(i) * d6; p.f[PSI + 5][o] = q5; d6 = d6 + q5;
-        float q6 = BZH(i) * p.f[PSI + 6][o] + AZH(i) * d7; p.f[PSI + 6][o] = q6; d7 = d7 + q6;
+        float q5 = BZ(i) * ps5 + AZ(i) * d6; p.f[PSI + 5][o] = q5; d6 = d6 + q5;
+        float q6 = BZH(i) * ps6 + AZH(i) * d7; p.f[PSI + 6][o] = q6; d7 = d7 + q6;
     }
     const float e1 = d5, e2 = d6, e3 = d7 + d8;
-    const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
     if (FS && i == p.fs_row) {
         // on the free surface szz stays zero, which removes e2 from the sxx update: (l2m - lam^2 / l2m) e1
-        p.f[SXX][o] = p.f[SXX][o] + p.dt * ((l2m - lam * lam / l2m) * e1);
+        p.f[SXX][o] = sxx0 + p.dt * ((l2m - lam * lam / l2m) * e1);
     } else {
-        p.f[SXX][o] = p.f[SXX][o] + p.dt * (l2m * e1 + lam * e2);
-        p.f[SZZ][o] = p.f[SZZ][o] + p.dt * (lam * e1 + l2m * e2);
+        p.f[SXX][o] = sxx0 + p.dt * (l2m * e1 + lam * e2);
+        p.f[SZZ][o] = szz0 + p.dt * (lam * e1 + l2m * e2);
     }
-    p.f[SYZ][o] = p.f[SYZ][o] + (p.dt * mu) * e3;
+    p.f[SYZ][o] = syz0 + (p.dt * mu) * e3;
     if (SAVE) {
         __stcs(p.snap + 2 * fs + o, e1);
         __stcs(p.snap + 3 * fs + o, e2);
@@ -311,7 +336,7 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b2_fuse
             const long long c0 = (long long)i * p.nyp + j, o = so + c0;
             const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1);
             const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1);
-            const float asxx = __ldg(p.f[SXX] + o), aszz = __ldg(p.f[SZZ] + o), asyz = __ldg(p.f[SYZ] + o);
+            const float asxx = p.f[SXX][o], aszz = p.f[SZZ][o], asyz = p.f[SYZ][o];
             const float l2m = __ldg(p.l2m + c0), lam = __ldg(p.lam + c0), mu = __ldg(p.mu + c0);
             float ae1 = p.dt * (l2m * asxx + lam * aszz), ae2 = p.dt * (lam * asxx + l2m * aszz);
             const float ae3 = (p.dt * mu) * asyz;
@@ -347,7 +372,7 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b2_fuse
         const bool in = i < p.nzp - p.h && j < p.nyp - p.h;
         const long long o = so + (long long)(in ? i : p.h) * p.nyp + (in ? j : p.h);
         oo[q] = in ? o : -1;
-        sx[q] = __ldg(p.f[SXX] + o); sz[q] = __ldg(p.f[SZZ] + o); sy[q] = __ldg(p.f[SYZ] + o);
+        sx[q] = p.f[SXX][o]; sz[q] = p.f[SZZ][o]; sy[q] = p.f[SYZ][o];
         e1[q] = __ldcs(p.snap + 2 * fs + o); e2[q] = __ldcs(p.snap + 3 * fs + o); e3[q] = __ldcs(p.snap + 4 * fs + o);
         g0[q] = p.grad[o]; g1[q] = p.grad[fs + o]; g2[q] = p.grad[2 * fs + o];
         vy[q] = p.f[VY][o]; vz[q] = p.f[VZ][o];
@@ -398,7 +423,7 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b1_fuse
             const long long c0 = (long long)i * p.nyp + j, o = so + c0;
             const bool ypml = p.pml > 0 && (j < p.h + p.pml || j >= p.nyp - p.h - p.pml - 1);
             const bool zpml = p.pml > 0 && (i < p.h + p.pml || i >= p.nzp - p.h - p.pml - 1);
-            const float avy = __ldg(p.f[VY] + o), avz = __ldg(p.f[VZ] + o);
+            const float avy = p.f[VY][o], avz = p.f[VZ][o];
             const float agy = (p.dt * __ldg(p.by + c0)) * avy, agz = (p.dt * __ldg(p.bz + c0)) * avz;
             y1 = agy; y2 = agy; y3 = agz; y4 = agz;
             if (ypml || zpml) {
@@ -427,7 +452,7 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_b1_fuse
         const bool in = i < p.nzp - p.h && j < p.nyp - p.h;
         const long long o = so + (long long)(in ? i : p.h) * p.nyp + (in ? j : p.h);
         oo[q] = in ? o : -1;
-        vy[q] = __ldg(p.f[VY] + o); vz[q] = __ldg(p.f[VZ] + o);
+        vy[q] = p.f[VY][o]; vz[q] = p.f[VZ][o];
         fy[q] = __ldcs(p.snap + o); fz[q] = __ldcs(p.snap + fs + o);
         g3[q] = p.grad[3 * fs + o]; g4[q] = p.grad[4 * fs + o];
         sx[q] = p.f[SXX][o]; sy[q] = p.f[SYZ][o]; sz[q] = p.f[SZZ][o];
@@ -501,7 +526,7 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_f_fused
         float a = 0.f, b = 0.f, c = 0.f;
         if (i >= 0 && i < p.nzp && j >= 0 && j < p.nyp) {
             const long long o = so + (long long)i * p.nyp + j;
-            a = __ldg(p.f[SXX] + o); b = __ldg(p.f[SZZ] + o); c = __ldg(p.f[SYZ] + o);
+            a = p.f[SXX][o]; b = p.f[SZZ][o]; c = p.f[SYZ][o];
         }
         Sxx[t] = a; Szz[t] = b; Syz[t] = c;
     }
@@ -514,7 +539,7 @@ __global__ void __launch_bounds__(NT, NT <= 512 ? 1024 / NT : 1) elastic_f_fused
         const int i = i0 - H + lz, j = j0 - H + lx;
         const bool in = t < SX1 * SZ1 && i >= p.h && i < p.nzp - p.h && j >= p.h && j < p.nyp - p.h;
         const long long c0 = (long long)(in ? i : p.h) * p.nyp + (in ? j : p.h);
-        pvy[q] = __ldg(p.f[VY] + so + c0); pvz[q] = __ldg(p.f[VZ] + so + c0);
+        pvy[q] = p.f[VY][so + c0]; pvz[q] = p.f[VZ][so + c0];
         pby[q] = __ldg(p.by + c0); pbz[q] = __ldg(p.bz + c0);
     }
     __syncthreads();

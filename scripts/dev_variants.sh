@@ -8,7 +8,7 @@ S=physicsbasedfwi2_b200/csrc
 while [ $# -ge 2 ]; do
   name=$1; flags=$2; shift 2
   ( nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false -Xcompiler -fPIC -shared $flags \
-      -o build/variants/lib_$name.so $S/common.cu $S/acoustic.cu $S/acoustic_small.cu $S/elastic.cu $S/misfit.cu $S/host_kernels.cu \
+      -o build/variants/lib_$name.so $S/common.cu $S/acoustic.cu $S/acoustic_small.cu $S/elastic.cu $S/misfit.cu $S/host_kernels.cu $S/glue.cu \
       > build/variants/$name.log 2>&1 && echo "built $name" || echo "FAILED $name" ) &
 done
 wait
