@@ -155,3 +155,33 @@ def test_torch_library_extension_loads_and_registers_every_operator():
         ops.scalar_plan(torch.zeros(4, 4), 1e-3, 10.0, 10.0, 4, 10, -1.0, 1, 0, 0, 0)
     with pytest.raises(RuntimeError, match="2-D"):
         ops.scalar_plan(torch.zeros(4), 1e-3, 10.0, 10.0, 4, 10, -1.0, 1, 0, 0, 0)
+
+
+def test_no_wavefield_load_is_scheduled_ahead_of_the_dependent_launch_wait():
+    """Kernels of the time loops start under programmatic dependent launch and wait (griddepcontrol.wait, SASS ACQBULK)
+    before touching a wavefield.  ld.global.nc loads may be moved above that wait by the compiler, so wavefields must be
+    read with plain loads (csrc/elastic.cu, csrc/acoustic.cu:ld_field); what sits ahead of the wait in the SASS may only
+    be LDG.E.CONSTANT (__ldg of tables and material grids that no kernel of a time loop writes), never a plain LDG, a
+    bulk-tensor load or a store."""
+    import shutil
+    import subprocess
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    src = open(os.path.join(ROOT, "physicsbasedfwi2_b200", "csrc", "elastic.cu")).read()
+    assert "__ldg(p.f[" not in src and "__ldg(f +" not in src, "elastic.cu reads a wavefield with __ldg"
+    sass = subprocess.run([cuobjdump, "-sass", pkg.build()], capture_output=True, text=True, check=True).stdout
+    name, before_wait, waits, bad = None, [], 0, []
+    for line in sass.splitlines():
+        if "Function :" in line:
+            name, before_wait = line.split(":", 1)[1].strip(), []
+        elif name and "ACQBULK" in line:
+            waits += 1
+            bad += [(name, ins) for ins in before_wait]
+            name = None                                   # only what precedes the first wait matters
+        elif name:
+            m = re.search(r"\b(LDG\.[A-Z0-9.]*|STG\.[A-Z0-9.]*|UTMALDG[A-Z0-9.]*|RED\.[A-Z0-9.]*|ATOMG?\.[A-Z0-9.]*)", line)
+            if m and ".CONSTANT" not in m.group(1):
+                before_wait.append(m.group(1))
+    assert waits >= 20, f"only {waits} kernels with a dependent-launch wait found: did the SASS format change?"
+    assert not bad, f"memory operations ahead of griddepcontrol.wait: {bad[:5]}"
