@@ -42,6 +42,44 @@ struct CellMap {
     __device__ __forceinline__ size_t glob(int lr, int x) const { return (size_t)(r0 + lr) * pitch + col0 + x; }
 };
 
+// ---- halo rows through asynchronous remote stores (p.async_halo) ---------------------------------------------
+// The edge rows a CTA pushes into its neighbours' halo rows are written with st.async, which signals the bytes it has
+// delivered on an mbarrier in the RECEIVER's shared memory; the receiver waits on that barrier for the bytes of both
+// neighbours.  A step then synchronises a CTA with its two neighbours only, and nothing waits for a release fence (the
+// fence of cluster.sync also waited for the step's snapshot stores to reach L2: 10 % of the step, as much again for the
+// barrier itself - profiles/r02e_small_full.txt).  Two barriers alternate by step parity: a neighbour can be at most
+// one step ahead (its step n + 1 needs my rows of step n), so the bytes of step n + 2 cannot arrive before the wait of
+// step n has been passed.
+__device__ __forceinline__ unsigned smem_addr(const void *p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ unsigned map_to_rank(unsigned addr, unsigned rank) {
+    unsigned r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_async_f32(unsigned remote_addr, float v, unsigned remote_bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(remote_addr),
+                 "r"(__float_as_uint(v)), "r"(remote_bar)
+                 : "memory");
+}
+__device__ __forceinline__ void halo_bar_expect(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void halo_bar_wait(unsigned bar, unsigned parity) {
+    unsigned done = 0;
+    for (unsigned spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n"
+            ".reg .pred P1;\n"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, P1;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (spin > (1u << 24)) __trap();       // (seconds: a lost signal must not hang the device)
+    }
+}
+
 // CPT = cells per thread (compile-time bound: per-cell constants and accumulators live in registers
 // for the whole time loop); ADJ = adjoint pass with imaging (reads the snapshot, accumulates the image).
 template <int H, int CPT, bool ADJ>
@@ -160,10 +198,23 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
             if (cell[k] >= 0) qreg[k] = __ldcs(qr + cm.glob((cell[k] >> 12) & 0xfff, cell[k] & 0xfff));
         }
     }
+    // (two mbarriers behind the profiles, in the dynamic allocation: static shared memory would count against the opt-in limit)
+    unsigned long long *halo_bar = reinterpret_cast<unsigned long long *>(sm + (((p.wave_pml ? 6 : 2) * fld + LR + W + 1) & ~1));
+    if (p.async_halo && tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&halo_bar[0])) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&halo_bar[1])) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // bytes my neighbours deliver per step: H rows of the field (and of pz) from each of them
+    const unsigned halo_bytes = (unsigned)((rank > 0 ? 1 : 0) + (rank < p.C - 1 ? 1 : 0)) * (unsigned)(H * W) * 4u * (p.wave_pml ? 2u : 1u);
+    const unsigned sm_up = rank > 0 ? map_to_rank(smem_addr(sm), rank - 1) : 0u;            // the neighbours' dynamic shared memory
+    const unsigned sm_dn = rank < p.C - 1 ? map_to_rank(smem_addr(sm), rank + 1) : 0u;
     cluster.sync();
 
     for (int it = 0; it < p.nsteps; ++it) {
         const int n = p.adjoint ? p.nsteps - 1 - it : it;
+        const unsigned hb = smem_addr(&halo_bar[it & 1]);
+        if (p.async_halo && tid == 0) halo_bar_expect(hb, halo_bytes);
         // the amplitude this thread injects at the end of the step: in flight during the stencil work
         float amp0 = 0.f;
         const float *amp = p.n_inj > 0 ? p.inj_amp + ((size_t)n * p.S + s) * p.n_inj : nullptr;
@@ -249,31 +300,53 @@ __global__ void __launch_bounds__(kNT, 1) acoustic_small_kernel(const SmallParam
         }
         __syncthreads();
         // ---- push my edge rows of the new field and of pz into the neighbours' halo rows (DSMEM) ----
-        if (rows > 0) {
+        if (p.async_halo) {
             const int nedge = H * W;
+            const unsigned o_um = (unsigned)(UM - sm) * 4u, o_pz = (unsigned)(PZN - sm) * 4u;
             if (rank > 0) {                      // my first H rows -> the lower halo of the CTA above
-                float *nUM = cluster.map_shared_rank(UM, rank - 1), *nPZ = cluster.map_shared_rank(PZN, rank - 1);
+                const unsigned rbar = map_to_rank(hb, rank - 1);
+                const int dst0 = (H + (r0 - p.row_start[rank - 1])) * W;
                 for (int t = tid; t < nedge; t += kNT) {
-                    const int src = H * W + t, dst = (H + (r0 - p.row_start[rank - 1])) * W + t;
-                    nUM[dst] = UM[src];
-                    if (p.wave_pml) nPZ[dst] = PZN[src];
+                    st_async_f32(sm_up + o_um + (unsigned)(dst0 + t) * 4u, UM[H * W + t], rbar);
+                    if (p.wave_pml) st_async_f32(sm_up + o_pz + (unsigned)(dst0 + t) * 4u, PZN[H * W + t], rbar);
                 }
             }
             if (rank < p.C - 1) {                // my last H rows -> the upper halo of the CTA below
-                float *nUM = cluster.map_shared_rank(UM, rank + 1), *nPZ = cluster.map_shared_rank(PZN, rank + 1);
+                const unsigned rbar = map_to_rank(hb, rank + 1);
                 for (int t = tid; t < nedge; t += kNT) {
-                    const int src = rows * W + t, dst = t;
-                    nUM[dst] = UM[src];
-                    if (p.wave_pml) nPZ[dst] = PZN[src];
+                    st_async_f32(sm_dn + o_um + (unsigned)t * 4u, UM[rows * W + t], rbar);
+                    if (p.wave_pml) st_async_f32(sm_dn + o_pz + (unsigned)t * 4u, PZN[rows * W + t], rbar);
                 }
             }
+            halo_bar_wait(hb, (unsigned)(it >> 1) & 1u);     // my halo rows of the new field / pz have arrived
+        } else {
+            if (rows > 0) {
+                const int nedge = H * W;
+                if (rank > 0) {                      // my first H rows -> the lower halo of the CTA above
+                    float *nUM = cluster.map_shared_rank(UM, rank - 1), *nPZ = cluster.map_shared_rank(PZN, rank - 1);
+                    for (int t = tid; t < nedge; t += kNT) {
+                        const int src = H * W + t, dst = (H + (r0 - p.row_start[rank - 1])) * W + t;
+                        nUM[dst] = UM[src];
+                        if (p.wave_pml) nPZ[dst] = PZN[src];
+                    }
+                }
+                if (rank < p.C - 1) {                // my last H rows -> the upper halo of the CTA below
+                    float *nUM = cluster.map_shared_rank(UM, rank + 1), *nPZ = cluster.map_shared_rank(PZN, rank + 1);
+                    for (int t = tid; t < nedge; t += kNT) {
+                        const int src = rows * W + t, dst = t;
+                        nUM[dst] = UM[src];
+                        if (p.wave_pml) nPZ[dst] = PZN[src];
+                    }
+                }
+            }
+            cluster.sync();      // halos of the new field and of the new pz are in place
         }
-        cluster.sync();      // halos of the new field and of the new pz are in place
         float *tmp = U; U = UM; UM = tmp;
         tmp = PZ; PZ = PZN; PZN = tmp;
         tmp = PY; PY = PYN; PYN = tmp;
     }
 
+    if (p.async_halo) cluster.sync();      // no CTA exits while remote stores into it may be in flight
     // ---- store the state back: own rows; fields in the slots the general kernel would leave them in ----
     const int odd = p.nsteps & 1;
     float *gu = p.wave + (odd ? gfld : 0) + gshot, *gum = p.wave + (odd ? 0 : gfld) + gshot;
@@ -306,10 +379,12 @@ int try_launch(const SmallParams &p0, cudaStream_t st, bool *launched) {
     }
     const int nf = p0.wave_pml ? 6 : 2;
     if (p0.nyp >= 4096 || p0.nzp >= 4096) return FWI_OK;      // cell descriptors pack row and column in 12 bits each
+    const int env_async = getenv("FWI_B200_SMALL_ASYNC") ? atoi(getenv("FWI_B200_SMALL_ASYNC")) : 1;
     const int cmax = getenv("FWI_B200_SMALL_CLUSTER") ? atoi(getenv("FWI_B200_SMALL_CLUSTER")) : 8;
     for (int C = std::min(cmax, 8); C >= 1; --C) {        // the largest cluster whose shots are all co-resident
         SmallParams p = p0;
         p.C = C;
+        p.async_halo = env_async;
         // cost-balanced split of the computational rows: a row of the PML frame costs about 2.6 interior rows,
         // an interior row 1 + 1.6 x (share of its columns in the frame)
         const int zlo = 2 * H + p.pw, zhi = p.nzp - 2 * H - p.pw, ncols = p.nyp - 2 * H;
@@ -337,7 +412,8 @@ int try_launch(const SmallParams &p0, cudaStream_t st, bool *launched) {
         }
         if (!ok) continue;
         if ((long long)p.rows_per * ncols > (long long)CPT * kNT) continue;   // too many cells per thread
-        const size_t smem = ((size_t)nf * (p.rows_per + 2 * H) * p.nyp + (p.rows_per + 2 * H) + p.nyp) * sizeof(float);
+        // fields, the two profiles, and two 8-byte mbarriers on an 8-byte boundary
+        const size_t smem = ((((size_t)nf * (p.rows_per + 2 * H) * p.nyp + (p.rows_per + 2 * H) + p.nyp + 1) & ~(size_t)1) + 4) * sizeof(float);
         if (smem > (size_t)max_smem) continue;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(p.S * C);

@@ -11,6 +11,7 @@ struct SmallParams {
     int nsteps, adjoint, mode;                  // mode 0: plain, 1: write q, 2: read q + image
     int n_inj, inj_scale_a, n_smp, smp_div_a;
     int wave_pml;                               // 1: pz / py exist
+    int async_halo;                             // 1: halo rows by st.async + mbarrier (set by small_run), 0: plain remote stores + cluster.sync
     long long stride;                           // floats per shot per field
     float c0, cz2[5], cy2[5], cz1[5], cy1[5], dt, dt2, hdt;
     const float *w, *sigz, *sigy;
