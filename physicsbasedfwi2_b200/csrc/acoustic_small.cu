@@ -5,8 +5,9 @@
 // step is a few microseconds, but every step pays a kernel hand-over and a TMA round trip.  Here the
 // WHOLE time loop of a call is one kernel.  A shot is owned by one thread-block cluster; CTA r of the
 // cluster keeps a band of rows of u, u-, pz, py (plus order/2 halo rows) in its shared memory for the
-// entire loop, the CTAs exchange their edge rows through distributed shared memory after every step,
-// and two cluster barriers per step replace the kernel boundary.  HBM sees only what the algorithm
+// entire loop, the CTAs exchange their edge rows through distributed shared memory after every step
+// (asynchronous remote stores that signal an mbarrier of the receiver: a CTA waits for its two
+// neighbours, not for the cluster).  HBM sees only what the algorithm
 // needs: the snapshot q (written once per step forward, read once per step in the adjoint), the
 // L2-resident w = v^2 dt^2 and image partials, and the receiver traces.
 //
