@@ -232,3 +232,33 @@ def test_snapshot_decimation_matches_its_oracle_restatement(cuda_lib, k, monkeyp
     # an approximation of the exact (k = 1) gradient; how close depends on how well k inner steps sample the fields (here a
     # white-noise residual and a coarse 1 ms inner step, the worst case: 3 % at k = 2, 40 % at k = 5)
     assert 0 < K.rel_l2(gv, gv1) < 0.6
+
+
+@pytest.mark.parametrize("idx", [0, 2, 4])
+def test_async_halo_rows_are_bit_identical_to_the_cluster_barrier_form(cuda_lib, idx, monkeypatch):
+    """The cluster-resident kernel moves its halo rows as st.async remote stores signalled on an mbarrier (default) or as
+    plain remote stores followed by cluster.sync (FWI_B200_SMALL_ASYNC=0): the same arithmetic, so the same bits -
+    traces, model gradient and source gradient - on a PML case, a 5-shot order-2 case and a case without PML."""
+    from physicsbasedfwi2_b200.scalar import Propagator
+    import physicsbasedfwi2_b200 as pkg
+    c = CASES[idx]
+    v = K.layered_model(c["nz"], c["ny"], seed=1)
+    x_s, x_r = K.survey(c["nz"], c["ny"], c["dx"], c["S"], c["R"], c["Ns"], seed=2, scattered=c["scattered"])
+    src = K.ricker(c["f"], c["nt"], c["dt"], 1.0 / c["f"]).reshape(-1, 1, 1).repeat(1, c["S"], c["Ns"]).contiguous()
+    grad_rec = torch.randn(c["nt"], c["S"], c["R"], generator=torch.Generator().manual_seed(3))
+    dev = torch.device("cuda:0")
+    monkeypatch.setenv("FWI_B200_SMALL", "1")
+    outs = []
+    for mode in ("1", "0"):
+        monkeypatch.setenv("FWI_B200_SMALL_ASYNC", mode)
+        vg = v.to(dev).requires_grad_(True)
+        sg = src.to(dev).requires_grad_(True)
+        n0 = pkg.kernel_launches()
+        rec = Propagator({"vp": vg}, c["dx"], pml_width=c["pml"], accuracy=c["order"])(sg, x_s.to(dev), x_r.to(dev), c["dt"])
+        (rec * grad_rec.to(dev)).sum().backward()
+        torch.cuda.synchronize()
+        assert pkg.kernel_launches() - n0 <= 12, "the cluster-resident path (one launch per time loop) was not taken"
+        outs.append((rec.detach().clone(), vg.grad.clone(), sg.grad.clone()))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+    assert float(outs[0][0].abs().max()) > 0 and float(outs[0][1].abs().max()) > 0
