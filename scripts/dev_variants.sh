@@ -1,5 +1,8 @@
 #!/bin/bash
 # Builds tuning variants of libfwi_b200.so (kernel configuration macros of csrc/acoustic.cu) into build/variants/.
+# NOTE: FWI_B200_LIB redirects the ctypes entry points only (elastic, misfit, slab, glue).  The scalar propagator goes
+# through _b200fwi_torch.so, which binds to the in-tree libfwi_b200.so: to A/B an acoustic variant copy it over the in-tree
+# file on the GPU box (scripts/gpu_small_ab.sh does).
 # usage: scripts/dev_variants.sh name "-DFWI_CFG_W2=3 -DFWI_CFG_C2=4 -DFWI_CFG_D2=1" [name2 "flags2" ...]
 set -u
 cd "$(dirname "$0")/.."
