@@ -12,7 +12,9 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_HERE, "csrc")
-SO_PATH = os.environ.get("FWI_B200_LIB") or os.path.join(_HERE, "libfwi_b200.so")   # (env: tuning variants, scripts/dev_variants.sh)
+# (FWI_B200_LIB: a tuning variant for the ctypes entry points - elastic, misfit, slab, glue; _b200fwi_torch.so, i.e. the
+# scalar propagator, is linked against the in-tree file whatever this says: scripts/dev_variants.sh)
+SO_PATH = os.environ.get("FWI_B200_LIB") or os.path.join(_HERE, "libfwi_b200.so")
 _SOURCES = ["common.cu", "acoustic.cu", "acoustic_small.cu", "elastic.cu", "misfit.cu", "host_kernels.cu", "glue.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
